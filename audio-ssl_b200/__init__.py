@@ -1,0 +1,17 @@
+"""audiossl_b200 -- B200-native drop-in for the audio-ssl upstream input path.
+
+Exports the reference's names for this path (log-mel front end, two-view augmentation) backed by
+hand-written sm_100a CUDA kernels behind the C ABI in ``include/assl.h``.  There is no CPU fallback.
+
+    from audiossl_b200 import MelSpectrogramLibrosa, extract_log_mel_spectrogram, AugmentationModule
+"""
+from . import _native
+from .augmentations import (MixupBYOLA, NormalizeBatch, PrecomputedNorm, RandomResizeCrop,  # noqa: F401
+                            RunningNorm)
+from .engine import ViewEngine, shard_bounds  # noqa: F401
+from .frontend import MelSpectrogramLibrosa, Plan, extract_log_mel_spectrogram  # noqa: F401
+from .module import AugmentationModule, UpstreamInputPipeline  # noqa: F401
+from .sampler import FastSampler, ReferenceSampler, ViewParams  # noqa: F401
+
+build = _native.build
+__version__ = "0.1.0"

@@ -1,0 +1,46 @@
+// Shared declarations for the assl CUDA sources (sm_100a only, no host fallback).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <vector>
+
+#include "../../include/assl.h"
+
+namespace assl {
+
+constexpr int kNfft = 1024;             // the FFT kernel is specialised for 32 x 32 points
+constexpr int kBins = kNfft / 2 + 1;    // 513
+constexpr int kMaxMels = 128;
+
+constexpr float kPowerEps = 2.220446049250313e-16f;   // np.finfo(float).eps   (utils.py:28)
+constexpr float kLogEps = 1.1920928955078125e-07f;    // torch.finfo().eps     (utils.py:48)
+constexpr float kF32Max = 3.4028234663852886e+38f;
+
+inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+inline int launch_status() {
+  return cudaPeekAtLastError() == cudaSuccess ? ASSL_OK : ASSL_ERR_CUDA;
+}
+
+__host__ __device__ inline long long ring_slot(long long slot0, long long b, long long cap) {
+  return cap > 0 ? (slot0 + b) % cap : slot0 + b;
+}
+
+}  // namespace assl
+
+// Plan: immutable after creation.  Device tables are owned by the library.
+struct assl_plan {
+  assl_cfg cfg;
+  int device;
+  int sm_count;
+  int nnz;                      // stored filterbank taps (contiguous support of every band)
+  float* d_win_half;            // [n_fft]      0.5 * periodic Hann (the 1/2 of the two-frame unpack folded in)
+  float2* d_twiddle;            // [32][32]     tw[k2][n1] = exp(-2 pi i n1 k2 / 1024)
+  int* d_mel_k0;                // [n_mels]     first bin of the band's support
+  int* d_mel_cnt;               // [n_mels]     bins in the support
+  int* d_mel_off;               // [n_mels]     offset into d_mel_w
+  float* d_mel_w;               // [nnz]        fp32 weights
+  std::vector<float> h_fb;      // dense [n_mels][513] copy for assl_plan_filterbank
+};

@@ -1,0 +1,245 @@
+// Running pre-normalisation statistics, batch post-normalisation, fixed-statistics normalisation.
+//
+// running_stats_kernel reproduces the reference's sequential RunningMean / RunningVariance updates
+// (/root/reference/src/augmentations/augmentations.py:222-228, 249-256, 275-281) for a whole batch
+// at once.  The reference divides by the number of samples seen BEFORE the current one, so after
+// k >= 1 updates  mu_k = mean(m_1..m_k)  (sample 0 is overwritten) and the variance tracker does
+// the same with v_j = mean((x_j - mu_j)^2) = q_j - 2 mu_j m_j + mu_j^2.  Both are prefix means, so the
+// recurrence becomes two block-wide scans over per-clip (m_j, q_j) = (sum x, sum x^2) / elems in fp64.
+#include "common.cuh"
+
+namespace assl {
+
+constexpr int kScanThreads = 1024;
+
+// inclusive scan over the block; returns this thread's prefix, *total gets the block total
+__device__ inline double block_scan_incl(double v, double* s_warp, double* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const double n = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += n;
+  }
+  __syncthreads();                 // s_warp may still be read from the previous scan
+  if (lane == 31) s_warp[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    double w = s_warp[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const double n = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += n;
+    }
+    s_warp[lane] = w;
+  }
+  __syncthreads();
+  if (warp > 0) v += s_warp[warp - 1];
+  *total = s_warp[31];
+  return v;
+}
+
+// state: [0] n_put  [1] sum of m_j (j>=1)  [2] sum of v_j (j>=1)  [3] mean  [4] std  [5..7] reserved
+__global__ void __launch_bounds__(kScanThreads) running_stats_kernel(
+    double* state, const double* sums, long long n_clips, long long n_parts, double inv_elems,
+    long long max_update, long long first, long long count, float* mean_std, long long slot0, long long cap) {
+  __shared__ double s_warp[32];
+  __shared__ float s_frozen[2];
+  const int tid = threadIdx.x;
+  const long long n0 = static_cast<long long>(state[0]);
+  double carry_m = state[1], carry_v = state[2];
+  if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); }
+  __syncthreads();
+
+  for (long long base = 0; base < n_clips; base += kScanThreads) {
+    const long long idx = base + tid;
+    const bool valid = idx < n_clips;
+    const long long k = n0 + idx;                     // put index of this clip
+    double m = 0.0, q = 0.0;
+    if (valid) {
+      double sx = 0.0, sxx = 0.0;
+      for (long long p = 0; p < n_parts; ++p) {
+        sx += sums[(idx * n_parts + p) * 2];
+        sxx += sums[(idx * n_parts + p) * 2 + 1];
+      }
+      m = sx * inv_elems;
+      q = sxx * inv_elems;
+    }
+    const bool active = valid && k < max_update;
+    const bool counted = active && k >= 1;
+    double tot;
+    const double pm = block_scan_incl(counted ? m : 0.0, s_warp, &tot) + carry_m;
+    carry_m += tot;
+    const double mu = (k == 0) ? m : pm / static_cast<double>(k);
+    double v = q - 2.0 * mu * m + mu * mu;
+    v = v > 0.0 ? v : 0.0;
+    const double pv = block_scan_incl(counted ? v : 0.0, s_warp, &tot) + carry_v;
+    carry_v += tot;
+    const double s2 = (k == 0) ? v : pv / static_cast<double>(k);
+    float my_mean = 0.f, my_std = 1.f;
+    if (active) {
+      my_mean = static_cast<float>(mu);
+      my_std = fminf(fmaxf(sqrtf(static_cast<float>(s2)), kLogEps), kF32Max);   // clamp(std, eps, max) :281
+      if (k == max_update - 1 || idx == n_clips - 1) { s_frozen[0] = my_mean; s_frozen[1] = my_std; }
+    }
+    __syncthreads();
+    if (valid && !active) { my_mean = s_frozen[0]; my_std = s_frozen[1]; }     // statistics frozen :276
+    if (valid && idx >= first && idx < first + count) {
+      const long long s = ring_slot(slot0, idx - first, cap);
+      mean_std[2 * s] = my_mean;
+      mean_std[2 * s + 1] = my_std;
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    long long n1 = n0;
+    if (n0 < max_update) n1 = (n0 + n_clips < max_update) ? n0 + n_clips : max_update;
+    state[0] = static_cast<double>(n1);
+    state[1] = carry_m;
+    state[2] = carry_v;
+    state[3] = s_frozen[0];
+    state[4] = s_frozen[1];
+  }
+}
+
+__global__ void clip_sums_kernel(const double* tile_sums, long long B, long long n_parts, double* clip_sums) {
+  const long long b = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (b >= B) return;
+  double sx = 0.0, sxx = 0.0;
+  for (long long p = 0; p < n_parts; ++p) { sx += tile_sums[(b * n_parts + p) * 2]; sxx += tile_sums[(b * n_parts + p) * 2 + 1]; }
+  clip_sums[2 * b] = sx;
+  clip_sums[2 * b + 1] = sxx;
+}
+
+// per-clip (sum x, sum x^2) in fp64, one CTA per clip
+__global__ void __launch_bounds__(256) clip_moments_kernel(const float* x, long long elems, double* sums) {
+  __shared__ double s_red[16];
+  const float* src = x + blockIdx.x * elems;
+  double s1 = 0.0, s2 = 0.0;
+  for (long long i = threadIdx.x; i < elems; i += 256) { const double v = src[i]; s1 += v; s2 += v * v; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { s1 += __shfl_down_sync(0xffffffffu, s1, o); s2 += __shfl_down_sync(0xffffffffu, s2, o); }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { s_red[2 * warp] = s1; s_red[2 * warp + 1] = s2; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double r1 = 0.0, r2 = 0.0;
+    for (int w = 0; w < 8; ++w) { r1 += s_red[2 * w]; r2 += s_red[2 * w + 1]; }
+    sums[2 * blockIdx.x] = r1;
+    sums[2 * blockIdx.x + 1] = r2;
+  }
+}
+
+__global__ void __launch_bounds__(256) clip_normalize_kernel(const float* x, float* y, long long elems, const float* mean_std,
+                                                              long long slot0, long long cap) {
+  const long long s = ring_slot(slot0, blockIdx.y, cap);
+  const float mean = mean_std[2 * s], std = mean_std[2 * s + 1];
+  const float* src = x + blockIdx.y * elems;
+  float* dst = y + blockIdx.y * elems;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < elems; i += gridDim.x * 256ll) dst[i] = (src[i] - mean) / std;
+}
+
+// ---- NormalizeBatch (augmentations.py:321-324): sums in fp64, one atomic triple per CTA
+__global__ void __launch_bounds__(256) batch_sums_kernel(const float* x, long long n, double* sums) {
+  __shared__ double s_red[16];
+  double s1 = 0.0, s2 = 0.0;
+  const long long stride = static_cast<long long>(gridDim.x) * 256;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n; i += stride) {
+    const double v = x[i];
+    s1 += v; s2 += v * v;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { s1 += __shfl_down_sync(0xffffffffu, s1, o); s2 += __shfl_down_sync(0xffffffffu, s2, o); }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { s_red[2 * warp] = s1; s_red[2 * warp + 1] = s2; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double r1 = 0.0, r2 = 0.0;
+    for (int w = 0; w < 8; ++w) { r1 += s_red[2 * w]; r2 += s_red[2 * w + 1]; }
+    atomicAdd(&sums[1], r1);
+    atomicAdd(&sums[2], r2);
+    if (blockIdx.x == 0) atomicAdd(&sums[0], static_cast<double>(n));
+  }
+}
+
+__global__ void __launch_bounds__(256) normalize_apply_kernel(const float* x, float* y, long long n, const double* sums) {
+  const double cnt = sums[0];
+  const double mean = sums[1] / cnt;
+  double var = (sums[2] - cnt * mean * mean) / (cnt - 1.0);     // torch.std default: unbiased
+  var = var > 0.0 ? var : 0.0;
+  const float fmean = static_cast<float>(mean);
+  const float fstd = fminf(fmaxf(static_cast<float>(sqrt(var)), kLogEps), kF32Max);
+  const long long stride = static_cast<long long>(gridDim.x) * 256;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n; i += stride) y[i] = (x[i] - fmean) / fstd;
+}
+
+__global__ void __launch_bounds__(256) affine_norm_kernel(const float* x, float* y, long long n, float mean, float std) {
+  const long long stride = static_cast<long long>(gridDim.x) * 256;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n; i += stride) y[i] = (x[i] - mean) / std;
+}
+
+inline unsigned ew_grid(long long n) {
+  long long g = (n + 255) / 256;
+  const long long cap = 148ll * 16;
+  return static_cast<unsigned>(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace assl
+
+extern "C" int assl_running_stats(double* state, const double* sums, int64_t n_clips, int64_t n_parts,
+                                  int64_t elems, int64_t max_update, int64_t first, int64_t count,
+                                  float* mean_std, int64_t slot0, int64_t cap, void* stream) {
+  using namespace assl;
+  if (!state || !sums || !mean_std || n_clips < 0 || n_parts < 1 || elems < 1 || max_update < 1) return ASSL_ERR_INVALID_ARG;
+  if (first < 0 || count < 0 || first + count > n_clips || slot0 < 0 || cap < 0) return ASSL_ERR_INVALID_ARG;
+  if (cap > 0 && (count > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
+  if (n_clips == 0) return ASSL_OK;
+  running_stats_kernel<<<1, kScanThreads, 0, as_stream(stream)>>>(state, sums, n_clips, n_parts, 1.0 / static_cast<double>(elems),
+                                                                  max_update, first, count, mean_std, slot0, cap);
+  return launch_status();
+}
+
+extern "C" int assl_clip_moments_f32(const float* x, int64_t B, int64_t elems, double* sums, void* stream) {
+  if (!x || !sums || B < 0 || elems < 1) return ASSL_ERR_INVALID_ARG;
+  if (B == 0) return ASSL_OK;
+  assl::clip_moments_kernel<<<static_cast<unsigned>(B), 256, 0, assl::as_stream(stream)>>>(x, elems, sums);
+  return assl::launch_status();
+}
+
+extern "C" int assl_clip_normalize_f32(const float* x, float* y, int64_t B, int64_t elems, const float* mean_std,
+                                       int64_t slot0, int64_t cap, void* stream) {
+  if (!x || !y || !mean_std || B < 0 || B > 65535 || elems < 1 || slot0 < 0 || cap < 0) return ASSL_ERR_INVALID_ARG;
+  if (B == 0) return ASSL_OK;
+  long long gx = (elems + 255) / 256;
+  gx = gx > 64 ? 64 : gx;
+  assl::clip_normalize_kernel<<<dim3(static_cast<unsigned>(gx), static_cast<unsigned>(B)), 256, 0, assl::as_stream(stream)>>>(
+      x, y, elems, mean_std, slot0, cap);
+  return assl::launch_status();
+}
+
+extern "C" int assl_clip_sums(const double* tile_sums, int64_t B, int64_t n_parts, double* clip_sums, void* stream) {
+  if (!tile_sums || !clip_sums || B < 0 || n_parts < 1) return ASSL_ERR_INVALID_ARG;
+  if (B == 0) return ASSL_OK;
+  assl::clip_sums_kernel<<<static_cast<unsigned>((B + 255) / 256), 256, 0, assl::as_stream(stream)>>>(tile_sums, B, n_parts, clip_sums);
+  return assl::launch_status();
+}
+
+extern "C" int assl_batch_sums(const float* x, int64_t n, double* sums, void* stream) {
+  if (!x || !sums || n < 0) return ASSL_ERR_INVALID_ARG;
+  if (n == 0) return ASSL_OK;
+  assl::batch_sums_kernel<<<assl::ew_grid(n), 256, 0, assl::as_stream(stream)>>>(x, n, sums);
+  return assl::launch_status();
+}
+
+extern "C" int assl_normalize_apply_f32(const float* x, float* y, int64_t n, const double* sums, void* stream) {
+  if (!x || !y || !sums || n < 0) return ASSL_ERR_INVALID_ARG;
+  if (n == 0) return ASSL_OK;
+  assl::normalize_apply_kernel<<<assl::ew_grid(n), 256, 0, assl::as_stream(stream)>>>(x, y, n, sums);
+  return assl::launch_status();
+}
+
+extern "C" int assl_affine_norm_f32(const float* x, float* y, int64_t n, float mean, float std, void* stream) {
+  if (!x || !y || n < 0) return ASSL_ERR_INVALID_ARG;
+  if (n == 0) return ASSL_OK;
+  assl::affine_norm_kernel<<<assl::ew_grid(n), 256, 0, assl::as_stream(stream)>>>(x, y, n, mean, std);
+  return assl::launch_status();
+}

@@ -1,0 +1,230 @@
+// Fused two-view generation: pre-normalise -> log-mixup-exp against a bank entry -> zero-canvas
+// crop -> bicubic / bilinear resample, one CTA per (clip, view, tile of output frames).
+//
+// Replaces the body of AugmentationModule.__call__ (/root/reference/src/augmentations/__init__.py:32-35):
+//   RunningNorm.forward's (x - mean) / std            augmentations.py:282
+//   MixupBYOLA.forward / log_mixup_exp                augmentations.py:99-106, 8-12
+//   RandomResizeCrop.forward                          augmentations.py:40-55
+// with every random draw (alpha, bank entry, crop box) passed in.
+//
+// The resampler follows ATen's upsample_bicubic2d / upsample_bilinear2d with align_corners=True
+// (what F.interpolate reaches at augmentations.py:53-54): source coordinate dst * (in-1)/(out-1)
+// in fp32, A = -0.75 cubic convolution weights, taps clamped to the CROP, rows nested over columns.
+// It is evaluated separably: stage A mixes the needed crop span once into shared memory (3 MUFU
+// per source pixel instead of per tap), stage B resamples along time, stage C along frequency.
+#include "common.cuh"
+
+namespace assl {
+
+constexpr int kViewThreads = 256;
+constexpr int kSrcPad = 8;
+
+struct ViewArgs {
+  assl_view_cfg c;
+  const float* lms;
+  const float* mean_std;
+  long long cap, B;
+  const int* clip_slot;
+  const int* mix_slot;
+  const float* alpha;
+  const int* crop;
+  float* view1;
+  float* view2;
+  int tiles_t;     // output-time tiles per view
+  int src_w;       // staged source columns per tile (row stride of the source tile)
+  int y0, x0;      // where the clip sits in the canvas (augmentations.py:47)
+};
+
+__device__ __forceinline__ float cubic1(float x) {   // |x| <= 1
+  const float A = -0.75f;
+  return ((A + 2.f) * x - (A + 3.f)) * x * x + 1.f;
+}
+__device__ __forceinline__ float cubic2(float x) {   // 1 < |x| < 2
+  const float A = -0.75f;
+  return ((A * x - 5.f * A) * x + 8.f * A) * x - 4.f * A;
+}
+
+// ATen area_pixel_compute_scale (align_corners=True) + guard_index_and_lambda
+__device__ __forceinline__ void source_index(int dst, int n_in, int n_out, int* idx, float* lam) {
+  const float scale = n_out > 1 ? static_cast<float>(n_in - 1) / static_cast<float>(n_out - 1) : 0.f;
+  const float real = scale * static_cast<float>(dst);
+  int i = static_cast<int>(floorf(real));
+  i = i < n_in - 1 ? i : n_in - 1;
+  *idx = i;
+  *lam = fminf(fmaxf(real - static_cast<float>(i), 0.f), 1.f);
+}
+
+__device__ __forceinline__ void tap_weights(float t, int bilinear, float w[4]) {
+  if (bilinear) {
+    w[0] = 0.f; w[1] = 1.f - t; w[2] = t; w[3] = 0.f;
+  } else {
+    w[0] = cubic2(t + 1.f); w[1] = cubic1(t); w[2] = cubic1(1.f - t); w[3] = cubic2(2.f - t);
+  }
+}
+
+__host__ __device__ inline size_t views_smem_bytes(int canvas_h, int src_w, int tw, int n_freq) {
+  return sizeof(float) * (static_cast<size_t>(canvas_h) * src_w + static_cast<size_t>(canvas_h) * tw) +
+         (sizeof(float) + sizeof(int)) * 4 * static_cast<size_t>(n_freq);
+}
+
+template <int TW>
+__global__ void __launch_bounds__(kViewThreads) two_views_kernel(const ViewArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int F = a.c.n_freq, T = a.c.n_time;
+  float4* s_wy = reinterpret_cast<float4*>(smem_raw);                // [F]         frequency tap weights
+  int4* s_ya = reinterpret_cast<int4*>(s_wy + F);                    // [F]         frequency tap rows
+  float* s_src = reinterpret_cast<float*>(s_ya + F);                 // [h][src_w]  mixed crop span
+  float* s_h = s_src + static_cast<size_t>(a.c.canvas_h) * a.src_w;  // [h][TW]     time-resampled rows
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  long long blk = blockIdx.x;
+  const int tile = static_cast<int>(blk % a.tiles_t); blk /= a.tiles_t;
+  const int v = static_cast<int>(blk & 1);
+  const long long b = blk >> 1;
+
+  const int* cr = a.crop + (b * 2 + v) * 4;
+  // the host mirror validates crops; the clamps only keep a bad box from leaving shared memory
+  const int h = min(max(cr[2], 1), a.c.canvas_h), w = min(max(cr[3], 1), a.c.canvas_w);
+  const int ci = min(max(cr[0], 0), a.c.canvas_h - h), cj = min(max(cr[1], 0), a.c.canvas_w - w);
+  const int bil = a.c.interp;
+
+  const int ox0 = tile * TW;
+  const int ncol = min(TW, T - ox0);
+  // crop columns this tile's taps can touch
+  int ix_lo, ix_hi; float lam;
+  source_index(ox0, w, T, &ix_lo, &lam);
+  source_index(ox0 + ncol - 1, w, T, &ix_hi, &lam);
+  const int xs_lo = max(ix_lo - 1, 0);
+  const int xs_hi = min(ix_hi + 2, w - 1);
+  const int nsx = min(xs_hi - xs_lo + 1, a.src_w);
+
+  // ---- frequency-axis taps, shared by every column of the tile
+  for (int oy = tid; oy < F; oy += kViewThreads) {
+    int iy; float ty;
+    source_index(oy, h, F, &iy, &ty);
+    float wt[4];
+    tap_weights(ty, bil, wt);
+    s_wy[oy] = make_float4(wt[0], wt[1], wt[2], wt[3]);
+    s_ya[oy] = make_int4(min(max(iy - 1, 0), h - 1), min(max(iy, 0), h - 1),
+                         min(max(iy + 1, 0), h - 1), min(max(iy + 2, 0), h - 1));
+  }
+
+  // ---- stage A: normalise + mix the crop span [0,h) x [xs_lo, xs_lo+nsx) into shared memory
+  {
+    const long long plane = static_cast<long long>(F) * T;
+    const int xslot = a.clip_slot[b];
+    const float* xp = a.lms + xslot * plane;
+    float mu = 0.f, inv = 1.f;
+    if (a.mean_std) { mu = a.mean_std[2 * xslot]; inv = 1.f / a.mean_std[2 * xslot + 1]; }
+    const int zslot = a.mix_slot[b * 2 + v];
+    const bool mix = zslot >= 0;
+    const float* zp = a.lms + (mix ? zslot : 0) * plane;
+    float zmu = 0.f, zinv = 1.f;
+    if (mix && a.mean_std) { zmu = a.mean_std[2 * zslot]; zinv = 1.f / a.mean_std[2 * zslot + 1]; }
+    const float al = a.alpha[b * 2 + v];
+    const float wx = 1.f - al, wz = al;
+    for (int y = warp; y < h; y += kViewThreads / 32) {
+      const int ly = ci + y - a.y0;
+      const bool row_in = ly >= 0 && ly < F;
+      for (int xs = lane; xs < nsx; xs += 32) {
+        const int lx = cj + xs_lo + xs - a.x0;
+        float val = 0.f;                                   // zero canvas outside the pasted clip
+        if (row_in && lx >= 0 && lx < T) {
+          const long long o = static_cast<long long>(ly) * T + lx;
+          const float xn = (__ldg(xp + o) - mu) * inv;
+          if (mix) {
+            const float zn = (__ldg(zp + o) - zmu) * zinv;
+            val = a.c.log_mixup ? __logf(wx * __expf(xn) + wz * __expf(zn) + kLogEps) : wz * zn + wx * xn;
+          } else {
+            val = xn;
+          }
+        }
+        s_src[y * a.src_w + xs] = val;
+      }
+    }
+  }
+  __syncthreads();
+
+  const int col = tid % TW, rg = tid / TW;
+  constexpr int kRowGroups = kViewThreads / TW;
+  const bool col_on = col < ncol;
+
+  // ---- stage B: along time.  Each thread owns one output column (taps and weights in registers).
+  if (col_on) {
+    int ix; float tx;
+    source_index(ox0 + col, w, T, &ix, &tx);
+    float wt[4];
+    tap_weights(tx, bil, wt);
+    int xi[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) xi[q] = min(max(min(max(ix - 1 + q, 0), w - 1) - xs_lo, 0), nsx - 1);
+    for (int y = rg; y < h; y += kRowGroups) {
+      const float* row = s_src + y * a.src_w;
+      float acc = row[xi[0]] * wt[0];
+      acc = fmaf(row[xi[1]], wt[1], acc);
+      acc = fmaf(row[xi[2]], wt[2], acc);
+      acc = fmaf(row[xi[3]], wt[3], acc);
+      s_h[y * TW + col] = acc;
+    }
+  }
+  __syncthreads();
+
+  // ---- stage C: along frequency, coalesced store
+  if (col_on) {
+    float* outp = (v == 0 ? a.view1 : a.view2) + b * (static_cast<long long>(F) * T) + ox0 + col;
+    for (int oy = rg; oy < F; oy += kRowGroups) {
+      const float4 wy = s_wy[oy];
+      const int4 ya = s_ya[oy];
+      float acc = s_h[ya.x * TW + col] * wy.x;
+      acc = fmaf(s_h[ya.y * TW + col], wy.y, acc);
+      acc = fmaf(s_h[ya.z * TW + col], wy.z, acc);
+      acc = fmaf(s_h[ya.w * TW + col], wy.w, acc);
+      outp[static_cast<long long>(oy) * T] = acc;
+    }
+  }
+}
+
+template <int TW>
+int launch_views(ViewArgs& a, cudaStream_t st) {
+  a.tiles_t = (a.c.n_time + TW - 1) / TW;
+  const size_t smem = views_smem_bytes(a.c.canvas_h, a.src_w, TW, a.c.n_freq);
+  if (smem > 227 * 1024) return ASSL_ERR_UNSUPPORTED;
+  if (cudaFuncSetAttribute(two_views_kernel<TW>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
+    return ASSL_ERR_CUDA;
+  const long long grid = a.B * 2 * a.tiles_t;
+  if (grid > 0x7fffffffll) return ASSL_ERR_UNSUPPORTED;
+  two_views_kernel<TW><<<static_cast<unsigned>(grid), kViewThreads, smem, st>>>(a);
+  return launch_status();
+}
+
+}  // namespace assl
+
+extern "C" int assl_two_views_f32(const assl_view_cfg* vc, const float* lms, const float* mean_std, int64_t cap,
+                                  const int32_t* clip_slot, const int32_t* mix_slot, const float* alpha,
+                                  const int32_t* crop, int64_t B, float* view1, float* view2, void* stream) {
+  using namespace assl;
+  if (!vc || !lms || !clip_slot || !mix_slot || !alpha || !crop || !view1 || !view2 || B < 0) return ASSL_ERR_INVALID_ARG;
+  if (vc->n_freq < 1 || vc->n_time < 1 || vc->canvas_h < vc->n_freq || vc->canvas_w < vc->n_time) return ASSL_ERR_INVALID_ARG;
+  if (vc->interp != 0 && vc->interp != 1) return ASSL_ERR_INVALID_ARG;
+  if (B == 0) return ASSL_OK;
+  ViewArgs a;
+  a.c = *vc; a.lms = lms; a.mean_std = mean_std; a.cap = cap; a.B = B;
+  a.clip_slot = clip_slot; a.mix_slot = mix_slot; a.alpha = alpha; a.crop = crop;
+  a.view1 = view1; a.view2 = view2;
+  a.y0 = (vc->canvas_h - vc->n_freq) / 2;
+  a.x0 = (vc->canvas_w - vc->n_time) / 2;
+  // widest crop span a TW-column tile can touch: (TW-1) * max scale + 4 taps, never more than the canvas
+  const int T = vc->n_time;
+  const double smax = T > 1 ? static_cast<double>(vc->canvas_w - 1) / (T - 1) : 0.0;
+  auto span = [&](int tw) {
+    const int cols = tw < T ? tw : T;
+    long long s = static_cast<long long>((cols - 1) * smax) + 5;
+    if (s > vc->canvas_w) s = vc->canvas_w;
+    return static_cast<int>((s + kSrcPad - 1) / kSrcPad * kSrcPad) + 1;     // odd-ish stride spreads banks
+  };
+  int rc = ASSL_ERR_UNSUPPORTED;
+  if (T > 64) { a.src_w = span(128); rc = launch_views<128>(a, as_stream(stream)); }
+  if (rc == ASSL_ERR_UNSUPPORTED && T > 32) { a.src_w = span(64); rc = launch_views<64>(a, as_stream(stream)); }
+  if (rc == ASSL_ERR_UNSUPPORTED) { a.src_w = span(32); rc = launch_views<32>(a, as_stream(stream)); }
+  return rc;
+}

@@ -1,0 +1,158 @@
+"""Device-side state and launch plumbing shared by the drop-in augmentation classes.
+
+``ViewEngine`` owns (through the torch caching allocator -- the C library owns no data buffers):
+  * the log-mel RING: ``cap`` slots of ``[F, T]`` fp32.  Clip ``g`` of this process lives in slot
+    ``g % cap``; the spectrogram the front end writes there is also the clip's future mixup-bank
+    entry, so the FIFO of the reference's ``MixupBYOLA`` (augmentations.py:95, 109) never copies;
+  * the statistics ring ``[cap, 2]`` (mean, std current when each clip was normalised -- normalising
+    a bank entry on the fly equals storing the normalised tensor as the reference does);
+  * the running-norm state (8 doubles) of ``RunningNorm`` (augmentations.py:259-282).
+
+One process per GPU; with ``torch.distributed`` initialised and ``sync_stats=True`` the per-clip
+(sum, sum of squares) pairs are all-gathered (rank-major = global clip order) so every rank runs the
+identical statistics scan; the bank stays rank-local, as each reference worker's does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _native
+from .frontend import _ptr, _stream_ptr
+from .sampler import ViewParams, canvas_size, validate_crops
+
+INTERP = {"bicubic": 0, "bilinear": 1}
+
+
+def _dist_world():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_bounds(n_global: int, rank: int, world: int):
+    """Contiguous block split of a global batch by clip index."""
+    base, rem = divmod(n_global, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def gather_clip_sums(local):
+    """All-gather per-clip (sum, sum of squares) [b, 2] -> [world*b, 2] in rank-major order, which is
+    the global clip order of the contiguous block split.  NCCL on GPUs, gloo in the CPU tests."""
+    import torch.distributed as dist
+    world = dist.get_world_size()
+    gathered = torch.empty((world * local.shape[0], 2), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(gathered, local.contiguous())
+    return gathered
+
+
+class ViewEngine:
+    def __init__(self, n_memory=2048, pushes_per_clip=2, ratio=0.4, log_mixup=True,
+                 virtual_crop_scale=(1.0, 1.5), interp="bicubic", normalize=True, max_update=None,
+                 max_batch=4096, sync_stats=True):
+        if interp not in INTERP:
+            raise ValueError(f"interp must be one of {sorted(INTERP)}")
+        self.n_memory, self.nv = int(n_memory), int(pushes_per_clip)
+        self.log_mixup, self.vscale, self.interp = bool(log_mixup), tuple(virtual_crop_scale), interp
+        self.normalize, self.max_update = bool(normalize), max_update
+        if normalize and (max_update is None or max_update < 1):
+            raise ValueError("RunningNorm needs max_update >= 1 (epoch_samples * max_update_epochs)")
+        self.max_batch, self.sync_stats = int(max_batch), sync_stats
+        self.history = -(-self.n_memory // self.nv)          # distinct clips the FIFO can still hold
+        self.cap = self.history + self.max_batch
+        self.clips_done = 0
+        self.ring = self.stats = self.state = None
+        self.f = self.t = None
+
+    # ------------------------------------------------------------------ buffers
+    def ensure(self, f, t, device):
+        if self.ring is None:
+            self.f, self.t = int(f), int(t)
+            self.ring = torch.empty((self.cap, self.f, self.t), dtype=torch.float32, device=device)
+            self.stats = torch.zeros((self.cap, 2), dtype=torch.float32, device=device)
+            self.stats[:, 1] = 1.0
+            self.state = torch.zeros(8, dtype=torch.float64, device=device)
+        elif (self.f, self.t) != (int(f), int(t)):
+            raise ValueError(f"clip shape changed from {(self.f, self.t)} to {(f, t)}: the mixup bank holds one shape")
+
+    @property
+    def slot0(self):
+        return self.clips_done % self.cap
+
+    def ring_put(self, x):
+        """Copy a [B, F, T] batch into the ring at the current head (at most two slice copies)."""
+        b, s0 = x.shape[0], self.slot0
+        first = min(b, self.cap - s0)
+        self.ring[s0:s0 + first].copy_(x[:first])
+        if first < b:
+            self.ring[:b - first].copy_(x[first:])
+
+    # ------------------------------------------------------------------ statistics
+    def update_stats(self, sums, n_parts):
+        """sums: [B, n_parts, 2] fp64 on device for this rank's clips, in order."""
+        lib = _native.lib()
+        b = sums.shape[0]
+        rank, world = _dist_world()
+        elems = self.f * self.t
+        if world > 1 and self.sync_stats:
+            local = torch.empty((b, 2), dtype=torch.float64, device=sums.device)
+            _native.check(lib.assl_clip_sums(_ptr(sums), b, n_parts, _ptr(local), _stream_ptr()))
+            gathered = gather_clip_sums(local)
+            _native.check(lib.assl_running_stats(_ptr(self.state), _ptr(gathered), world * b, 1, elems,
+                                                 int(self.max_update), rank * b, b, _ptr(self.stats),
+                                                 self.slot0, self.cap, _stream_ptr()), "assl_running_stats")
+        else:
+            _native.check(lib.assl_running_stats(_ptr(self.state), _ptr(sums), b, n_parts, elems,
+                                                 int(self.max_update), 0, b, _ptr(self.stats),
+                                                 self.slot0, self.cap, _stream_ptr()), "assl_running_stats")
+
+    def moments(self, x):
+        sums = torch.empty((x.shape[0], 1, 2), dtype=torch.float64, device=x.device)
+        _native.check(_native.lib().assl_clip_moments_f32(_ptr(x), x.shape[0], x[0].numel(), _ptr(sums), _stream_ptr()))
+        return sums
+
+    # ------------------------------------------------------------------ views
+    def launch_views(self, params: ViewParams, batch: int, device):
+        """Two views of the ``batch`` clips at the ring head, then advance the head."""
+        ch, cw = canvas_size(self.f, self.t, self.vscale)
+        validate_crops(params.crop, ch, cw)
+        g0 = self.clips_done
+        src = params.src_clip
+        if np.any(src >= g0 + batch) or np.any((src >= 0) & (src < g0 + batch - self.cap)):
+            raise ValueError("mixup source outside the bank ring")
+        mix_slot = np.where(src >= 0, src % self.cap, -1).astype(np.int32)
+        clip_slot = ((g0 + np.arange(batch, dtype=np.int64)) % self.cap).astype(np.int32)
+        d_mix = torch.from_numpy(mix_slot).to(device, non_blocking=True)
+        d_clip = torch.from_numpy(clip_slot).to(device, non_blocking=True)
+        d_alpha = torch.from_numpy(np.ascontiguousarray(params.alpha, np.float32)).to(device, non_blocking=True)
+        d_crop = torch.from_numpy(np.ascontiguousarray(params.crop, np.int32)).to(device, non_blocking=True)
+        v1 = torch.empty((batch, 1, self.f, self.t), dtype=torch.float32, device=device)
+        v2 = torch.empty_like(v1)
+        vcfg = _native.ViewCfg(self.f, self.t, ch, cw, INTERP[self.interp], 1 if self.log_mixup else 0)
+        _native.check(_native.lib().assl_two_views_f32(
+            C.byref(vcfg), _ptr(self.ring), _ptr(self.stats if self.normalize else None), self.cap,
+            _ptr(d_clip), _ptr(d_mix), _ptr(d_alpha), _ptr(d_crop), batch, _ptr(v1), _ptr(v2), _stream_ptr()),
+            "assl_two_views_f32")
+        self.clips_done += batch
+        return v1, v2
+
+    # ------------------------------------------------------------------ checkpointing (the reference saves none of this)
+    def state_dict(self):
+        return {"clips_done": self.clips_done, "cap": self.cap,
+                "ring": None if self.ring is None else self.ring.cpu(),
+                "stats": None if self.stats is None else self.stats.cpu(),
+                "state": None if self.state is None else self.state.cpu()}
+
+    def load_state_dict(self, sd, device=None):
+        if sd["ring"] is not None:
+            if sd["cap"] != self.cap:
+                raise ValueError("ring capacity differs (n_memory / max_batch changed)")
+            device = device or torch.device("cuda", torch.cuda.current_device())
+            self.ensure(sd["ring"].shape[1], sd["ring"].shape[2], device)
+            self.ring.copy_(sd["ring"]); self.stats.copy_(sd["stats"]); self.state.copy_(sd["state"])
+        self.clips_done = int(sd["clips_done"])

@@ -1,0 +1,125 @@
+"""Drop-in for the reference's log-mel front end, running on the GPU.
+
+Mirrors ``MelSpectrogramLibrosa`` and ``extract_log_mel_spectrogram``
+(/root/reference/src/utils/utils.py:20-28, 43-49): same names, same constructor arguments, same
+result shapes (``[n_mels, T]`` per clip).  Additionally accepts a leading batch dimension
+(``[B, L]`` -> ``[B, n_mels, T]``).  CPU tensors / numpy arrays are copied to the current CUDA
+device; results are CUDA tensors.  There is no CPU implementation here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _native
+
+
+def _stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def as_cuda_f32(x, device=None):
+    if not torch.cuda.is_available():
+        raise RuntimeError("audiossl_b200 needs a CUDA device: the CUDA kernels are the only implementation")
+    if not isinstance(x, torch.Tensor):
+        x = torch.as_tensor(np.asarray(x))
+    if device is None:
+        device = x.device if x.is_cuda else torch.device("cuda", torch.cuda.current_device())
+    return x.to(device=device, dtype=torch.float32, non_blocking=True).contiguous()
+
+
+class Plan:
+    """Owns one ``assl_plan`` (window, twiddles, sparse filterbank on the current device)."""
+
+    def __init__(self, fs=16000, n_fft=1024, shift=160, n_mels=64, fmin=60, fmax=7800):
+        lib = _native.lib()
+        self.cfg = _native.Cfg(int(fs), int(n_fft), int(shift), int(n_mels), float(fmin),
+                               float(fmax) if fmax is not None else 0.0)
+        self.handle = C.c_void_p()
+        _native.check(lib.assl_plan_create(C.byref(self.handle), C.byref(self.cfg)), "assl_plan_create")
+        self.device = torch.cuda.current_device()
+        self.n_mels, self.hop, self.n_fft = int(n_mels), int(shift), int(n_fft)
+
+    def num_frames(self, n_samples):
+        t = _native.lib().assl_plan_num_frames(self.handle, int(n_samples))
+        if t < 0:
+            raise ValueError(f"clip of {n_samples} samples is too short: reflect padding needs more than n_fft/2")
+        return int(t)
+
+    def num_tiles(self, n_samples):
+        return int(_native.lib().assl_plan_num_tiles(self.handle, int(n_samples)))
+
+    def filterbank(self):
+        out = np.empty((self.n_mels, self.n_fft // 2 + 1), np.float32)
+        _native.check(_native.lib().assl_plan_filterbank(self.handle, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def logmel_into(self, wave, out, slot0=0, cap=0, tile_sums=None, gain=None, power=False):
+        """wave [B, L] cuda fp32 -> out (ring or [B, n_mels, T]); all on the current stream."""
+        b, n = wave.shape
+        _native.check(_native.lib().assl_logmel_f32(
+            self.handle, _ptr(wave), _ptr(gain), b, n, wave.stride(0), _ptr(out), int(slot0), int(cap),
+            _ptr(tile_sums), 1 if power else 0, _stream_ptr()), "assl_logmel_f32")
+
+    def __del__(self):
+        try:
+            if self.handle:
+                _native.lib().assl_plan_destroy(self.handle)
+                self.handle = C.c_void_p()
+        except Exception:
+            pass
+
+
+class MelSpectrogramLibrosa:
+    """Mel spectrogram with librosa 0.8.1 semantics (utils.py:20-28), computed by the fused kernel.
+
+    ``__call__(audio)`` returns the mel POWER spectrogram like the reference; use
+    :func:`extract_log_mel_spectrogram` (or :meth:`log_mel`) for the log-mel, which takes the log
+    inside the same kernel.
+    """
+
+    def __init__(self, fs=16000, n_fft=1024, shift=160, n_mels=64, fmin=60, fmax=7800):
+        self.fs, self.n_fft, self.shift, self.n_mels, self.fmin, self.fmax = fs, n_fft, shift, n_mels, fmin, fmax
+        self.plan = Plan(fs, n_fft, shift, n_mels, fmin, fmax)
+
+    @property
+    def mfb(self):
+        return self.plan.filterbank()
+
+    def _run(self, audio, power, l2_normalize=False):
+        wave = as_cuda_f32(audio)
+        single = wave.dim() == 1
+        if single:
+            wave = wave.unsqueeze(0)
+        if wave.dim() != 2:
+            raise ValueError("expected a waveform [L] or a batch [B, L]")
+        with torch.cuda.device(wave.device):
+            t = self.plan.num_frames(wave.shape[1])
+            out = torch.empty((wave.shape[0], self.n_mels, t), dtype=torch.float32, device=wave.device)
+            gain = None
+            if l2_normalize:
+                gain = torch.empty(wave.shape[0], dtype=torch.float32, device=wave.device)
+                _native.check(_native.lib().assl_wave_l2_gain_f32(
+                    _ptr(wave), wave.shape[0], wave.shape[1], wave.stride(0), _ptr(gain), _stream_ptr()))
+            self.plan.logmel_into(wave, out, gain=gain, power=power)
+        return out[0] if single else out
+
+    def __call__(self, audio):
+        return self._run(audio, power=True)
+
+    def log_mel(self, audio, l2_normalize=False):
+        """Fused log-mel; ``l2_normalize`` folds ``F.normalize(waveform, p=2)`` (upstream_dataset.py:62-63) in."""
+        return self._run(audio, power=False, l2_normalize=l2_normalize)
+
+
+def extract_log_mel_spectrogram(waveform, to_mel_spec):
+    """utils.py:43-49: ``(to_mel_spec(waveform) + eps).log()`` -- here one fused kernel."""
+    if not isinstance(to_mel_spec, MelSpectrogramLibrosa):
+        raise TypeError("to_mel_spec must be audiossl_b200.MelSpectrogramLibrosa")
+    return to_mel_spec.log_mel(waveform)

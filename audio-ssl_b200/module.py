@@ -1,0 +1,142 @@
+"""``AugmentationModule`` drop-in (/root/reference/src/augmentations/__init__.py:5-35) and the fused
+waveform -> two-views pipeline built on the same engine.
+
+The reference composes ``RunningNorm`` (once per clip) with ``Sequential(MixupBYOLA, RandomResizeCrop)``
+applied twice on ONE shared MixupBYOLA instance; here that is one statistics scan plus one fused kernel
+launch per batch.  ``Kmix`` and ``PatchDrop`` entries of the shipped configs are ignored with a warning:
+in the reference they cannot run (``centroid_path: None`` fails in ``torch.load``, augmentations.py:136;
+``PatchDrop.forward`` uses an undefined name, :72-75).
+"""
+from __future__ import annotations
+
+import warnings
+
+import numpy as np
+import torch
+
+from .augmentations import _as_batch, _chunks
+from .engine import ViewEngine
+from .frontend import Plan, as_cuda_f32
+from .sampler import FastSampler, ReferenceSampler, ViewParams
+
+
+class AugmentationModule:
+    """The Augmentation Module: ``tfms(x) -> (view1, view2)``.
+
+    config / len_of_files: exactly the reference's arguments (train_upstream.py:31).
+    Extras (keyword only): ``interpolation`` ('bicubic' as the reference, or 'bilinear'), ``sampler``
+    ('reference' replays np.random / random like the reference, 'fast' is a vectorised generator, or
+    any object with ``draw(clips_done, batch, F, T) -> ViewParams``), ``max_batch`` (ring head room).
+    """
+
+    def __init__(self, config, len_of_files, *, interpolation="bicubic", sampler="reference",
+                 max_batch=4096, seed=0, sync_stats=True):
+        pre = config["pretrain"]
+        aug = pre["augmentations"]
+        for name in ("Kmix", "PatchDrop"):
+            if name in aug:
+                warnings.warn(f"{name} is not part of the accelerated path and is ignored "
+                              "(it cannot run in the reference either)", stacklevel=2)
+        mix = aug.get("MixupBYOLA")
+        rrc = aug.get("RandomResizeCrop")
+        self.has_mix, self.has_crop = mix is not None, rrc is not None
+        ratio = mix["ratio"] if mix else 0.0
+        log_mixup = mix["log_mixup_exp"] if mix else True
+        vscale = tuple(rrc["virtual_crop_scale"]) if rrc else (1.0, 1.0)
+        fscale = tuple(rrc["freq_crop_scale"]) if rrc else (1.0, 1.0)
+        tscale = tuple(rrc["time_crop_scale"]) if rrc else (1.0, 1.0)
+        # __init__.py:13-14 -- RunningNorm(epoch_samples=2*len_of_files); any other setting means no pre-norm
+        self.pre_norm = pre.get("normalization") == "mean_var"
+        max_update = 2 * len_of_files * 10 if self.pre_norm else None
+        self.engine = ViewEngine(n_memory=2048 if mix else 0, pushes_per_clip=2, ratio=ratio, log_mixup=log_mixup,
+                                 virtual_crop_scale=vscale, interp=interpolation, normalize=self.pre_norm,
+                                 max_update=max_update, max_batch=max_batch, sync_stats=sync_stats)
+        kw = dict(ratio=ratio, n_memory=2048, freq_scale=fscale, time_scale=tscale, virtual_crop_scale=vscale,
+                  pushes_per_clip=2, mixup=self.has_mix, crop=self.has_crop)
+        if sampler == "reference":
+            self.sampler = ReferenceSampler(**kw)
+        elif sampler == "fast":
+            self.sampler = FastSampler(seed=seed, **kw)
+        else:
+            self.sampler = sampler
+        self.last_params = None
+
+    # -- spectrogram in, two views out (what BaseDataset.__getitem__ calls, upstream_dataset.py:86)
+    def __call__(self, x, params: ViewParams = None):
+        xb, single = _as_batch(x)
+        eng = self.engine
+        v1s, v2s = [], []
+        with torch.cuda.device(xb.device):
+            eng.ensure(xb.shape[1], xb.shape[2], xb.device)
+            for lo, hi in _chunks(xb.shape[0], eng.max_batch):
+                part = xb[lo:hi].contiguous()
+                eng.ring_put(part)
+                if self.pre_norm:
+                    eng.update_stats(eng.moments(part), 1)
+                p = self._params(params, lo, hi)
+                a, b = eng.launch_views(p, hi - lo, xb.device)
+                v1s.append(a); v2s.append(b)
+        v1 = v1s[0] if len(v1s) == 1 else torch.cat(v1s)
+        v2 = v2s[0] if len(v2s) == 1 else torch.cat(v2s)
+        return (v1[:, 0], v2[:, 0]) if single else (v1, v2)
+
+    def _params(self, params, lo, hi):
+        if params is None:
+            p = self.sampler.draw(self.engine.clips_done, hi - lo, self.engine.f, self.engine.t)
+        else:
+            p = ViewParams(params.alpha[lo:hi], params.src_clip[lo:hi], params.bank_index[lo:hi], params.crop[lo:hi])
+        self.last_params = p
+        return p
+
+    def state_dict(self):
+        return self.engine.state_dict()
+
+    def load_state_dict(self, sd):
+        self.engine.load_state_dict(sd)
+
+
+class UpstreamInputPipeline:
+    """Waveforms in, two augmented views out, everything on the GPU:
+
+        log-mel (fused kernel, written straight into the bank ring, per-tile sums on the side)
+        -> running-statistics scan -> two-view kernel.
+
+    This is the batched equivalent of ``BaseDataset.__getitem__`` lines :62-65, :82, :86
+    (/root/reference/src/dataset/upstream_dataset.py) for a whole batch.
+    """
+
+    def __init__(self, config, len_of_files, *, to_mel_spec=None, **kw):
+        self.tfms = AugmentationModule(config, len_of_files, **kw)
+        self.plan = to_mel_spec.plan if to_mel_spec is not None else Plan()
+        self.l2 = config["pretrain"].get("normalization") == "l2"
+        self.last_lms = None
+
+    def __call__(self, waveforms, params: ViewParams = None):
+        wave = as_cuda_f32(waveforms)
+        if wave.dim() == 1:
+            wave = wave.unsqueeze(0)
+        eng, tf = self.tfms.engine, self.tfms
+        from . import _native
+        from .frontend import _ptr, _stream_ptr
+        v1s, v2s = [], []
+        with torch.cuda.device(wave.device):
+            t = self.plan.num_frames(wave.shape[1])
+            tiles = self.plan.num_tiles(wave.shape[1])
+            eng.ensure(self.plan.n_mels, t, wave.device)
+            for lo, hi in _chunks(wave.shape[0], eng.max_batch):
+                part = wave[lo:hi]
+                b = hi - lo
+                gain = None
+                if self.l2:
+                    gain = torch.empty(b, dtype=torch.float32, device=wave.device)
+                    _native.check(_native.lib().assl_wave_l2_gain_f32(_ptr(part), b, part.shape[1], part.stride(0),
+                                                                      _ptr(gain), _stream_ptr()))
+                sums = torch.empty((b, tiles, 2), dtype=torch.float64, device=wave.device) if tf.pre_norm else None
+                self.plan.logmel_into(part, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain)
+                if tf.pre_norm:
+                    eng.update_stats(sums, tiles)
+                a, c = eng.launch_views(tf._params(params, lo, hi), b, wave.device)
+                v1s.append(a); v2s.append(c)
+        v1 = v1s[0] if len(v1s) == 1 else torch.cat(v1s)
+        v2 = v2s[0] if len(v2s) == 1 else torch.cat(v2s)
+        return v1, v2

@@ -1,0 +1,357 @@
+#!/usr/bin/env python3
+"""Benchmark of the fused log-mel + two-view augmentation path (BASELINE.json metric: clips/s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A step = one pass of the hot path over one batch of synthetic waveforms per GPU (weak scaling:
+per-GPU batch fixed).  Workload at N=1: BASELINE config 2 -- n_fft 1024, hop 160, 64 mels, 60-7800 Hz,
+1 s 16 kHz clips, batch 1024.  ``value`` is measured with inputs resident in HBM (CUDA events, max over
+ranks); ``e2e`` goes through the C-ABI host entry point with pinned HOST buffers, H2D and D2H inside the
+timed region.  ``roofline`` is for the dominant kernel (log-mel) from its live CUDA-event time;
+``cpu_baseline`` times the CPU oracle port on this box's host cores on a bounded sample.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+CFG = {"pretrain": {"normalization": "mean_var", "augmentations": {
+    "MixupBYOLA": {"ratio": 0.4, "log_mixup_exp": True},
+    "RandomResizeCrop": {"virtual_crop_scale": [1.0, 1.5], "freq_crop_scale": [0.6, 1.5],
+                         "time_crop_scale": [0.6, 1.5]}}}}
+METRIC = "log-mel+2-view aug clips/sec"
+UNIT = "clips/s"
+N_MELS, HOP = 64, 160
+
+
+def algorithmic_bytes(n_samples, frontend_only=False):
+    """4L (waveform) + 4FT (log-mel, written once) [+ 8FT bank reads + 8FT two views]."""
+    t = 1 + n_samples // HOP
+    return 4 * n_samples + (4 if frontend_only else 20) * N_MELS * t
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "MEASURED_PEAKS.json"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU arm: the oracle port (numpy librosa restatement + restated augmentations), one clip at a time
+# per worker process -- the reference's own execution model (DataLoader workers, upstream_dataset.py:118-125).
+def _cpu_worker(args):
+    seed, n_clips, n_samples = args
+    os.environ["OMP_NUM_THREADS"] = os.environ["OPENBLAS_NUM_THREADS"] = os.environ["MKL_NUM_THREADS"] = "1"
+    import random
+
+    import torch
+    torch.set_num_threads(1)
+    from oracle import frontend as ofe
+    from oracle import views as ov
+    rng = np.random.default_rng(seed)
+    waves = (rng.standard_normal((n_clips, n_samples)) * 0.1).astype(np.float32)
+    np.random.seed(seed); random.seed(seed)
+    mfb = ofe.mel_filterbank()
+    tf = ov.TwoViewOracle(1000)
+    t0 = time.perf_counter()
+    for w in waves:
+        lm = torch.from_numpy(ofe.log_mel(w, mfb=mfb))
+        tf(lm.unsqueeze(0))
+    return time.perf_counter() - t0
+
+
+class CpuArm:
+    def __init__(self, n_samples, cores=None):
+        import multiprocessing as mp
+        self.n_samples = n_samples
+        self.cores = cores or max(1, min(os.cpu_count() or 1, 64))
+        os.environ.setdefault("OMP_NUM_THREADS", "1")
+        os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
+        self.pool = mp.get_context("spawn").Pool(self.cores)
+        self.pool.map(_cpu_worker, [(0, 1, n_samples)] * self.cores)      # import + warm every worker
+
+    def run(self, clips_per_worker, seed=1):
+        t0 = time.perf_counter()
+        self.pool.map(_cpu_worker, [(seed * 1000 + i, clips_per_worker, self.n_samples) for i in range(self.cores)])
+        dt = time.perf_counter() - t0
+        return self.cores * clips_per_worker / dt, dt
+
+    def close(self):
+        self.pool.close(); self.pool.join()
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's CPU implementation of the path (oracle port: librosa is not
+    installable here) on all host cores; each step is a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n_samples = int(args.seconds * 16000)
+    arm = CpuArm(n_samples)
+    per_worker = max(2, args.cpu_clips // arm.cores)
+    for _ in range(args.warmup):
+        arm.run(max(1, per_worker // 4))
+    t0 = time.perf_counter()
+    clips = 0
+    for s in range(args.steps):
+        arm.run(per_worker, seed=s + 1)
+        clips += per_worker * arm.cores
+    dt = time.perf_counter() - t0
+    arm.close()
+    val = clips / dt
+    sample = f"{per_worker * arm.cores} clips/step x {args.steps} steps of {args.seconds:g} s 16 kHz noise"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32 (fp64 FFT)", "data": "synthetic",
+        "config": workload_config(args, per_gpu_batch=per_worker * arm.cores),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": arm.cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def workload_config(args, per_gpu_batch):
+    return {"workload": f"C2: log-mel (n_fft 1024, hop 160, 64 mels, 60-7800 Hz) + BYOL-A 2-view aug, "
+                        f"{args.seconds:g} s 16 kHz clips, batch {per_gpu_batch} per GPU",
+            "clip_seconds": args.seconds, "per_gpu_batch": per_gpu_batch, "global_batch": per_gpu_batch * args.gpus,
+            "interp": "bicubic", "parallelism": f"clip-sharded x{args.gpus}",
+            "l2": f"rotating {args.rotate} input batches + ring/views footprint > 126 MB L2"}
+
+
+# ----------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([c.strip() for c in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 7 for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import audiossl_b200 as A
+    from audiossl_b200 import _native
+    from audiossl_b200.engine import gather_clip_sums
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py times the CUDA path; no GPU is visible (there is no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _native.lib()
+    P = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)  # noqa: E731
+    stream = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)  # noqa: E731
+
+    B, L, W, K = args.batch, int(args.seconds * 16000), args.warmup, args.steps
+    plan = A.Plan()
+    T, tiles = plan.num_frames(L), plan.num_tiles(L)
+    tf = A.AugmentationModule(CFG, len_of_files=10 ** 7, sampler="fast", max_batch=B, seed=1234 + rank)
+    eng = tf.engine
+    eng.ensure(N_MELS, T, dev)
+    cap = eng.cap
+    gen = torch.Generator(device="cpu").manual_seed(1234 + 2 + rank)          # seed 1234 + config id
+    host_waves = [(torch.randn(B, L, generator=gen) * 0.1).to(torch.float32).pin_memory() for _ in range(args.rotate)]
+    waves = [w.to(dev) for w in host_waves]
+    v1 = torch.empty((B, N_MELS, T), dtype=torch.float32, device=dev)
+    v2 = torch.empty_like(v1)
+    sums = torch.empty((B, tiles, 2), dtype=torch.float64, device=dev)
+    local_sums = torch.empty((B, 2), dtype=torch.float64, device=dev)
+    ch, cw = int(N_MELS * 1.0), int(T * 1.5)
+    vcfg = _native.ViewCfg(N_MELS, T, ch, cw, 0, 1)
+    max_update = int(eng.max_update)
+
+    def upload(p, clips_done):
+        mix = np.where(p.src_clip >= 0, p.src_clip % cap, -1).astype(np.int32)
+        clip = ((clips_done + np.arange(B, dtype=np.int64)) % cap).astype(np.int32)
+        return [torch.from_numpy(a).to(dev) for a in (clip, mix, np.ascontiguousarray(p.alpha), np.ascontiguousarray(p.crop))]
+
+    steps_params = [upload(tf.sampler.draw(s * B, B, N_MELS, T), s * B) for s in range(W + K)]
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(W + K)]
+
+    def device_step(s):
+        slot0 = (s * B) % cap
+        clip, mix, alpha, crop = steps_params[s]
+        e = evs[s]
+        e[0].record()
+        _native.check(lib.assl_logmel_f32(plan.handle, P(waves[s % args.rotate]), None, B, L, L, P(eng.ring), slot0, cap,
+                                          P(sums), 0, stream()))
+        e[1].record()
+        if world > 1:
+            _native.check(lib.assl_clip_sums(P(sums), B, tiles, P(local_sums), stream()))
+            gathered = gather_clip_sums(local_sums)
+            _native.check(lib.assl_running_stats(P(eng.state), P(gathered), world * B, 1, N_MELS * T, max_update,
+                                                 rank * B, B, P(eng.stats), slot0, cap, stream()))
+        else:
+            _native.check(lib.assl_running_stats(P(eng.state), P(sums), B, tiles, N_MELS * T, max_update, 0, B,
+                                                 P(eng.stats), slot0, cap, stream()))
+        e[2].record()
+        _native.check(lib.assl_two_views_f32(C.byref(vcfg), P(eng.ring), P(eng.stats), cap, P(clip), P(mix), P(alpha),
+                                             P(crop), B, P(v1), P(v2), stream()))
+        e[3].record()
+
+    def fence():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for s in range(W):
+        device_step(s)
+    fence()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.3)
+    fence()
+    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_begin.record()
+    for s in range(W, W + K):
+        device_step(s)
+    t_end.record()
+    fence()
+    ms_total = t_begin.elapsed_time(t_end)
+    k_ms = [statistics.fmean(evs[s][i].elapsed_time(evs[s][i + 1]) for s in range(W, W + K)) for i in range(3)]
+    if world > 1:
+        tmax = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        ms_total = float(tmax.item())
+
+    # ---- end to end through the C ABI with HOST buffers (H2D + kernels + D2H inside the timed region)
+    ws_bytes = lib.assl_pipeline_workspace_bytes(plan.handle, B, L, cap)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    ws[:64].zero_()
+    hv1 = torch.empty((B, N_MELS, T), dtype=torch.float32).pin_memory()
+    hv2 = torch.empty((B, N_MELS, T), dtype=torch.float32).pin_memory()
+    fast = A.FastSampler(seed=99 + rank)
+    keep = []
+
+    def host_step(s):
+        p = fast.draw(s * B, B, N_MELS, T)
+        mix = np.where(p.src_clip >= 0, p.src_clip % cap, -1).astype(np.int32)
+        alpha, crop = np.ascontiguousarray(p.alpha), np.ascontiguousarray(p.crop)
+        keep.append((mix, alpha, crop))                       # the async copies read these until the sync
+        _native.check(lib.assl_pipeline_host_f32(
+            plan.handle, C.byref(vcfg), P(ws), ws_bytes, C.c_void_p(host_waves[s % args.rotate].data_ptr()), B, L,
+            (s * B) % cap, cap, max_update, mix.ctypes.data_as(C.c_void_p), alpha.ctypes.data_as(C.c_void_p),
+            crop.ctypes.data_as(C.c_void_p), C.c_void_p(hv1.data_ptr()), C.c_void_p(hv2.data_ptr()), None, None, stream()),
+            "assl_pipeline_host_f32")
+
+    for s in range(W):
+        host_step(s)
+    fence()
+    t0 = time.perf_counter()
+    for s in range(W, W + K):
+        host_step(s)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        tmax = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        e2e_s = float(tmax.item())
+    clocks = sampler.stop() if sampler else None
+    checksum = float(hv1[0, 0, :4].sum())
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier(); dist.destroy_process_group()
+        return
+    peak, peak_src = measured_peak_gbs()
+    clips_per_s = world * B * K / (ms_total * 1e-3)
+    a_fe, a_all = algorithmic_bytes(L, True), algorithmic_bytes(L)
+    ach = B * a_fe / (k_ms[0] * 1e-3) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+            traffic = json.load(fh).get("logmel_kernel_bytes_per_launch")
+    except Exception:
+        pass
+    out = {
+        "metric": METRIC, "value": clips_per_s, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(args, B),
+        "roofline": {"bound": "hbm", "kernel": "logmel_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
+                     "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": B * a_fe, "kernel_ms": k_ms[0]},
+        "pipeline_roofline": {"achieved": clips_per_s / world * a_all / 1e9, "peak": peak, "unit": "GB/s",
+                              "frac": clips_per_s / world * a_all / 1e9 / peak, "bytes_per_clip": a_all},
+        "kernel_ms": {"logmel": k_ms[0], "running_stats(+gather)": k_ms[1], "two_views": k_ms[2]},
+        "e2e": {"value": world * B * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * L * 4 + B * 40,
+                "d2h_bytes_per_step": 2 * B * N_MELS * T * 4, "ms_per_step": 1e3 * e2e_s / K, "checksum": checksum,
+                "api": "assl_pipeline_host_f32 (pinned host waveforms in, both views back to pinned host memory)"},
+        "gpu_launches": K * (3 + (1 if world > 1 else 0)), "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu:
+        arm = CpuArm(L)
+        per_worker = max(2, args.cpu_clips // arm.cores)
+        val, dt = arm.run(per_worker)
+        arm.close()
+        out["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": arm.cores, "kind": "port",
+                               "sample": f"{per_worker * arm.cores} clips of {args.seconds:g} s noise in {dt:.1f} s, "
+                                         f"one single-threaded process per core (oracle port: numpy librosa restatement + "
+                                         f"restated reference augmentations)"}
+    print(json.dumps(out))
+    if world > 1:
+        dist.barrier(); dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=1024, help="clips per GPU per step")
+    ap.add_argument("--seconds", type=float, default=1.0, help="clip length")
+    ap.add_argument("--rotate", type=int, default=4, help="distinct input batches cycled through (L2 hygiene)")
+    ap.add_argument("--cpu-clips", type=int, default=2048, help="clips in one CPU-baseline sample")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

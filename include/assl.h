@@ -1,0 +1,178 @@
+/*
+ * assl.h -- C ABI of the B200-native audio-ssl upstream input path.
+ *
+ * Drop-in boundary for ONE hot path of Sreyan88/audio-ssl: the per-clip log-mel front end followed
+ * by the BYOL-A style two-view augmentation.  The reference is pure Python and has no FFI of its
+ * own; each entry point below states the reference interface (file:line under /root/reference)
+ * whose arithmetic it replaces.  The Python host side in ``audio-ssl_b200/`` binds these with
+ * ctypes and mirrors the reference's class names.
+ *
+ * Conventions
+ *   - every ``const float*`` / ``float*`` / ``double*`` / ``int32_t*`` argument is a raw DEVICE
+ *     pointer unless its name starts with ``host_``; the caller owns every data buffer, the
+ *     library owns only the plan-lifetime constants (window, twiddles, sparse filterbank);
+ *   - every call is asynchronous on ``stream`` (a ``cudaStream_t`` passed as ``void*``), never
+ *     synchronises, keeps no global mutable state; a plan is immutable after creation;
+ *   - return value: 0 = ASSL_OK, otherwise an ``assl_status``; nothing throws, aborts or prints;
+ *   - fp32 data, CUDA sm_100a only; there is no CPU fallback.
+ *
+ * "Ring" addressing: log-mels and their running statistics live in caller-owned rings of ``cap``
+ * clip slots so that the spectrogram written by the front end IS the future mixup-bank entry
+ * (no copy).  Slot of clip b of a call = (slot0 + b) % cap.  cap == 0 means a plain [B, ...] array.
+ */
+#ifndef ASSL_H_
+#define ASSL_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ASSL_VERSION 100 /* 0.1.0 */
+
+typedef enum assl_status {
+  ASSL_OK = 0,
+  ASSL_ERR_INVALID_ARG = 1,   /* null pointer, negative size, crop outside the canvas ...      */
+  ASSL_ERR_UNSUPPORTED = 2,   /* shape/config outside what the kernels are built for           */
+  ASSL_ERR_CUDA = 3,          /* allocation / copy / launch failure reported by the runtime    */
+  ASSL_ERR_NO_DEVICE = 4      /* no sm_100 device visible                                      */
+} assl_status;
+
+/* Front-end constants: MelSpectrogramLibrosa.__init__ defaults, src/utils/utils.py:22. */
+typedef struct assl_cfg {
+  int32_t sample_rate; /* fs     = 16000 */
+  int32_t n_fft;       /* n_fft  = 1024 (the only size the kernel is specialised for)          */
+  int32_t hop;         /* shift  = 160  (1 .. n_fft)                                           */
+  int32_t n_mels;      /* n_mels = 64   (1 .. 128)                                             */
+  float fmin;          /* fmin   = 60                                                          */
+  float fmax;          /* fmax   = 7800 (<= 0 means sample_rate / 2)                           */
+} assl_cfg;
+
+typedef struct assl_plan assl_plan;
+
+/* Parameters of one two-view call that do not vary per clip. */
+typedef struct assl_view_cfg {
+  int32_t n_freq;      /* F : mel bands per clip                                               */
+  int32_t n_time;      /* T : frames per clip                                                  */
+  int32_t canvas_h;    /* int(F * virtual_crop_scale[0])   augmentations.py:42                 */
+  int32_t canvas_w;    /* int(T * virtual_crop_scale[1])                                       */
+  int32_t interp;      /* 0 = bicubic (reference, augmentations.py:27), 1 = bilinear           */
+  int32_t log_mixup;   /* 1 = log-mixup-exp (augmentations.py:8-12), 0 = linear mix (:104)     */
+} assl_view_cfg;
+
+int assl_version(void);
+const char* assl_status_string(int status);
+
+/* -- plan ----------------------------------------------------------------------------------
+ * Replaces MelSpectrogramLibrosa.__init__ (src/utils/utils.py:22-24): builds the Slaney mel
+ * filterbank the way librosa.filters.mel does (fp64 -> fp32), stores it sparse, and uploads the
+ * periodic Hann window and FFT twiddles.  Uses the current CUDA device. */
+int assl_plan_create(assl_plan** out, const assl_cfg* cfg);
+int assl_plan_destroy(assl_plan* plan);
+/* Frames per clip of L samples: 1 + L / hop (librosa.stft, center=True).  <0 on error. */
+int64_t assl_plan_num_frames(const assl_plan* plan, int64_t n_samples);
+/* Tiles of frames the front end splits one clip into (second dim of ``tile_sums``). */
+int64_t assl_plan_num_tiles(const assl_plan* plan, int64_t n_samples);
+/* Copy the dense filterbank [n_mels, 1 + n_fft/2] (fp32) to HOST memory -- for parity tests. */
+int assl_plan_filterbank(const assl_plan* plan, float* host_out);
+
+/* -- log-mel front end ---------------------------------------------------------------------
+ * Replaces MelSpectrogramLibrosa.__call__ (src/utils/utils.py:26-28) + extract_log_mel_spectrogram
+ * (src/utils/utils.py:43-49) for B clips at once:
+ *   reflect-pad n_fft/2, frame n_fft / hop, periodic Hann, rFFT, |X|^2 + 2.22e-16, mel, log(. + 1.19e-7).
+ * wave      [B, ld] fp32, clip b starts at wave + b*ld, L valid samples (L > n_fft/2, ld >= L)
+ * wave_gain optional [B] fp32 per-clip scale applied on load (the reference's F.normalize(p=2),
+ *           src/dataset/upstream_dataset.py:62-63, fused); NULL = 1
+ * lms       ring/array of [n_mels, T] fp32 slots, see "Ring" above
+ * tile_sums optional [B, num_tiles, 2] fp64: per tile (sum x, sum x^2) of the values written,
+ *           input of assl_running_stats; NULL to skip
+ * out_kind  0 = log-mel (extract_log_mel_spectrogram), 1 = mel power (MelSpectrogramLibrosa.__call__
+ *           alone, i.e. without the final log(. + eps))                                        */
+int assl_logmel_f32(const assl_plan* plan, const float* wave, const float* wave_gain, int64_t B,
+                    int64_t L, int64_t ld, float* lms, int64_t slot0, int64_t cap,
+                    double* tile_sums, int32_t out_kind, void* stream);
+
+/* Per-clip sum of squares of the waveform -> gain[b] = 1 / max(||wave_b||_2, 1e-12)
+ * (F.normalize(p=2), src/dataset/upstream_dataset.py:62-63). */
+int assl_wave_l2_gain_f32(const float* wave, int64_t B, int64_t L, int64_t ld, float* gain,
+                          void* stream);
+
+/* -- running pre-normalisation -------------------------------------------------------------
+ * Replaces RunningMean.put / RunningVariance.put / RunningNorm.forward's statistics update
+ * (src/augmentations/augmentations.py:222-228, 249-256, 275-281), including the divisor that
+ * makes the 2nd sample overwrite the 1st, for ``n_clips`` clips in sequence order.
+ * state      [8] fp64, caller-owned, zero-filled = fresh: {n_put, sum_mean, sum_var, mean, std, ...}
+ * sums       [n_clips, n_parts, 2] fp64 (sum x, sum x^2) per clip part (tile_sums, or the
+ *            all-gathered per-clip sums with n_parts = 1)
+ * elems      elements per clip (F*T)
+ * max_update RunningNorm.max_update = epoch_samples * max_update_epochs (augmentations.py:271)
+ * mean_std   ring/array of [2] fp32 (mean, std) slots; written for clips [first, first+count)
+ *            of the sequence, clip first+b -> slot (slot0 + b) % cap                           */
+int assl_running_stats(double* state, const double* sums, int64_t n_clips, int64_t n_parts,
+                       int64_t elems, int64_t max_update, int64_t first, int64_t count,
+                       float* mean_std, int64_t slot0, int64_t cap, void* stream);
+
+/* Per-clip (sum x, sum x^2) of an arbitrary [B, elems] fp32 array -> sums [B, 2] fp64: the
+ * x.mean(axis) / ((x-mu)**2).mean(axis) reductions of RunningMean.put / RunningVariance.put
+ * (augmentations.py:223-226, 250) when the clips did not come from assl_logmel_f32. */
+int assl_clip_moments_f32(const float* x, int64_t B, int64_t elems, double* sums, void* stream);
+/* y[b] = (x[b] - mean_b) / std_b with (mean, std) = mean_std[(slot0 + b) % cap]: the last line of
+ * RunningNorm.forward (augmentations.py:282) on its own. */
+int assl_clip_normalize_f32(const float* x, float* y, int64_t B, int64_t elems, const float* mean_std,
+                            int64_t slot0, int64_t cap, void* stream);
+
+/* Reduce tile_sums [B, n_parts, 2] -> clip_sums [B, 2] (what ranks all-gather). */
+int assl_clip_sums(const double* tile_sums, int64_t B, int64_t n_parts, double* clip_sums,
+                   void* stream);
+
+/* -- two views -----------------------------------------------------------------------------
+ * Replaces, per clip and per view, RunningNorm.forward's (x-mean)/std (augmentations.py:282),
+ * MixupBYOLA.forward's mix (:99-106, log_mixup_exp :8-12) and RandomResizeCrop.forward (:40-55:
+ * zero canvas, centred paste, crop, F.interpolate(bicubic, align_corners=True)) -- i.e. the
+ * body of AugmentationModule.__call__ (src/augmentations/__init__.py:32-35) -- with every random
+ * draw passed in explicitly.
+ * lms, mean_std  rings (cap slots) holding this call's clips AND the bank sources
+ * mean_std may be NULL (no pre-normalisation: x is used as is)
+ * clip_slot [B]      int32 ring slot of each clip's log-mel
+ * mix_slot  [B,2]    int32 ring slot of the bank entry mixed into view v, -1 = no mix
+ * alpha     [B,2]    fp32 weight of the bank entry (the clip gets 1 - alpha)
+ * crop      [B,2,4]  int32 (i, j, h, w) in canvas coordinates, as RandomResizeCrop.get_params
+ *                    (augmentations.py:30-38) returns them
+ * view1/2   [B, F, T] fp32 outputs
+ * The host-side mirror validates crops (1<=h<=canvas_h, i+h<=canvas_h, ...) before calling; the
+ * kernel additionally clamps them into the canvas so a bad box cannot leave its shared memory.  */
+int assl_two_views_f32(const assl_view_cfg* vcfg, const float* lms, const float* mean_std,
+                       int64_t cap, const int32_t* clip_slot, const int32_t* mix_slot,
+                       const float* alpha, const int32_t* crop, int64_t B, float* view1,
+                       float* view2, void* stream);
+
+/* -- batch post-normalisation --------------------------------------------------------------
+ * Replaces NormalizeBatch.forward (src/augmentations/augmentations.py:321-324).
+ * assl_batch_sums accumulates {count, sum x, sum x^2} of x[n] into sums[3] (fp64; the caller zeroes
+ * it, may all-reduce it across ranks); assl_normalize_apply then writes
+ * y = (x - mean) / clamp(std_unbiased, eps, max).  x == y is allowed.                          */
+int assl_batch_sums(const float* x, int64_t n, double* sums, void* stream);
+int assl_normalize_apply_f32(const float* x, float* y, int64_t n, const double* sums, void* stream);
+/* PrecomputedNorm.forward (augmentations.py:299-300): y = (x - mean) / std. */
+int assl_affine_norm_f32(const float* x, float* y, int64_t n, float mean, float std, void* stream);
+
+/* -- whole path, HOST buffers (what a DataLoader-side caller binds) --------------------------
+ * host_wave [B, L] (pinned for async copies) -> H2D -> log-mel -> running stats -> two views -> D2H
+ * into host_view1/2 [B, F, T].  Parameter arrays are HOST pointers with the layouts above
+ * (slots refer to the ring inside ``ws``).  ``ws`` is a caller-owned DEVICE workspace of at least
+ * assl_pipeline_workspace_bytes(); the ring (cap slots) and the norm state live at its start
+ * and persist between calls.  host_view* may be NULL to leave the views on the device (their
+ * device addresses are returned through dev_view1/2 when non-NULL).                            */
+int64_t assl_pipeline_workspace_bytes(const assl_plan* plan, int64_t B, int64_t L, int64_t cap);
+int assl_pipeline_host_f32(const assl_plan* plan, const assl_view_cfg* vcfg, void* ws,
+                           int64_t ws_bytes, const float* host_wave, int64_t B, int64_t L,
+                           int64_t slot0, int64_t cap, int64_t max_update,
+                           const int32_t* host_mix_slot, const float* host_alpha,
+                           const int32_t* host_crop, float* host_view1, float* host_view2,
+                           float** dev_view1, float** dev_view2, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ASSL_H_ */
