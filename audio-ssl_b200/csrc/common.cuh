@@ -42,5 +42,6 @@ struct assl_plan {
   int* d_mel_cnt;               // [n_mels]     bins in the support
   int* d_mel_off;               // [n_mels]     offset into d_mel_w
   float* d_mel_w;               // [nnz]        fp32 weights
+  float* d_mel_const;           // [n_mels]     2.22e-16 * sum of the band's weights (folded "+ eps" of utils.py:28)
   std::vector<float> h_fb;      // dense [n_mels][513] copy for assl_plan_filterbank
 };

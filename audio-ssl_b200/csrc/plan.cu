@@ -106,6 +106,12 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
     off[m] = static_cast<int>(w.size());
     for (int k = 0; k < cnt[m]; ++k) w.push_back(p->h_fb[static_cast<size_t>(m) * n_bins + k0[m] + k]);
   }
+  std::vector<float> mconst(n_mels);
+  for (int m = 0; m < n_mels; ++m) {
+    float acc = 0.f;
+    for (int k = 0; k < cnt[m]; ++k) acc += w[off[m] + k] * assl::kPowerEps;
+    mconst[m] = acc;
+  }
   if (w.empty()) w.push_back(0.f);
   p->nnz = static_cast<int>(w.size());
 
@@ -126,6 +132,7 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
   if (rc == ASSL_OK) rc = upload(&p->d_mel_cnt, cnt);
   if (rc == ASSL_OK) rc = upload(&p->d_mel_off, off);
   if (rc == ASSL_OK) rc = upload(&p->d_mel_w, w);
+  if (rc == ASSL_OK) rc = upload(&p->d_mel_const, mconst);
   if (rc != ASSL_OK) { assl_plan_destroy(p); return rc; }
   *out = p;
   return ASSL_OK;
@@ -139,6 +146,7 @@ extern "C" int assl_plan_destroy(assl_plan* p) {
   cudaFree(p->d_mel_cnt);
   cudaFree(p->d_mel_off);
   cudaFree(p->d_mel_w);
+  cudaFree(p->d_mel_const);
   delete p;
   return ASSL_OK;
 }

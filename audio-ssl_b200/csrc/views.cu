@@ -35,6 +35,12 @@ struct ViewArgs {
   int y0, x0;      // where the clip sits in the canvas (augmentations.py:47)
 };
 
+__device__ __forceinline__ float ex2_approx(float x) {    // MUFU.EX2, flush-to-zero (|rel err| <= 2 ulp)
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ float cubic1(float x) {   // |x| <= 1
   const float A = -0.75f;
   return ((A + 2.f) * x - (A + 3.f)) * x * x + 1.f;
@@ -109,77 +115,108 @@ __global__ void __launch_bounds__(kViewThreads) two_views_kernel(const ViewArgs 
                          min(max(iy + 1, 0), h - 1), min(max(iy + 2, 0), h - 1));
   }
 
-  // ---- stage A: normalise + mix the crop span [0,h) x [xs_lo, xs_lo+nsx) into shared memory
+  // ---- stage A: normalise + mix the crop span [0,h) x [xs_lo, xs_lo+nsx) into shared memory.
+  //      exp(xn) = ex2(x*a + b) with a = log2e/std, b = -mean*log2e/std: one FFMA + one MUFU per operand.
   {
-    const long long plane = static_cast<long long>(F) * T;
+    const int plane = F * T;
     const int xslot = a.clip_slot[b];
-    const float* xp = a.lms + xslot * plane;
+    const float* xp = a.lms + static_cast<long long>(xslot) * plane;
     float mu = 0.f, inv = 1.f;
     if (a.mean_std) { mu = a.mean_std[2 * xslot]; inv = 1.f / a.mean_std[2 * xslot + 1]; }
     const int zslot = a.mix_slot[b * 2 + v];
     const bool mix = zslot >= 0;
-    const float* zp = a.lms + (mix ? zslot : 0) * plane;
+    const float* zp = a.lms + static_cast<long long>(mix ? zslot : 0) * plane;
     float zmu = 0.f, zinv = 1.f;
     if (mix && a.mean_std) { zmu = a.mean_std[2 * zslot]; zinv = 1.f / a.mean_std[2 * zslot + 1]; }
     const float al = a.alpha[b * 2 + v];
     const float wx = 1.f - al, wz = al;
+    const bool logmix = mix && a.c.log_mixup;
+    const float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
+    const float xa = logmix ? inv * kLog2e : inv, xb = -mu * xa;
+    const float za = logmix ? zinv * kLog2e : zinv, zb = -zmu * za;
+    // columns of the span that fall inside the pasted clip: lx = cj + xs_lo + xs - x0 in [0, T)
+    const int lx0 = cj + xs_lo - a.x0;
+    const int xs_in0 = max(0, -lx0), xs_in1 = min(nsx, T - lx0);
     for (int y = warp; y < h; y += kViewThreads / 32) {
       const int ly = ci + y - a.y0;
-      const bool row_in = ly >= 0 && ly < F;
+      float* drow = s_src + y * a.src_w;
+      if (ly < 0 || ly >= F) {                                 // warp-uniform: zero canvas row
+        for (int xs = lane; xs < nsx; xs += 32) drow[xs] = 0.f;
+        continue;
+      }
+      const float* xr = xp + ly * T + lx0;
+      const float* zr = zp + ly * T + lx0;
       for (int xs = lane; xs < nsx; xs += 32) {
-        const int lx = cj + xs_lo + xs - a.x0;
-        float val = 0.f;                                   // zero canvas outside the pasted clip
-        if (row_in && lx >= 0 && lx < T) {
-          const long long o = static_cast<long long>(ly) * T + lx;
-          const float xn = (__ldg(xp + o) - mu) * inv;
-          if (mix) {
-            const float zn = (__ldg(zp + o) - zmu) * zinv;
-            val = a.c.log_mixup ? __logf(wx * __expf(xn) + wz * __expf(zn) + kLogEps) : wz * zn + wx * xn;
+        float val = 0.f;                                       // zero canvas outside the pasted clip
+        if (xs >= xs_in0 && xs < xs_in1) {
+          const float xv = fmaf(__ldg(xr + xs), xa, xb);
+          if (logmix) {
+            const float zv = fmaf(__ldg(zr + xs), za, zb);
+            val = kLn2 * __log2f(fmaf(wx, ex2_approx(xv), fmaf(wz, ex2_approx(zv), kLogEps)));
+          } else if (mix) {
+            val = fmaf(wz, fmaf(__ldg(zr + xs), za, zb), wx * xv);
           } else {
-            val = xn;
+            val = xv;
           }
         }
-        s_src[y * a.src_w + xs] = val;
+        drow[xs] = val;
       }
     }
   }
   __syncthreads();
 
-  const int col = tid % TW, rg = tid / TW;
-  constexpr int kRowGroups = kViewThreads / TW;
-  const bool col_on = col < ncol;
-
-  // ---- stage B: along time.  Each thread owns one output column (taps and weights in registers).
-  if (col_on) {
-    int ix; float tx;
-    source_index(ox0 + col, w, T, &ix, &tx);
-    float wt[4];
-    tap_weights(tx, bil, wt);
-    int xi[4];
+  constexpr int NC = TW / 32;                                  // output columns per lane: lane + 32*c
+  // ---- stage B: along time.  lanes <-> output columns (taps and weights in registers), warps <-> crop rows
+  {
+    int xi[NC][4];
+    float wt[NC][4];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) xi[q] = min(max(min(max(ix - 1 + q, 0), w - 1) - xs_lo, 0), nsx - 1);
-    for (int y = rg; y < h; y += kRowGroups) {
+    for (int c = 0; c < NC; ++c) {
+      const int col = min(lane + 32 * c, ncol - 1);
+      int ix; float tx;
+      source_index(ox0 + col, w, T, &ix, &tx);
+      tap_weights(tx, bil, wt[c]);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) xi[c][q] = min(max(min(max(ix - 1 + q, 0), w - 1) - xs_lo, 0), nsx - 1);
+    }
+    for (int y = warp; y < h; y += kViewThreads / 32) {
       const float* row = s_src + y * a.src_w;
-      float acc = row[xi[0]] * wt[0];
-      acc = fmaf(row[xi[1]], wt[1], acc);
-      acc = fmaf(row[xi[2]], wt[2], acc);
-      acc = fmaf(row[xi[3]], wt[3], acc);
-      s_h[y * TW + col] = acc;
+      float* hrow = s_h + y * TW + lane;
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        if (32 * c < ncol) {                                   // warp-uniform
+          float acc = row[xi[c][0]] * wt[c][0];
+          acc = fmaf(row[xi[c][1]], wt[c][1], acc);
+          acc = fmaf(row[xi[c][2]], wt[c][2], acc);
+          acc = fmaf(row[xi[c][3]], wt[c][3], acc);
+          hrow[32 * c] = acc;
+        }
+      }
     }
   }
   __syncthreads();
 
-  // ---- stage C: along frequency, coalesced store
-  if (col_on) {
-    float* outp = (v == 0 ? a.view1 : a.view2) + b * (static_cast<long long>(F) * T) + ox0 + col;
-    for (int oy = rg; oy < F; oy += kRowGroups) {
+  // ---- stage C: along frequency, coalesced stores.  lanes <-> columns, warps <-> output rows
+  {
+    float* outp = (v == 0 ? a.view1 : a.view2) + b * (static_cast<long long>(F) * T) + ox0 + lane;
+    for (int oy = warp; oy < F; oy += kViewThreads / 32) {
       const float4 wy = s_wy[oy];
       const int4 ya = s_ya[oy];
-      float acc = s_h[ya.x * TW + col] * wy.x;
-      acc = fmaf(s_h[ya.y * TW + col], wy.y, acc);
-      acc = fmaf(s_h[ya.z * TW + col], wy.z, acc);
-      acc = fmaf(s_h[ya.w * TW + col], wy.w, acc);
-      outp[static_cast<long long>(oy) * T] = acc;
+      const float* r0 = s_h + ya.x * TW + lane;
+      const float* r1 = s_h + ya.y * TW + lane;
+      const float* r2 = s_h + ya.z * TW + lane;
+      const float* r3 = s_h + ya.w * TW + lane;
+      float* orow = outp + static_cast<long long>(oy) * T;
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        if (lane + 32 * c < ncol) {
+          float acc = r0[32 * c] * wy.x;
+          acc = fmaf(r1[32 * c], wy.y, acc);
+          acc = fmaf(r2[32 * c], wy.z, acc);
+          acc = fmaf(r3[32 * c], wy.w, acc);
+          orow[32 * c] = acc;
+        }
+      }
     }
   }
 }
