@@ -74,7 +74,7 @@ __host__ __device__ inline size_t views_smem_bytes(int canvas_h, int src_w, int 
 }
 
 template <int TW>
-__global__ void __launch_bounds__(kViewThreads) two_views_kernel(const ViewArgs a) {
+__global__ void __launch_bounds__(kViewThreads, 3) two_views_kernel(const ViewArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int F = a.c.n_freq, T = a.c.n_time;
   float4* s_wy = reinterpret_cast<float4*>(smem_raw);                // [F]         frequency tap weights
@@ -137,29 +137,53 @@ __global__ void __launch_bounds__(kViewThreads) two_views_kernel(const ViewArgs 
     // columns of the span that fall inside the pasted clip: lx = cj + xs_lo + xs - x0 in [0, T)
     const int lx0 = cj + xs_lo - a.x0;
     const int xs_in0 = max(0, -lx0), xs_in1 = min(nsx, T - lx0);
-    for (int y = warp; y < h; y += kViewThreads / 32) {
-      const int ly = ci + y - a.y0;
-      float* drow = s_src + y * a.src_w;
-      if (ly < 0 || ly >= F) {                                 // warp-uniform: zero canvas row
-        for (int xs = lane; xs < nsx; xs += 32) drow[xs] = 0.f;
-        continue;
+    // Rows are taken kRowBatch at a time per warp and ALL their global loads are issued before any
+    // arithmetic, so a warp keeps 2 * kRowBatch * ceil(nsx/32) loads in flight instead of 2.
+    constexpr int kRowBatch = 2;
+    constexpr int kColGroups = (TW * 3 / 2 + 16 + 31) / 32;     // covers span() for virtual_crop_scale <= 1.5
+    for (int yb = warp * kRowBatch; yb < h; yb += (kViewThreads / 32) * kRowBatch) {
+      float xv[kRowBatch][kColGroups], zv[kRowBatch][kColGroups];
+#pragma unroll
+      for (int r = 0; r < kRowBatch; ++r) {
+        const int ly = ci + yb + r - a.y0;
+        const bool row_in = (yb + r < h) && ly >= 0 && ly < F;     // warp-uniform
+        const float* xr = xp + ly * T + lx0;
+        const float* zr = zp + ly * T + lx0;
+#pragma unroll
+        for (int c = 0; c < kColGroups; ++c) {
+          const int xs = lane + 32 * c;
+          const bool in = row_in && xs >= xs_in0 && xs < xs_in1;
+          xv[r][c] = in ? __ldg(xr + xs) : 0.f;
+          zv[r][c] = (in && mix) ? __ldg(zr + xs) : 0.f;
+        }
       }
-      const float* xr = xp + ly * T + lx0;
-      const float* zr = zp + ly * T + lx0;
-      for (int xs = lane; xs < nsx; xs += 32) {
-        float val = 0.f;                                       // zero canvas outside the pasted clip
-        if (xs >= xs_in0 && xs < xs_in1) {
-          const float xv = fmaf(__ldg(xr + xs), xa, xb);
-          if (logmix) {
-            const float zv = fmaf(__ldg(zr + xs), za, zb);
-            val = kLn2 * __log2f(fmaf(wx, ex2_approx(xv), fmaf(wz, ex2_approx(zv), kLogEps)));
-          } else if (mix) {
-            val = fmaf(wz, fmaf(__ldg(zr + xs), za, zb), wx * xv);
-          } else {
-            val = xv;
+#pragma unroll
+      for (int r = 0; r < kRowBatch; ++r) {
+        const int y = yb + r;
+        const int ly = ci + y - a.y0;
+        const bool row_in = ly >= 0 && ly < F;
+        float* drow = s_src + y * a.src_w;
+        if (y < h) {
+#pragma unroll
+          for (int c = 0; c < kColGroups; ++c) {
+            const int xs = lane + 32 * c;
+            if (xs < nsx) {
+              float val = 0.f;                                   // zero canvas outside the pasted clip
+              if (row_in && xs >= xs_in0 && xs < xs_in1) {
+                const float xn = fmaf(xv[r][c], xa, xb);
+                if (logmix) {
+                  const float zn = fmaf(zv[r][c], za, zb);
+                  val = kLn2 * __log2f(fmaf(wx, ex2_approx(xn), fmaf(wz, ex2_approx(zn), kLogEps)));
+                } else if (mix) {
+                  val = fmaf(wz, fmaf(zv[r][c], za, zb), wx * xn);
+                } else {
+                  val = xn;
+                }
+              }
+              drow[xs] = val;
+            }
           }
         }
-        drow[xs] = val;
       }
     }
   }
@@ -224,6 +248,8 @@ __global__ void __launch_bounds__(kViewThreads) two_views_kernel(const ViewArgs 
 template <int TW>
 int launch_views(ViewArgs& a, cudaStream_t st) {
   a.tiles_t = (a.c.n_time + TW - 1) / TW;
+  constexpr int kColGroups = (TW * 3 / 2 + 16 + 31) / 32;       // must match stage A of the kernel
+  if (a.src_w - 1 > 32 * kColGroups) return ASSL_ERR_UNSUPPORTED;   // virtual_crop_scale[1] well above 1.5
   const size_t smem = views_smem_bytes(a.c.canvas_h, a.src_w, TW, a.c.n_freq);
   if (smem > 227 * 1024) return ASSL_ERR_UNSUPPORTED;
   if (cudaFuncSetAttribute(two_views_kernel<TW>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
