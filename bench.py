@@ -52,7 +52,8 @@ def measured_peak_gbs():
 # CPU arm: the oracle port (numpy librosa restatement + restated augmentations), one clip at a time
 # per worker process -- the reference's own execution model (DataLoader workers, upstream_dataset.py:118-125).
 def _cpu_worker(args):
-    seed, n_clips, n_samples = args
+    """One DataLoader-style worker: its own augmentation state, one clip at a time, for ``budget_s`` seconds."""
+    seed, budget_s, n_samples = args
     os.environ["OMP_NUM_THREADS"] = os.environ["OPENBLAS_NUM_THREADS"] = os.environ["MKL_NUM_THREADS"] = "1"
     import random
 
@@ -61,15 +62,16 @@ def _cpu_worker(args):
     from oracle import frontend as ofe
     from oracle import views as ov
     rng = np.random.default_rng(seed)
-    waves = (rng.standard_normal((n_clips, n_samples)) * 0.1).astype(np.float32)
+    waves = (rng.standard_normal((32, n_samples)) * 0.1).astype(np.float32)
     np.random.seed(seed); random.seed(seed)
     mfb = ofe.mel_filterbank()
-    tf = ov.TwoViewOracle(1000)
-    t0 = time.perf_counter()
-    for w in waves:
-        lm = torch.from_numpy(ofe.log_mel(w, mfb=mfb))
-        tf(lm.unsqueeze(0))
-    return time.perf_counter() - t0
+    tf = ov.TwoViewOracle(10 ** 6)
+    done, t0 = 0, time.perf_counter()
+    while time.perf_counter() - t0 < budget_s:
+        for w in waves[:8]:
+            tf(torch.from_numpy(ofe.log_mel(waves[done % 32], mfb=mfb)).unsqueeze(0))
+            done += 1
+    return done
 
 
 class CpuArm:
@@ -80,13 +82,14 @@ class CpuArm:
         os.environ.setdefault("OMP_NUM_THREADS", "1")
         os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
         self.pool = mp.get_context("spawn").Pool(self.cores)
-        self.pool.map(_cpu_worker, [(0, 1, n_samples)] * self.cores)      # import + warm every worker
+        self.pool.map(_cpu_worker, [(0, 0.05, n_samples)] * self.cores)      # import + warm every worker
 
-    def run(self, clips_per_worker, seed=1):
+    def run(self, budget_s, seed=1):
+        """All workers run for ``budget_s`` seconds; returns (clips/s, clips, wall seconds)."""
         t0 = time.perf_counter()
-        self.pool.map(_cpu_worker, [(seed * 1000 + i, clips_per_worker, self.n_samples) for i in range(self.cores)])
+        done = self.pool.map(_cpu_worker, [(seed * 1000 + i, budget_s, self.n_samples) for i in range(self.cores)])
         dt = time.perf_counter() - t0
-        return self.cores * clips_per_worker / dt, dt
+        return sum(done) / dt, sum(done), dt
 
     def close(self):
         self.pool.close(); self.pool.join()
@@ -94,29 +97,27 @@ class CpuArm:
 
 def run_reference_arm(args):
     """--impl reference: the reference's CPU implementation of the path (oracle port: librosa is not
-    installable here) on all host cores; each step is a bounded sample of the workload."""
+    installable here) on all host cores; each step is a time-bounded sample of the workload."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     n_samples = int(args.seconds * 16000)
     arm = CpuArm(n_samples)
-    per_worker = max(2, args.cpu_clips // arm.cores)
+    step_s = min(args.cpu_seconds, 120.0 / max(1, args.steps + args.warmup))      # whole run stays within minutes
     for _ in range(args.warmup):
-        arm.run(max(1, per_worker // 4))
-    t0 = time.perf_counter()
-    clips = 0
+        arm.run(min(step_s, 1.0))
+    clips, wall = 0, 0.0
     for s in range(args.steps):
-        arm.run(per_worker, seed=s + 1)
-        clips += per_worker * arm.cores
-    dt = time.perf_counter() - t0
+        _, c, dt = arm.run(step_s, seed=s + 1)
+        clips += c; wall += dt
     arm.close()
-    val = clips / dt
-    sample = f"{per_worker * arm.cores} clips/step x {args.steps} steps of {args.seconds:g} s 16 kHz noise"
+    val = clips / wall
+    sample = f"{clips} clips in {args.steps} steps of {step_s:.1f} s, {args.seconds:g} s 16 kHz noise clips"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32 (fp64 FFT)", "data": "synthetic",
-        "config": workload_config(args, per_gpu_batch=per_worker * arm.cores),
+        "config": workload_config(args, per_gpu_batch=args.batch),
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": arm.cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
@@ -323,11 +324,10 @@ def run_ours(args):
     }
     if world == 1 and not args.no_cpu:
         arm = CpuArm(L)
-        per_worker = max(2, args.cpu_clips // arm.cores)
-        val, dt = arm.run(per_worker)
+        val, n_done, dt = arm.run(args.cpu_seconds)
         arm.close()
         out["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": arm.cores, "kind": "port",
-                               "sample": f"{per_worker * arm.cores} clips of {args.seconds:g} s noise in {dt:.1f} s, "
+                               "sample": f"{n_done} clips of {args.seconds:g} s noise in {dt:.1f} s, "
                                          f"one single-threaded process per core (oracle port: numpy librosa restatement + "
                                          f"restated reference augmentations)"}
     print(json.dumps(out))
@@ -344,7 +344,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1024, help="clips per GPU per step")
     ap.add_argument("--seconds", type=float, default=1.0, help="clip length")
     ap.add_argument("--rotate", type=int, default=4, help="distinct input batches cycled through (L2 hygiene)")
-    ap.add_argument("--cpu-clips", type=int, default=2048, help="clips in one CPU-baseline sample")
+    ap.add_argument("--cpu-seconds", type=float, default=10.0, help="wall seconds of one CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
