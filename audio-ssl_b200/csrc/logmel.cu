@@ -24,7 +24,6 @@ namespace assl {
 
 constexpr int kWarps = 8;
 constexpr int kThreads = kWarps * 32;
-constexpr int kFramesPerTile = 2 * kWarps;
 constexpr int kExStride = 33;                       // float2 units: lane-major rows padded by one
 constexpr int kExWarp = 32 * kExStride + 2;         // 1058 float2 = 2116 words == 4 (mod 32)
 
@@ -33,8 +32,11 @@ struct LogmelArgs {
   const float* gain;
   float* lms;
   double* tile_sums;
-  long long B, L, ld, slot0, cap;
-  int T, hop, n_mels, tiles_per_clip, tile_samples, nnz, out_kind, bulk_ok;
+  long long L, ld, slot0, cap;
+  int B, T, hop, n_mels, nnz, out_kind, bulk_ok;
+  int ppc;            // frame pairs per clip = ceil(T / 2)
+  int straddle;       // 1: a tile is 8 consecutive pairs of the flattened (clip, pair) list and may span two clips
+  int total_tiles, n_parts, wave_floats;
   const float* win;
   const float2* tw;
   const int* mk0;
@@ -44,15 +46,15 @@ struct LogmelArgs {
   const float* mconst;   // [n_mels] 2.22e-16 * sum of the band's weights (the "+ eps" of utils.py:28, folded)
 };
 
-__host__ __device__ inline size_t logmel_smem_bytes(int tile_samples, int nnz) {
+__host__ __device__ inline size_t logmel_smem_bytes(int wave_floats, int nnz) {
   size_t b = 0;
   b += sizeof(float2) * kWarps * kExWarp;   // exchange / power buffers
   b += sizeof(float2) * 1024;               // twiddles
   b += sizeof(float) * 1024;                // window
-  b += sizeof(float) * ((tile_samples + 3) & ~3);
+  b += sizeof(float) * ((wave_floats + 3) & ~3);
   b += sizeof(float) * ((nnz + 3) & ~3);
   b += sizeof(int) * 3 * kMaxMels + sizeof(float) * kMaxMels;
-  b += sizeof(double) * 2 * 2 * kWarps;     // per-warp (sum, sum^2), double-buffered by tile parity
+  b += sizeof(float2) * 2 * kWarps * kWarps;   // per (warp, frame pair) (sum, sum^2), double-buffered by tile parity
   b += 2 * sizeof(unsigned long long);      // mbarriers
   return b;
 }
@@ -82,11 +84,42 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-// in-range part of a tile that the bulk copy covers, tile-relative [lo, hi), both multiples of 4
-__device__ __forceinline__ void bulk_range(long long base, long long L, int tile_samples, int* lo, int* hi) {
-  const long long l = base < 0 ? -base : 0;
-  long long h = L - base;
-  h = h > tile_samples ? tile_samples : h;
+// A tile = up to 8 frame pairs; its pairs belong to one clip, or (straddle mode) to two consecutive clips.
+struct Segment {
+  int clip;      // clip index in the batch
+  int q0;        // first pair of the clip in this tile
+  int n;         // pairs of this clip in the tile (0 = segment absent)
+  int off;       // where the segment's waveform span starts in s_wave (floats, multiple of 4)
+  int span;      // samples the segment's frames touch: (2n - 1) * hop + 1024
+  long long base;   // clip-relative sample index of the span start: 2*q0*hop - 512 (may be negative)
+};
+
+__device__ __forceinline__ void tile_segments(const LogmelArgs& a, int tile, Segment seg[2]) {
+  int p0, np;
+  if (a.straddle) {
+    p0 = tile * kWarps;
+    const int total = a.B * a.ppc;
+    np = total - p0 < kWarps ? total - p0 : kWarps;
+  } else {                                 // clips shorter than 8 pairs: one clip per tile
+    p0 = tile * a.ppc;
+    np = a.ppc;
+  }
+  const int b0 = p0 / a.ppc;
+  const int q0 = p0 - b0 * a.ppc;
+  const int n0 = np < a.ppc - q0 ? np : a.ppc - q0;
+  seg[0].clip = b0; seg[0].q0 = q0; seg[0].n = n0; seg[0].off = 0;
+  seg[0].span = (2 * n0 - 1) * a.hop + kNfft;
+  seg[0].base = 2ll * q0 * a.hop - kNfft / 2;
+  seg[1].clip = b0 + 1; seg[1].q0 = 0; seg[1].n = np - n0; seg[1].off = (seg[0].span + 3) & ~3;
+  seg[1].span = (2 * seg[1].n - 1) * a.hop + kNfft;
+  seg[1].base = -kNfft / 2;
+}
+
+// part of a segment's span the bulk copy covers (in range of the clip), span-relative [lo, hi), multiples of 4
+__device__ __forceinline__ void bulk_range(const Segment& g, long long L, int* lo, int* hi) {
+  const long long l = g.base < 0 ? -g.base : 0;
+  long long h = L - g.base;
+  h = h > g.span ? g.span : h;
   h &= ~3ll;
   *lo = static_cast<int>(l);
   *hi = static_cast<int>(h > l ? h : l);
@@ -100,18 +133,17 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
   float2* s_tw = s_ex + kWarps * kExWarp;
   float* s_win = reinterpret_cast<float*>(s_tw + 1024);
   float* s_wave = s_win + 1024;
-  float* s_mw = s_wave + ((a.tile_samples + 3) & ~3);
+  float* s_mw = s_wave + ((a.wave_floats + 3) & ~3);
   int* s_mk0 = reinterpret_cast<int*>(s_mw + ((a.nnz + 3) & ~3));
   int* s_mcnt = s_mk0 + kMaxMels;
   int* s_moff = s_mcnt + kMaxMels;
   float* s_mconst = reinterpret_cast<float*>(s_moff + kMaxMels);
-  double* s_red = reinterpret_cast<double*>(s_mconst + kMaxMels);          // [2][kWarps][2]
-  unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_red + 4 * kWarps);
-  void* bar_wave = s_bar;        // tile's waveform span has landed (tx bytes)
+  float2* s_red = reinterpret_cast<float2*>(s_mconst + kMaxMels);          // [2][kWarps][kWarps]
+  unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_red + 2 * kWarps * kWarps);
+  void* bar_wave = s_bar;        // tile's waveform spans have landed (tx bytes)
   void* bar_mel = s_bar + 1;     // every thread is done reading the previous tile's power spectra
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const long long total_tiles = a.B * a.tiles_per_clip;
 
   if (tid == 0) { mbar_init(bar_wave, 1); mbar_init(bar_mel, kThreads); }
   for (int i = tid; i < 1024; i += kThreads) { s_tw[i] = a.tw[i]; s_win[i] = a.win[i]; }
@@ -122,56 +154,100 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();
 
-  // producer: bulk-copy the in-range span of a tile into s_wave (one elected thread)
-  auto issue_tile = [&](long long tile) {
-    const long long b = tile / a.tiles_per_clip;
-    const int t0 = static_cast<int>(tile - b * a.tiles_per_clip) * kFramesPerTile;
-    const long long base = static_cast<long long>(t0) * a.hop - kNfft / 2;
-    int lo, hi;
-    bulk_range(base, a.L, a.tile_samples, &lo, &hi);
-    const unsigned bytes = static_cast<unsigned>(hi - lo) * 4u;
-    mbar_expect_tx(bar_wave, bytes);
-    if (bytes) bulk_g2s(s_wave + lo, a.wave + b * a.ld + base + lo, bytes, bar_wave);
+  // producer: bulk-copy the in-range spans of a tile into s_wave (one elected thread)
+  auto issue_tile = [&](int tile) {
+    Segment seg[2];
+    tile_segments(a, tile, seg);
+    unsigned bytes[2] = {0u, 0u};
+    int lo[2] = {0, 0};
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      if (seg[s].n > 0) {
+        int hi;
+        bulk_range(seg[s], a.L, &lo[s], &hi);
+        bytes[s] = static_cast<unsigned>(hi - lo[s]) * 4u;
+      }
+    }
+    mbar_expect_tx(bar_wave, bytes[0] + bytes[1]);
+#pragma unroll
+    for (int s = 0; s < 2; ++s)
+      if (bytes[s]) bulk_g2s(s_wave + seg[s].off + lo[s], a.wave + seg[s].clip * a.ld + seg[s].base + lo[s], bytes[s], bar_wave);
   };
-  if (a.bulk_ok && tid == 0 && blockIdx.x < total_tiles) issue_tile(blockIdx.x);
+  if (a.bulk_ok && tid == 0 && static_cast<int>(blockIdx.x) < a.total_tiles) issue_tile(blockIdx.x);
+
+  // flush the statistics a tile left in s_red: one (sum, sum^2) pair per clip segment, fixed summation
+  // order.  Called by warp 0: lane f adds up frame pair f over the 8 producing warps, then a masked
+  // butterfly combines the pairs of each segment.
+  auto flush_stats = [&](int tile, unsigned parity) {
+    Segment seg[2];
+    tile_segments(a, tile, seg);
+    const float2* r = s_red + parity * kWarps * kWarps;
+    double r1 = 0.0, r2 = 0.0;
+    if (lane < kWarps) {
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) { const float2 v = r[w * kWarps + lane]; r1 += v.x; r2 += v.y; }
+    }
+    const int n0 = seg[0].n, np = n0 + seg[1].n;
+    double a1 = lane < n0 ? r1 : 0.0, a2 = lane < n0 ? r2 : 0.0;            // segment 0
+    double b1 = (lane >= n0 && lane < np) ? r1 : 0.0, b2 = (lane >= n0 && lane < np) ? r2 : 0.0;   // segment 1
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+      a1 += __shfl_xor_sync(0xffffffffu, a1, o); a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+      b1 += __shfl_xor_sync(0xffffffffu, b1, o); b2 += __shfl_xor_sync(0xffffffffu, b2, o);
+    }
+    if (lane < 2 && (lane == 0 ? n0 : seg[1].n) > 0) {
+      const int clip = seg[0].clip + lane;
+      const int first_tile = a.straddle ? (clip * a.ppc) / kWarps : tile;
+      double* dst = a.tile_sums + (static_cast<long long>(clip) * a.n_parts + (tile - first_tile)) * 2;
+      dst[0] = lane == 0 ? a1 : b1;
+      dst[1] = lane == 0 ? a2 : b2;
+    }
+  };
 
   unsigned it = 0;
-  long long prev_tile = -1;
-  for (long long tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-    const long long b = tile / a.tiles_per_clip;
-    const int tile_in_clip = static_cast<int>(tile - b * a.tiles_per_clip);
-    const int t0 = tile_in_clip * kFramesPerTile;
-    const long long base = static_cast<long long>(t0) * a.hop - kNfft / 2;
-    const float* src = a.wave + b * a.ld;
+  int prev_tile = -1;
+  for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+    Segment seg[2];
+    tile_segments(a, tile, seg);
+    const int n0 = seg[0].n, np = n0 + seg[1].n;
 
-    // ---- waveform span: wait for the bulk copy, patch what it could not cover (reflect padding of
+    // ---- waveform spans: wait for the bulk copies, patch what they could not cover (reflect padding of
     //      np.pad(mode='reflect'): p<0 -> -p, p>L-1 -> 2(L-1)-p; tail remainder when L % 4 != 0)
-    int lo = 0, hi = 0;
-    if (a.bulk_ok) {
-      bulk_range(base, a.L, a.tile_samples, &lo, &hi);
-      mbar_wait(bar_wave, it & 1);
-    } else {
-      __syncthreads();                              // previous tile's input reads are done
-    }
-    if (lo > 0 || hi < a.tile_samples) {            // CTA-uniform
-      const int last = static_cast<int>(a.L - 1);
-      const int n_fix = lo + (a.tile_samples - hi);
-      for (int q = tid; q < n_fix; q += kThreads) {
-        const int i = q < lo ? q : hi + (q - lo);
-        long long p = base + i;
-        if (p < 0) p = -p;
-        if (p > last) p = 2ll * last - p;
-        p = p < 0 ? 0 : (p > last ? last : p);      // only frames >= T can land here; never read back
-        s_wave[i] = __ldg(src + p);
+    if (a.bulk_ok) mbar_wait(bar_wave, it & 1);
+    else __syncthreads();                            // previous tile's input reads are done
+    bool fixed = false;
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      if (seg[s].n > 0) {
+        int lo = 0, hi = 0;
+        if (a.bulk_ok) bulk_range(seg[s], a.L, &lo, &hi);
+        if (lo > 0 || hi < seg[s].span) {             // CTA-uniform
+          const int last = static_cast<int>(a.L - 1);
+          const int n_fix = lo + (seg[s].span - hi);
+          const float* src = a.wave + seg[s].clip * a.ld;
+          float* dst = s_wave + seg[s].off;
+          for (int q = tid; q < n_fix; q += kThreads) {
+            const int i = q < lo ? q : hi + (q - lo);
+            long long p = seg[s].base + i;
+            if (p < 0) p = -p;
+            if (p > last) p = 2ll * last - p;
+            p = p < 0 ? 0 : (p > last ? last : p);    // only frames >= T can land here; never read back
+            dst[i] = __ldg(src + p);
+          }
+          fixed = true;
+        }
       }
-      __syncthreads();
     }
+    if (fixed) __syncthreads();
 
+    // this warp's pair: which clip, which frames, where its samples start
+    const bool have = warp < np;                      // warp-uniform
+    const int wseg = warp >= n0 ? 1 : 0;
+    const int wpair = wseg ? warp - n0 : seg[0].q0 + warp;        // pair index inside its clip
     float2* ex = s_ex + warp * kExWarp;
-    const bool have = t0 + 2 * warp < a.T;          // warp-uniform
     float re[32], im[32];
     if (have) {
-      const float* w0 = s_wave + (2 * warp) * a.hop + lane;
+      const float* w0 = s_wave + (wseg ? seg[1].off + wpair * 2 * a.hop : warp * 2 * a.hop) + lane;
       if (H32 > 0) {
         float s[32 + H32];
 #pragma unroll
@@ -196,7 +272,7 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
     if (a.bulk_ok) {
       if (warp == 0) {
         asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory");
-        if (lane == 0 && tile + gridDim.x < total_tiles) issue_tile(tile + gridDim.x);
+        if (lane == 0 && tile + static_cast<int>(gridDim.x) < a.total_tiles) issue_tile(tile + gridDim.x);
       } else {
         asm volatile("bar.arrive 1, %0;" ::"n"(kThreads) : "memory");
       }
@@ -244,71 +320,56 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
     __syncthreads();                               // power spectra of the whole tile are in shared memory
 
     // flush the previous tile's statistics (all warps wrote them before reaching the barrier above)
-    if (a.tile_sums && tid == 0 && prev_tile >= 0) {
-      const double* r = s_red + ((it - 1) & 1) * 2 * kWarps;
-      double r1 = 0.0, r2 = 0.0;
-      for (int w = 0; w < kWarps; ++w) { r1 += r[2 * w]; r2 += r[2 * w + 1]; }
-      a.tile_sums[2 * prev_tile] = r1;
-      a.tile_sums[2 * prev_tile + 1] = r2;
-    }
+    if (a.tile_sums && warp == 0 && prev_tile >= 0) flush_stats(prev_tile, (it - 1) & 1);
 
     // ---- sparse filterbank + log: thread = (band, frame pair); 32 bands per pass
-    const int fp = tid & 7;
+    const int fp = tid & 7;                         // frame pair = the warp that produced it
+    const int fseg = fp >= n0 ? 1 : 0;
+    const int ta = 2 * (fseg ? fp - n0 : seg[0].q0 + fp);
+    const int fclip = seg[0].clip + fseg;
+    const bool fhave = fp < np && ta < a.T;
+    const bool fhave2 = fhave && ta + 1 < a.T;
     const float2* pw = s_ex + fp * kExWarp;
-    const int ta = t0 + 2 * fp;
-    float* out = a.lms + ring_slot(a.slot0, b, a.cap) * (static_cast<long long>(a.n_mels) * a.T);
+    float* out = a.lms + ring_slot(a.slot0, fclip, a.cap) * (static_cast<long long>(a.n_mels) * a.T) + ta;
     float g2 = 1.f;
-    if (a.gain) { const float g = a.gain[b]; g2 = g * g; }   // |g x|^2 = g^2 |x|^2: the per-clip gain is applied here
-    double s1 = 0.0, s2 = 0.0;
+    if (a.gain && fhave) { const float g = a.gain[fclip]; g2 = g * g; }   // |g x|^2 = g^2 |x|^2: per-clip gain applied here
+    float s1 = 0.f, s2 = 0.f;
     for (int mb = 0, pass = 0; mb < a.n_mels; mb += 32, ++pass) {
       // odd passes walk their 32 bands backwards so wide and narrow bands share a warp's time
       const int m = (pass & 1) ? mb + 31 - (tid >> 3) : mb + (tid >> 3);
-      if (m < a.n_mels && ta < a.T) {
-        const int k0 = s_mk0[m], cnt = s_mcnt[m];
+      if (m < a.n_mels && fhave) {
+        const int cnt = s_mcnt[m];
         const float* wgt = s_mw + s_moff[m];
+        const float2* pk = pw + s_mk0[m];
         float acc0 = 0.f, acc1 = 0.f;
 #pragma unroll 4
         for (int j = 0; j < cnt; ++j) {
           const float w = wgt[j];
-          const float2 p = pw[k0 + j];
+          const float2 p = pk[j];
           acc0 = fmaf(w, p.x, acc0);
           acc1 = fmaf(w, p.y, acc1);
         }
         const float c = s_mconst[m];
         acc0 = fmaf(acc0, g2, c);
         acc1 = fmaf(acc1, g2, c);
-        const float l0 = a.out_kind ? acc0 : logf(acc0 + kLogEps);
-        out[static_cast<long long>(m) * a.T + ta] = l0;
-        s1 += l0; s2 += static_cast<double>(l0) * l0;
-        if (ta + 1 < a.T) {
-          const float l1 = a.out_kind ? acc1 : logf(acc1 + kLogEps);
-          out[static_cast<long long>(m) * a.T + ta + 1] = l1;
-          s1 += l1; s2 += static_cast<double>(l1) * l1;
-        }
+        const float l0 = a.out_kind ? acc0 : __logf(acc0 + kLogEps);
+        const float l1 = a.out_kind ? acc1 : __logf(acc1 + kLogEps);
+        float* o = out + m * a.T;
+        o[0] = l0;
+        s1 += l0; s2 = fmaf(l0, l0, s2);
+        if (fhave2) { o[1] = l1; s1 += l1; s2 = fmaf(l1, l1, s2); }
       }
     }
     mbar_arrive(bar_mel);                          // this thread no longer reads the power buffers
-    if (a.tile_sums) {                             // deterministic per-tile (sum, sum of squares)
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        s1 += __shfl_down_sync(0xffffffffu, s1, o);
-        s2 += __shfl_down_sync(0xffffffffu, s2, o);
-      }
-      if (lane == 0) {
-        double* r = s_red + (it & 1) * 2 * kWarps;
-        r[2 * warp] = s1; r[2 * warp + 1] = s2;
-      }
+    if (a.tile_sums) {                             // per (warp, frame pair) partial sums; lanes with equal fp combine
+      s1 += __shfl_xor_sync(0xffffffffu, s1, 8);  s2 += __shfl_xor_sync(0xffffffffu, s2, 8);
+      s1 += __shfl_xor_sync(0xffffffffu, s1, 16); s2 += __shfl_xor_sync(0xffffffffu, s2, 16);
+      if (lane < kWarps) s_red[((it & 1) * kWarps + warp) * kWarps + lane] = make_float2(s1, s2);
     }
     prev_tile = tile;
   }
   __syncthreads();
-  if (a.tile_sums && tid == 0 && prev_tile >= 0) {
-    const double* r = s_red + ((it - 1) & 1) * 2 * kWarps;
-    double r1 = 0.0, r2 = 0.0;
-    for (int w = 0; w < kWarps; ++w) { r1 += r[2 * w]; r2 += r[2 * w + 1]; }
-    a.tile_sums[2 * prev_tile] = r1;
-    a.tile_sums[2 * prev_tile + 1] = r2;
-  }
+  if (a.tile_sums && warp == 0 && prev_tile >= 0) flush_stats(prev_tile, (it - 1) & 1);
 }
 
 // gain[b] = 1 / max(||wave_b||_2, 1e-12): F.normalize(p=2), upstream_dataset.py:62-63
@@ -338,9 +399,21 @@ int launch_logmel(const LogmelArgs& a, size_t smem, unsigned grid, cudaStream_t 
 
 }  // namespace assl
 
+namespace {
+// frame pairs per clip, and how many tiles (parts of tile_sums) can touch one clip
+inline void tiling(int64_t T, int* ppc, int* straddle, int* n_parts) {
+  *ppc = static_cast<int>((T + 1) / 2);
+  *straddle = *ppc >= assl::kWarps ? 1 : 0;
+  *n_parts = *straddle ? (*ppc - 1) / assl::kWarps + 2 : 1;
+}
+}  // namespace
+
 extern "C" int64_t assl_plan_num_tiles(const assl_plan* p, int64_t n_samples) {
   const int64_t t = assl_plan_num_frames(p, n_samples);
-  return t < 0 ? -1 : (t + assl::kFramesPerTile - 1) / assl::kFramesPerTile;
+  if (t < 0) return -1;
+  int ppc, straddle, n_parts;
+  tiling(t, &ppc, &straddle, &n_parts);
+  return n_parts;
 }
 
 extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const float* wave_gain, int64_t B,
@@ -353,22 +426,27 @@ extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const floa
   if (cap > 0 && (B > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
   if (B == 0) return ASSL_OK;
   const int64_t T = 1 + L / p->cfg.hop;
-  if (T > (1ll << 30)) return ASSL_ERR_UNSUPPORTED;
   LogmelArgs a;
+  tiling(T, &a.ppc, &a.straddle, &a.n_parts);
+  const int64_t total_pairs = B * a.ppc;
+  if (T > (1ll << 24) || total_pairs > (1ll << 30) || L > (1ll << 31) - 4096) return ASSL_ERR_UNSUPPORTED;
   a.wave = wave; a.gain = wave_gain; a.lms = lms; a.tile_sums = tile_sums;
-  a.B = B; a.L = L; a.ld = ld; a.slot0 = slot0; a.cap = cap;
+  a.B = static_cast<int>(B); a.L = L; a.ld = ld; a.slot0 = slot0; a.cap = cap;
   a.T = static_cast<int>(T); a.hop = p->cfg.hop; a.n_mels = p->cfg.n_mels;
-  a.tiles_per_clip = static_cast<int>((T + kFramesPerTile - 1) / kFramesPerTile);
-  a.tile_samples = (kFramesPerTile - 1) * p->cfg.hop + kNfft;
+  a.total_tiles = a.straddle ? static_cast<int>((total_pairs + kWarps - 1) / kWarps) : static_cast<int>(B);
+  // two spans per tile at most: (16 - 2) hops + 2 windows, each span start rounded to 4 floats
+  a.wave_floats = 2 * kWarps * p->cfg.hop + 2 * kNfft + 8;
   a.nnz = p->nnz; a.out_kind = out_kind;
-  // the bulk (TMA) copy needs 16-byte aligned global addresses: clip starts and tile starts (t0*hop - 512, t0 % 16 == 0)
-  a.bulk_ok = (reinterpret_cast<uintptr_t>(wave) % 16 == 0) && (ld % 4 == 0);
+  // the bulk (TMA) copy needs 16-byte aligned global addresses: clip starts and span starts (2*q*hop - 512)
+  a.bulk_ok = (reinterpret_cast<uintptr_t>(wave) % 16 == 0) && (ld % 4 == 0) && (p->cfg.hop % 2 == 0);
   a.win = p->d_win_half; a.tw = p->d_twiddle;
   a.mk0 = p->d_mel_k0; a.mcnt = p->d_mel_cnt; a.moff = p->d_mel_off; a.mw = p->d_mel_w; a.mconst = p->d_mel_const;
-  const size_t smem = logmel_smem_bytes(a.tile_samples, a.nnz);
+  const size_t smem = logmel_smem_bytes(a.wave_floats, a.nnz);
   if (smem > 227 * 1024) return ASSL_ERR_UNSUPPORTED;
-  const long long total = B * a.tiles_per_clip;
-  const unsigned grid = static_cast<unsigned>(total < 2ll * p->sm_count ? total : 2ll * p->sm_count);
+  // parts of tile_sums no tile writes (a clip touches at most n_parts tiles, usually fewer) must read as zero
+  if (tile_sums && cudaMemsetAsync(tile_sums, 0, sizeof(double) * 2 * B * a.n_parts, as_stream(stream)) != cudaSuccess)
+    return ASSL_ERR_CUDA;
+  const unsigned grid = static_cast<unsigned>(a.total_tiles < 2 * p->sm_count ? a.total_tiles : 2 * p->sm_count);
   if (a.hop == 160) return launch_logmel<5>(a, smem, grid, as_stream(stream));
   return launch_logmel<0>(a, smem, grid, as_stream(stream));
 }

@@ -72,7 +72,7 @@ int assl_plan_create(assl_plan** out, const assl_cfg* cfg);
 int assl_plan_destroy(assl_plan* plan);
 /* Frames per clip of L samples: 1 + L / hop (librosa.stft, center=True).  <0 on error. */
 int64_t assl_plan_num_frames(const assl_plan* plan, int64_t n_samples);
-/* Tiles of frames the front end splits one clip into (second dim of ``tile_sums``). */
+/* Parts per clip of ``tile_sums`` (tiles of 8 frame pairs that can touch one clip; second dim). */
 int64_t assl_plan_num_tiles(const assl_plan* plan, int64_t n_samples);
 /* Copy the dense filterbank [n_mels, 1 + n_fft/2] (fp32) to HOST memory -- for parity tests. */
 int assl_plan_filterbank(const assl_plan* plan, float* host_out);
