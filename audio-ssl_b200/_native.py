@@ -73,6 +73,7 @@ SIGNATURES = {
     "assl_normalize_apply_f32": (C.c_int, [_P, _P, _I64, _P, _P]),
     "assl_affine_norm_f32": (C.c_int, [_P, _P, _I64, _F, _F, _P]),
     "assl_pipeline_workspace_bytes": (_I64, [_P, _I64, _I64, _I64]),
+    "assl_pipeline_host_sync": (C.c_int, [_P]),
     "assl_pipeline_host_f32": (C.c_int, [_P, C.POINTER(ViewCfg), _P, _I64, _P, _I64, _I64, _I64, _I64, _I64,
                                           _P, _P, _P, _P, _P, C.POINTER(_P), C.POINTER(_P), _P]),
 }

@@ -44,4 +44,13 @@ struct assl_plan {
   float* d_mel_w;               // [nnz]        fp32 weights
   float* d_mel_const;           // [n_mels]     2.22e-16 * sum of the band's weights (folded "+ eps" of utils.py:28)
   std::vector<float> h_fb;      // dense [n_mels][513] copy for assl_plan_filterbank
+  // Copy streams + events of assl_pipeline_host_f32 (created on first use; that entry point is
+  // single-caller per plan, everything else on a plan is read-only and thread-safe).
+  static constexpr int kMaxChunks = 8;
+  mutable bool aux_ready = false;
+  mutable cudaStream_t s_in = nullptr, s_out = nullptr;
+  mutable cudaEvent_t ev_fork = nullptr;
+  mutable cudaEvent_t ev_in[kMaxChunks] = {}, ev_out[kMaxChunks] = {};
+  mutable cudaEvent_t ev_kern[2] = {}, ev_d2h[2] = {};   // per buffer parity: kernels / downloads of that call done
+  mutable long long calls = 0;
 };

@@ -1,6 +1,13 @@
-// Whole path with HOST buffers: H2D -> log-mel -> running stats -> two views -> D2H, all enqueued
-// on one stream.  This is the entry a DataLoader-side caller of the reference would bind in place
-// of BaseDataset.__getitem__'s per-clip CPU work (/root/reference/src/dataset/upstream_dataset.py:65,82,86).
+// Whole path with HOST buffers: H2D -> log-mel -> running stats -> two views -> D2H.
+// This is the entry a DataLoader-side caller of the reference would bind in place of
+// BaseDataset.__getitem__'s per-clip CPU work (/root/reference/src/dataset/upstream_dataset.py:65,82,86).
+//
+// Three queues: uploads (s_in), kernels (the caller's stream), downloads (s_out).  The batch is cut into
+// chunks so chunk c+1 uploads while chunk c computes and chunk c-1 downloads, and the waveform / view
+// buffers of the workspace are double-buffered by call parity so call k+1's upload and kernels overlap
+// call k's download: PCIe is full duplex, so steady state costs max(upload, download) per batch instead
+// of their sum.  Kernels stay in order on the caller's stream (statistics scan and bank are sequential
+// in clip order).  Host result buffers are complete after assl_pipeline_host_sync().
 #include "common.cuh"
 
 namespace {
@@ -8,26 +15,28 @@ namespace {
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
 struct WsLayout {
-  size_t state, stats_ring, lms_ring, wave, tile_sums, clip_slot, mix_slot, alpha, crop, view1, view2, total;
+  size_t state, stats_ring, lms_ring, tile_sums, clip_slot, mix_slot, alpha, crop, wave[2], view1[2], view2[2], total;
 };
 
 WsLayout layout(const assl_plan* p, int64_t B, int64_t L, int64_t cap) {
   const int64_t T = 1 + L / p->cfg.hop;
-  const int64_t tiles = assl_plan_num_tiles(p, L);
+  const int64_t parts = assl_plan_num_tiles(p, L);
   const size_t plane = static_cast<size_t>(p->cfg.n_mels) * T * sizeof(float);
   WsLayout w;
   size_t o = 0;
   w.state = o;      o = align_up(o + 8 * sizeof(double));
   w.stats_ring = o; o = align_up(o + static_cast<size_t>(cap) * 2 * sizeof(float));
   w.lms_ring = o;   o = align_up(o + static_cast<size_t>(cap) * plane);
-  w.wave = o;       o = align_up(o + static_cast<size_t>(B) * L * sizeof(float));
-  w.tile_sums = o;  o = align_up(o + static_cast<size_t>(B) * tiles * 2 * sizeof(double));
+  w.tile_sums = o;  o = align_up(o + static_cast<size_t>(B) * parts * 2 * sizeof(double));
   w.clip_slot = o;  o = align_up(o + static_cast<size_t>(B) * sizeof(int32_t));
-  w.mix_slot = o;   o = align_up(o + static_cast<size_t>(B) * 2 * sizeof(int32_t));
-  w.alpha = o;      o = align_up(o + static_cast<size_t>(B) * 2 * sizeof(float));
-  w.crop = o;       o = align_up(o + static_cast<size_t>(B) * 8 * sizeof(int32_t));
-  w.view1 = o;      o = align_up(o + static_cast<size_t>(B) * plane);
-  w.view2 = o;      o = align_up(o + static_cast<size_t>(B) * plane);
+  w.mix_slot = o;   o = align_up(o + 2 * static_cast<size_t>(B) * 2 * sizeof(int32_t));   // x2: double-buffered
+  w.alpha = o;      o = align_up(o + 2 * static_cast<size_t>(B) * 2 * sizeof(float));
+  w.crop = o;       o = align_up(o + 2 * static_cast<size_t>(B) * 8 * sizeof(int32_t));
+  for (int i = 0; i < 2; ++i) {
+    w.wave[i] = o;  o = align_up(o + static_cast<size_t>(B) * L * sizeof(float));
+    w.view1[i] = o; o = align_up(o + static_cast<size_t>(B) * plane);
+    w.view2[i] = o; o = align_up(o + static_cast<size_t>(B) * plane);
+  }
   w.total = o;
   return w;
 }
@@ -37,11 +46,32 @@ __global__ void iota_slots_kernel(int32_t* slot, long long B, long long slot0, l
   if (b < B) slot[b] = static_cast<int32_t>(assl::ring_slot(slot0, b, cap));
 }
 
+int ensure_aux(const assl_plan* p) {
+  if (p->aux_ready) return ASSL_OK;
+  bool ok = cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking) == cudaSuccess;
+  auto mk = [&](cudaEvent_t* e) { ok = ok && cudaEventCreateWithFlags(e, cudaEventDisableTiming) == cudaSuccess; };
+  mk(&p->ev_fork);
+  for (int i = 0; i < 2; ++i) { mk(&p->ev_kern[i]); mk(&p->ev_d2h[i]); }
+  for (int i = 0; i < assl_plan::kMaxChunks; ++i) { mk(&p->ev_in[i]); mk(&p->ev_out[i]); }
+  if (!ok) return ASSL_ERR_CUDA;
+  p->aux_ready = true;
+  return ASSL_OK;
+}
+
 }  // namespace
 
 extern "C" int64_t assl_pipeline_workspace_bytes(const assl_plan* p, int64_t B, int64_t L, int64_t cap) {
   if (!p || B < 1 || cap < B || L <= p->cfg.n_fft / 2) return -1;
   return static_cast<int64_t>(layout(p, B, L, cap).total);
+}
+
+extern "C" int assl_pipeline_host_sync(const assl_plan* p) {
+  if (!p) return ASSL_ERR_INVALID_ARG;
+  if (!p->aux_ready) return ASSL_OK;
+  bool ok = cudaStreamSynchronize(p->s_in) == cudaSuccess;
+  ok = cudaStreamSynchronize(p->s_out) == cudaSuccess && ok;
+  return ok ? ASSL_OK : ASSL_ERR_CUDA;
 }
 
 extern "C" int assl_pipeline_host_f32(const assl_plan* p, const assl_view_cfg* vc, void* ws, int64_t ws_bytes,
@@ -56,38 +86,71 @@ extern "C" int assl_pipeline_host_f32(const assl_plan* p, const assl_view_cfg* v
   if (vc->n_freq != p->cfg.n_mels || vc->n_time != T) return ASSL_ERR_INVALID_ARG;
   const WsLayout w = layout(p, B, L, cap);
   if (static_cast<size_t>(ws_bytes) < w.total) return ASSL_ERR_INVALID_ARG;
+  int rc = ensure_aux(p);
+  if (rc != ASSL_OK) return rc;
+
   cudaStream_t st = as_stream(stream);
+  const int par = static_cast<int>(p->calls & 1);
   char* base = static_cast<char*>(ws);
   double* state = reinterpret_cast<double*>(base + w.state);
   float* stats = reinterpret_cast<float*>(base + w.stats_ring);
   float* lms = reinterpret_cast<float*>(base + w.lms_ring);
-  float* wave = reinterpret_cast<float*>(base + w.wave);
   double* tsums = reinterpret_cast<double*>(base + w.tile_sums);
   int32_t* clip_slot = reinterpret_cast<int32_t*>(base + w.clip_slot);
-  int32_t* mix_slot = reinterpret_cast<int32_t*>(base + w.mix_slot);
-  float* alpha = reinterpret_cast<float*>(base + w.alpha);
-  int32_t* crop = reinterpret_cast<int32_t*>(base + w.crop);
-  float* v1 = reinterpret_cast<float*>(base + w.view1);
-  float* v2 = reinterpret_cast<float*>(base + w.view2);
-  const size_t plane = static_cast<size_t>(p->cfg.n_mels) * T * sizeof(float);
+  int32_t* mix_slot = reinterpret_cast<int32_t*>(base + w.mix_slot) + par * B * 2;
+  float* alpha = reinterpret_cast<float*>(base + w.alpha) + par * B * 2;
+  int32_t* crop = reinterpret_cast<int32_t*>(base + w.crop) + par * B * 8;
+  float* wave = reinterpret_cast<float*>(base + w.wave[par]);
+  float* v1 = reinterpret_cast<float*>(base + w.view1[par]);
+  float* v2 = reinterpret_cast<float*>(base + w.view2[par]);
+  const int64_t elems = static_cast<int64_t>(p->cfg.n_mels) * T;
+  const size_t plane = static_cast<size_t>(elems) * sizeof(float);
+  const int64_t n_parts = assl_plan_num_tiles(p, L);
+  const int n_chunks = B >= 256 ? 4 : (B >= 32 ? 2 : 1);
 
   bool ok = true;
-  ok &= cudaMemcpyAsync(wave, host_wave, static_cast<size_t>(B) * L * sizeof(float), cudaMemcpyHostToDevice, st) == cudaSuccess;
-  ok &= cudaMemcpyAsync(mix_slot, host_mix_slot, static_cast<size_t>(B) * 2 * sizeof(int32_t), cudaMemcpyHostToDevice, st) == cudaSuccess;
-  ok &= cudaMemcpyAsync(alpha, host_alpha, static_cast<size_t>(B) * 2 * sizeof(float), cudaMemcpyHostToDevice, st) == cudaSuccess;
-  ok &= cudaMemcpyAsync(crop, host_crop, static_cast<size_t>(B) * 8 * sizeof(int32_t), cudaMemcpyHostToDevice, st) == cudaSuccess;
-  if (!ok) return ASSL_ERR_CUDA;
+  auto cp = [&](void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t s) {
+    ok = ok && cudaMemcpyAsync(dst, src, bytes, kind, s) == cudaSuccess;
+  };
+  // order the uploads against whatever the caller queued on its stream before the first calls (its own
+  // zero-fill of the workspace state ...), later against the kernels of the call that last used this parity
+  if (p->calls < 2) {
+    ok = ok && cudaEventRecord(p->ev_fork, st) == cudaSuccess;
+    ok = ok && cudaStreamWaitEvent(p->s_in, p->ev_fork, 0) == cudaSuccess;
+  } else {
+    ok = ok && cudaStreamWaitEvent(p->s_in, p->ev_kern[par], 0) == cudaSuccess;
+  }
+  cp(mix_slot, host_mix_slot, static_cast<size_t>(B) * 2 * sizeof(int32_t), cudaMemcpyHostToDevice, p->s_in);
+  cp(alpha, host_alpha, static_cast<size_t>(B) * 2 * sizeof(float), cudaMemcpyHostToDevice, p->s_in);
+  cp(crop, host_crop, static_cast<size_t>(B) * 8 * sizeof(int32_t), cudaMemcpyHostToDevice, p->s_in);
   iota_slots_kernel<<<static_cast<unsigned>((B + 255) / 256), 256, 0, st>>>(clip_slot, B, slot0, cap);
+  // the view buffers of this parity were downloaded two calls ago; kernels that overwrite them wait for that
+  if (p->calls >= 2) ok = ok && cudaStreamWaitEvent(st, p->ev_d2h[par], 0) == cudaSuccess;
 
-  int rc = assl_logmel_f32(p, wave, nullptr, B, L, L, lms, slot0, cap, tsums, 0, stream);
+  for (int c = 0; c < n_chunks && ok && rc == ASSL_OK; ++c) {
+    const int64_t b0 = B * c / n_chunks, b1 = B * (c + 1) / n_chunks, nb = b1 - b0;
+    if (nb == 0) continue;
+    cp(wave + b0 * L, host_wave + b0 * L, static_cast<size_t>(nb) * L * sizeof(float), cudaMemcpyHostToDevice, p->s_in);
+    ok = ok && cudaEventRecord(p->ev_in[c], p->s_in) == cudaSuccess;
+    ok = ok && cudaStreamWaitEvent(st, p->ev_in[c], 0) == cudaSuccess;
+    const int64_t s0 = (slot0 + b0) % cap;
+    rc = assl_logmel_f32(p, wave + b0 * L, nullptr, nb, L, L, lms, s0, cap, tsums + b0 * n_parts * 2, 0, stream);
+    if (rc == ASSL_OK)
+      rc = assl_running_stats(state, tsums + b0 * n_parts * 2, nb, n_parts, elems, max_update, 0, nb, stats, s0, cap, stream);
+    if (rc == ASSL_OK)
+      rc = assl_two_views_f32(vc, lms, stats, cap, clip_slot + b0, mix_slot + b0 * 2, alpha + b0 * 2, crop + b0 * 8, nb,
+                              v1 + b0 * elems, v2 + b0 * elems, stream);
+    if (rc == ASSL_OK && (host_view1 || host_view2)) {
+      ok = ok && cudaEventRecord(p->ev_out[c], st) == cudaSuccess;
+      ok = ok && cudaStreamWaitEvent(p->s_out, p->ev_out[c], 0) == cudaSuccess;
+      if (host_view1) cp(host_view1 + b0 * elems, v1 + b0 * elems, static_cast<size_t>(nb) * plane, cudaMemcpyDeviceToHost, p->s_out);
+      if (host_view2) cp(host_view2 + b0 * elems, v2 + b0 * elems, static_cast<size_t>(nb) * plane, cudaMemcpyDeviceToHost, p->s_out);
+    }
+  }
   if (rc != ASSL_OK) return rc;
-  rc = assl_running_stats(state, tsums, B, assl_plan_num_tiles(p, L), static_cast<int64_t>(p->cfg.n_mels) * T,
-                          max_update, 0, B, stats, slot0, cap, stream);
-  if (rc != ASSL_OK) return rc;
-  rc = assl_two_views_f32(vc, lms, stats, cap, clip_slot, mix_slot, alpha, crop, B, v1, v2, stream);
-  if (rc != ASSL_OK) return rc;
-  if (host_view1) ok &= cudaMemcpyAsync(host_view1, v1, static_cast<size_t>(B) * plane, cudaMemcpyDeviceToHost, st) == cudaSuccess;
-  if (host_view2) ok &= cudaMemcpyAsync(host_view2, v2, static_cast<size_t>(B) * plane, cudaMemcpyDeviceToHost, st) == cudaSuccess;
+  ok = ok && cudaEventRecord(p->ev_kern[par], st) == cudaSuccess;
+  ok = ok && cudaEventRecord(p->ev_d2h[par], p->s_out) == cudaSuccess;
+  p->calls += 1;
   if (dev_view1) *dev_view1 = v1;
   if (dev_view2) *dev_view2 = v2;
   return ok ? launch_status() : ASSL_ERR_CUDA;

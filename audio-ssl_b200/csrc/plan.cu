@@ -147,6 +147,12 @@ extern "C" int assl_plan_destroy(assl_plan* p) {
   cudaFree(p->d_mel_off);
   cudaFree(p->d_mel_w);
   cudaFree(p->d_mel_const);
+  if (p->aux_ready) {
+    cudaStreamDestroy(p->s_in); cudaStreamDestroy(p->s_out);
+    cudaEventDestroy(p->ev_fork);
+    for (int i = 0; i < 2; ++i) { cudaEventDestroy(p->ev_kern[i]); cudaEventDestroy(p->ev_d2h[i]); }
+    for (int i = 0; i < assl_plan::kMaxChunks; ++i) { cudaEventDestroy(p->ev_in[i]); cudaEventDestroy(p->ev_out[i]); }
+  }
   delete p;
   return ASSL_OK;
 }

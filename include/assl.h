@@ -158,12 +158,16 @@ int assl_normalize_apply_f32(const float* x, float* y, int64_t n, const double* 
 int assl_affine_norm_f32(const float* x, float* y, int64_t n, float mean, float std, void* stream);
 
 /* -- whole path, HOST buffers (what a DataLoader-side caller binds) --------------------------
- * host_wave [B, L] (pinned for async copies) -> H2D -> log-mel -> running stats -> two views -> D2H
- * into host_view1/2 [B, F, T].  Parameter arrays are HOST pointers with the layouts above
- * (slots refer to the ring inside ``ws``).  ``ws`` is a caller-owned DEVICE workspace of at least
- * assl_pipeline_workspace_bytes(); the ring (cap slots) and the norm state live at its start
- * and persist between calls.  host_view* may be NULL to leave the views on the device (their
- * device addresses are returned through dev_view1/2 when non-NULL).                            */
+ * host_wave [B, L] (pinned, so the copies are asynchronous) -> H2D -> log-mel -> running stats -> two views
+ * -> D2H into host_view1/2 [B, F, T].  Parameter arrays are HOST pointers with the layouts above (slots refer
+ * to the ring inside ``ws``).  ``ws`` is a caller-owned DEVICE workspace of at least
+ * assl_pipeline_workspace_bytes(), zero-filled before first use; the ring (cap slots) and the norm state
+ * live at its start and persist between calls.  Kernels run in order on ``stream``; uploads and downloads
+ * run on two internal copy streams, chunked and double-buffered so that consecutive calls overlap upload,
+ * kernels and download.  Every host buffer passed in must stay untouched, and host_view* is complete, only
+ * after assl_pipeline_host_sync(plan) returns.  host_view* may be NULL to leave the views on the device:
+ * their device addresses are returned through dev_view1/2 and are valid in ``stream`` order until the call
+ * after next.  One caller at a time per plan for these two entry points.                               */
 int64_t assl_pipeline_workspace_bytes(const assl_plan* plan, int64_t B, int64_t L, int64_t cap);
 int assl_pipeline_host_f32(const assl_plan* plan, const assl_view_cfg* vcfg, void* ws,
                            int64_t ws_bytes, const float* host_wave, int64_t B, int64_t L,
@@ -171,6 +175,7 @@ int assl_pipeline_host_f32(const assl_plan* plan, const assl_view_cfg* vcfg, voi
                            const int32_t* host_mix_slot, const float* host_alpha,
                            const int32_t* host_crop, float* host_view1, float* host_view2,
                            float** dev_view1, float** dev_view2, void* stream);
+int assl_pipeline_host_sync(const assl_plan* plan);
 
 #ifdef __cplusplus
 }
