@@ -13,6 +13,9 @@ namespace assl {
 constexpr int kNfft = 1024;             // the FFT kernel is specialised for 32 x 32 points
 constexpr int kBins = kNfft / 2 + 1;    // 513
 constexpr int kMaxMels = 128;
+constexpr int kIvSlots = 8;             // most filterbank-interval parts a lane of the log-mel kernel can own
+constexpr int kPartBins = 8;            // bins per part (two per 128-bit load)
+constexpr int kScratchEntries = 208;    // 16-byte interval totals that fit behind a warp's power spectra
 
 constexpr float kPowerEps = 2.220446049250313e-16f;   // np.finfo(float).eps   (utils.py:28)
 constexpr float kLogEps = 1.1920928955078125e-07f;    // torch.finfo().eps     (utils.py:48)
@@ -35,15 +38,18 @@ struct assl_plan {
   assl_cfg cfg;
   int device;
   int sm_count;
-  int nnz;                      // stored filterbank taps (contiguous support of every band)
-  float* d_win_half;            // [n_fft]      0.5 * periodic Hann (the 1/2 of the two-frame unpack folded in)
+  int n_iw;                     // stored filterbank weight pairs (interval form, see plan.cu)
+  int n_slots;                  // interval parts a lane owns in the log-mel kernel (rows of d_lane_iv in use)
   float2* d_twiddle;            // [32][32]     tw[k2][n1] = exp(-2 pi i n1 k2 / 1024)
-  int* d_mel_k0;                // [n_mels]     first bin of the band's support
-  int* d_mel_cnt;               // [n_mels]     bins in the support
-  int* d_mel_off;               // [n_mels]     offset into d_mel_w
-  float* d_mel_w;               // [nnz]        fp32 weights
+  float2* d_iv_w;               // [n_iw]       {falling-edge weight of band j-1, rising-edge weight of band j}
+  int4* d_lane_iv;              // [slots][32]  interval owned by (slot, lane) in the log-mel kernel:
+                                //              {first bin (even), bin pairs, offset into d_iv_w (even),
+                                //               scratch entry | starts-the-total << 16, or -1}
   float* d_mel_const;           // [n_mels]     2.22e-16 * sum of the band's weights (folded "+ eps" of utils.py:28)
   std::vector<float> h_fb;      // dense [n_mels][513] copy for assl_plan_filterbank
+  std::vector<int4> h_lane_iv;  // host copy of d_lane_iv
+  std::vector<int> h_iv_pos;    // [n_mels+1] scratch entry of every interval's total
+  int* d_iv_pos = nullptr;
   // Copy streams + events of assl_pipeline_host_f32 (created on first use; that entry point is
   // single-caller per plan, everything else on a plan is read-only and thread-safe).
   static constexpr int kMaxChunks = 8;

@@ -4,28 +4,54 @@
 // extract_log_mel_spectrogram (/root/reference/src/utils/utils.py:43-49).
 //
 // Work decomposition
-//   persistent CTAs (2 per SM) loop over tiles of kFramesPerTile consecutive frames of one clip;
-//   the tile's waveform span is brought into shared memory by ONE bulk async copy (TMA, cp.async.bulk
-//   + mbarrier) issued a tile ahead, so the 6.4x overlap between hop-160 frames never goes back to
-//   L2/HBM and the global latency hides behind the previous tile's FFTs; librosa's reflect padding
-//   only touches the first/last tiles of a clip and is patched in by a short scalar fix-up;
-//   each warp transforms TWO real frames at once as one 1024-point complex FFT laid out 32 x 32:
-//   lane n1 holds samples n1 + 32*n2 (stride-32, conflict-free LDS; when hop is a multiple of 32 the
-//   second frame's samples are the first frame's shifted by hop/32 registers, so 37 loads feed both),
-//   runs a register-resident 32-point FFT (fft32_gen.cuh), multiplies by the inter-stage twiddles,
-//   transposes through a padded per-warp shared buffer, runs the second 32-point FFT, and unpacks the
-//   two spectra with one shuffle per partner value (bin k of lane l pairs with bin 1024-k of lane 32-l);
-//   the two power spectra go back to the warp's own shared buffer, then the whole CTA applies the
-//   sparse (triangular-support) filterbank, takes the log and writes [n_mels, T] row-major.
+//   persistent CTAs (2 per SM) loop over tiles of 8 consecutive frame pairs; the tile's waveform span is
+//   brought into shared memory by ONE bulk async copy (TMA, cp.async.bulk + mbarrier) issued a tile
+//   ahead, so the 6.4x overlap between hop-160 frames never goes back to L2/HBM and the global latency
+//   hides behind the previous tile's FFTs; librosa's reflect padding only touches the first/last tiles
+//   of a clip and is patched in by a short scalar fix-up.
+//   Each WARP then takes one frame pair from samples to log-mel values on its own, with no CTA-wide
+//   barrier in between (the only hand-off per tile is a non-blocking named-barrier arrive that lets
+//   warp 0 launch the next copy):
+//     * the two real frames are the real and imaginary part of one 1024-point complex FFT laid out
+//       32 x 32: lane n1 holds samples n1 + 32*n2 (stride-32, conflict-free LDS; when hop is a multiple
+//       of 32 the second frame is the first shifted by hop/32 registers, so 37 loads feed both);
+//     * all arithmetic is two-wide (f32x2.cuh: FFMA2/FADD2/FMUL2 on {re, im} register pairs): a
+//       register-resident 32-point FFT (fft32p_gen.cuh, 194 instructions), the inter-stage twiddles,
+//       a transpose through the warp's padded shared buffer (128-bit row stores, 64-bit column loads),
+//       the second 32-point FFT, and the two-for-one unpack (bin k of lane l pairs with bin 1024-k of
+//       lane 32-l: one shuffle per half) straight into the two power spectra;
+//     * the power spectra go back to the warp's buffer and the same warp applies the filterbank in
+//       "interval" form: the bins between two neighbouring band centres feed the falling edge of one
+//       band and the rising edge of the next, so every power value is read once; a lane owns the same
+//       few intervals for the whole launch, a second short pass adds the two halves of each band,
+//       takes the log and writes [n_mels, T] row-major.
 #include "common.cuh"
-#include "fft32_gen.cuh"
+#include "fft32p_gen.cuh"
 
 namespace assl {
 
 constexpr int kWarps = 8;
 constexpr int kThreads = kWarps * 32;
-constexpr int kExStride = 33;                       // float2 units: lane-major rows padded by one
-constexpr int kExWarp = 32 * kExStride + 2;         // 1058 float2 = 2116 words == 4 (mod 32)
+constexpr int kExStride = 34;                       // float2 units: lane-major rows of 32 + 2 pad (272 B: 128-bit
+                                                    // row stores of a quarter warp hit 8 distinct 16-byte bank groups)
+constexpr int kExWarp = 32 * kExStride + 2;         // 1090 float2 = 8720 B per warp
+constexpr int kScratch = 640;                       // float2 offset of the interval totals inside a warp's buffer
+                                                    // (padded power reads stay below 640; kScratchEntries x 16 B fit behind)
+static_assert(kScratch + 2 * kScratchEntries <= 32 * kExStride, "interval totals overflow the warp buffer");
+constexpr int kTwStride = 10;                       // float2 units: per lane w^8, w^16, w^24, w^1..w^7 (w = W_1024^lane);
+                                                    // 80-byte rows: an odd number of 16-byte groups, conflict-free
+
+// cos / sin of 2 pi n2 / 32, n2 = 0..16 (window phase of register n2, see the kernel prologue)
+__device__ constexpr double kCosPhi[17] = {
+    1.0, 0.98078528040323043, 0.92387953251128674, 0.83146961230254524, 0.70710678118654757,
+    0.55557023301960218, 0.38268343236508978, 0.19509032201612825, 0.0, -0.19509032201612825,
+    -0.38268343236508978, -0.55557023301960218, -0.70710678118654757, -0.83146961230254524,
+    -0.92387953251128674, -0.98078528040323043, -1.0};
+__device__ constexpr double kSinPhi[17] = {
+    0.0, 0.19509032201612825, 0.38268343236508978, 0.55557023301960218, 0.70710678118654757,
+    0.83146961230254524, 0.92387953251128674, 0.98078528040323043, 1.0, 0.98078528040323043,
+    0.92387953251128674, 0.83146961230254524, 0.70710678118654757, 0.55557023301960218,
+    0.38268343236508978, 0.19509032201612825, 0.0};
 
 struct LogmelArgs {
   const float* wave;
@@ -33,29 +59,32 @@ struct LogmelArgs {
   float* lms;
   double* tile_sums;
   long long L, ld, slot0, cap;
-  int B, T, hop, n_mels, nnz, out_kind, bulk_ok;
+  int B, T, hop, n_mels, out_kind, bulk_ok;
   int ppc;            // frame pairs per clip = ceil(T / 2)
+  unsigned ppc_mul;   // n / ppc == (t + ((n - t) >> ppc_sh1)) >> ppc_sh2 with t = umulhi(ppc_mul, n)
+  int ppc_sh1, ppc_sh2;
   int straddle;       // 1: a tile is 8 consecutive pairs of the flattened (clip, pair) list and may span two clips
   int total_tiles, n_parts, wave_floats;
-  const float* win;
+  int n_iw;           // float2 entries of iv_w
+  int n_slots;        // rows of lane_iv in use
   const float2* tw;
-  const int* mk0;
-  const int* mcnt;
-  const int* moff;
-  const float* mw;
+  const float2* iv_w;    // {falling-edge weight of band j-1, rising-edge weight of band j} per bin
+  const int4* lane_iv;   // [kIvSlots][32] interval owned by (slot, lane): {first bin, bin pairs, offset in iv_w, id or -1}
+  const int* iv_pos;     // [n_mels + 1] scratch entry holding interval j's total
   const float* mconst;   // [n_mels] 2.22e-16 * sum of the band's weights (the "+ eps" of utils.py:28, folded)
 };
 
-__host__ __device__ inline size_t logmel_smem_bytes(int wave_floats, int nnz) {
+__host__ __device__ inline size_t logmel_smem_bytes(int wave_floats, int n_iw) {
   size_t b = 0;
-  b += sizeof(float2) * kWarps * kExWarp;   // exchange / power buffers
-  b += sizeof(float2) * 1024;               // twiddles
-  b += sizeof(float) * 1024;                // window
+  b += sizeof(float2) * kWarps * kExWarp;   // exchange / power / interval-sum buffers
+  b += sizeof(float2) * 32 * kTwStride;     // twiddles
   b += sizeof(float) * ((wave_floats + 3) & ~3);
-  b += sizeof(float) * ((nnz + 3) & ~3);
-  b += sizeof(int) * 3 * kMaxMels + sizeof(float) * kMaxMels;
-  b += sizeof(float2) * 2 * kWarps * kWarps;   // per (warp, frame pair) (sum, sum^2), double-buffered by tile parity
-  b += 2 * sizeof(unsigned long long);      // mbarriers
+  b += sizeof(float2) * ((n_iw + 1) & ~1);
+  b += sizeof(float) * kMaxMels;            // per-band folded eps
+  b += sizeof(int4) * kIvSlots * 32;        // interval ownership
+  b += sizeof(int) * (kMaxMels + 4);        // scratch entry per interval
+  b += sizeof(float2) * 2 * kWarps;         // per (tile parity, warp) (sum, sum^2)
+  b += 2 * sizeof(unsigned long long);      // mbarrier
   return b;
 }
 
@@ -104,7 +133,8 @@ __device__ __forceinline__ void tile_segments(const LogmelArgs& a, int tile, Seg
     p0 = tile * a.ppc;
     np = a.ppc;
   }
-  const int b0 = p0 / a.ppc;
+  const unsigned t = __umulhi(a.ppc_mul, static_cast<unsigned>(p0));
+  const int b0 = static_cast<int>((t + ((static_cast<unsigned>(p0) - t) >> a.ppc_sh1)) >> a.ppc_sh2);
   const int q0 = p0 - b0 * a.ppc;
   const int n0 = np < a.ppc - q0 ? np : a.ppc - q0;
   seg[0].clip = b0; seg[0].q0 = q0; seg[0].n = n0; seg[0].off = 0;
@@ -131,26 +161,38 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float2* s_ex = reinterpret_cast<float2*>(smem_raw);
   float2* s_tw = s_ex + kWarps * kExWarp;
-  float* s_win = reinterpret_cast<float*>(s_tw + 1024);
-  float* s_wave = s_win + 1024;
-  float* s_mw = s_wave + ((a.wave_floats + 3) & ~3);
-  int* s_mk0 = reinterpret_cast<int*>(s_mw + ((a.nnz + 3) & ~3));
-  int* s_mcnt = s_mk0 + kMaxMels;
-  int* s_moff = s_mcnt + kMaxMels;
-  float* s_mconst = reinterpret_cast<float*>(s_moff + kMaxMels);
-  float2* s_red = reinterpret_cast<float2*>(s_mconst + kMaxMels);          // [2][kWarps][kWarps]
-  unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_red + 2 * kWarps * kWarps);
+  float* s_wave = reinterpret_cast<float*>(s_tw + 32 * kTwStride);
+  float2* s_ivw = reinterpret_cast<float2*>(s_wave + ((a.wave_floats + 3) & ~3));
+  float* s_mconst = reinterpret_cast<float*>(s_ivw + ((a.n_iw + 1) & ~1));
+  int4* s_lane = reinterpret_cast<int4*>(s_mconst + kMaxMels);             // [kIvSlots][32]
+  int* s_pos = reinterpret_cast<int*>(s_lane + kIvSlots * 32);              // [n_mels + 1]
+  float2* s_red = reinterpret_cast<float2*>(s_pos + kMaxMels + 4);          // [2][kWarps]
+  unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_red + 2 * kWarps);
   void* bar_wave = s_bar;        // tile's waveform spans have landed (tx bytes)
-  void* bar_mel = s_bar + 1;     // every thread is done reading the previous tile's power spectra
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-  if (tid == 0) { mbar_init(bar_wave, 1); mbar_init(bar_mel, kThreads); }
-  for (int i = tid; i < 1024; i += kThreads) { s_tw[i] = a.tw[i]; s_win[i] = a.win[i]; }
-  for (int i = tid; i < a.nnz; i += kThreads) s_mw[i] = a.mw[i];
-  for (int i = tid; i < a.n_mels; i += kThreads) {
-    s_mk0[i] = a.mk0[i]; s_mcnt[i] = a.mcnt[i]; s_moff[i] = a.moff[i]; s_mconst[i] = a.mconst[i];
+  if (tid == 0) mbar_init(bar_wave, 1);
+  // Inter-stage twiddles w^k2 (w = W_1024^lane): only w^8, w^16, w^24 and w^1..w^7 are kept per lane; the
+  // other 21 are applied as two rotations, (z * w^b) * w^(8a), trading 42 FFMA2/FMUL2 per transform for two
+  // thirds of the table's shared-memory traffic
+  for (int i = tid; i < 32 * kTwStride; i += kThreads) {
+    const int n1 = i / kTwStride, e = i - n1 * kTwStride;
+    const int k2 = e < 3 ? 8 * (e + 1) : e - 2;
+    s_tw[i] = a.tw[k2 * 32 + n1];
   }
+  // Window (periodic Hann, times the 1/2 of the two-frame unpack) without a table: for n = lane + 32 n2
+  //   w = 1/4 - 1/4 cos(theta + phi),  theta = 2 pi lane / 1024 (per lane),  phi = 2 pi n2 / 32 (compile time)
+  //     = 1/4 + wa cos(phi) + wb sin(phi),  wa = -1/4 cos(theta),  wb = 1/4 sin(theta)
+  float wa, wb;
+  sincospif(static_cast<float>(lane) * (1.0f / 512.0f), &wb, &wa);
+  wa *= -0.25f; wb *= 0.25f;
+  for (int i = tid; i < a.n_iw; i += kThreads) s_ivw[i] = a.iv_w[i];
+  for (int i = tid; i < a.n_mels; i += kThreads) s_mconst[i] = a.mconst[i];
+  for (int i = tid; i < kIvSlots * 32; i += kThreads) s_lane[i] = a.lane_iv[i];
+  for (int i = tid; i <= a.n_mels; i += kThreads) s_pos[i] = a.iv_pos[i];
+  // padded power reads (zero weights) must see finite values: the row padding of s_ex is never written again
+  for (int i = tid; i < kWarps * kExWarp; i += kThreads) s_ex[i] = make_float2(0.f, 0.f);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();
 
@@ -175,18 +217,13 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
   };
   if (a.bulk_ok && tid == 0 && static_cast<int>(blockIdx.x) < a.total_tiles) issue_tile(blockIdx.x);
 
-  // flush the statistics a tile left in s_red: one (sum, sum^2) pair per clip segment, fixed summation
-  // order.  Called by warp 0: lane f adds up frame pair f over the 8 producing warps, then a masked
-  // butterfly combines the pairs of each segment.
+  // flush the statistics a tile left in s_red (one (sum, sum^2) per frame pair): one pair of doubles per
+  // clip segment, fixed summation order.  Called by warp 0 once every warp is done with that tile.
   auto flush_stats = [&](int tile, unsigned parity) {
     Segment seg[2];
     tile_segments(a, tile, seg);
-    const float2* r = s_red + parity * kWarps * kWarps;
     double r1 = 0.0, r2 = 0.0;
-    if (lane < kWarps) {
-#pragma unroll
-      for (int w = 0; w < kWarps; ++w) { const float2 v = r[w * kWarps + lane]; r1 += v.x; r2 += v.y; }
-    }
+    if (lane < kWarps) { const float2 v = s_red[parity * kWarps + lane]; r1 = v.x; r2 = v.y; }
     const int n0 = seg[0].n, np = n0 + seg[1].n;
     double a1 = lane < n0 ? r1 : 0.0, a2 = lane < n0 ? r2 : 0.0;            // segment 0
     double b1 = (lane >= n0 && lane < np) ? r1 : 0.0, b2 = (lane >= n0 && lane < np) ? r2 : 0.0;   // segment 1
@@ -213,8 +250,12 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
 
     // ---- waveform spans: wait for the bulk copies, patch what they could not cover (reflect padding of
     //      np.pad(mode='reflect'): p<0 -> -p, p>L-1 -> 2(L-1)-p; tail remainder when L % 4 != 0)
-    if (a.bulk_ok) mbar_wait(bar_wave, it & 1);
-    else __syncthreads();                            // previous tile's input reads are done
+    if (a.bulk_ok) {
+      mbar_wait(bar_wave, it & 1);
+    } else {
+      __syncthreads();                               // previous tile's input reads are done
+      if (a.tile_sums && warp == 0 && prev_tile >= 0) flush_stats(prev_tile, (it - 1) & 1);
+    }
     bool fixed = false;
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
@@ -244,129 +285,162 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
     const bool have = warp < np;                      // warp-uniform
     const int wseg = warp >= n0 ? 1 : 0;
     const int wpair = wseg ? warp - n0 : seg[0].q0 + warp;        // pair index inside its clip
-    float2* ex = s_ex + warp * kExWarp;
-    float re[32], im[32];
+    c32* ex = reinterpret_cast<c32*>(s_ex + warp * kExWarp);
+    c32 z[32];                                       // {frame 2q, frame 2q+1} = {re, im} of one complex transform
     if (have) {
       const float* w0 = s_wave + (wseg ? seg[1].off + wpair * 2 * a.hop : warp * 2 * a.hop) + lane;
-      if (H32 > 0) {
-        float s[32 + H32];
+      float s[32 + (H32 > 0 ? H32 : 32)];              // frame 2q: s[n2]; frame 2q+1: s[n2 + H32] (or the second half)
+      constexpr int kB = H32 > 0 ? H32 : 32;
 #pragma unroll
-        for (int j = 0; j < 32 + H32; ++j) s[j] = w0[32 * j];
-#pragma unroll
-        for (int n2 = 0; n2 < 32; ++n2) {
-          const float w = s_win[lane + 32 * n2];
-          re[n2] = w * s[n2];
-          im[n2] = w * s[n2 + H32];
-        }
-      } else {
+      for (int j = 0; j < 32 + (H32 > 0 ? H32 : 0); ++j) s[j] = w0[32 * j];
+      if (H32 == 0) {
         const float* w1 = w0 + a.hop;
 #pragma unroll
-        for (int n2 = 0; n2 < 32; ++n2) {
-          const float w = s_win[lane + 32 * n2];
-          re[n2] = w * w0[32 * n2];
-          im[n2] = w * w1[32 * n2];
-        }
+        for (int j = 0; j < 32; ++j) s[32 + j] = w1[32 * j];
+      }
+      // (the asm keeps the compiler from hoisting 32 window values out of the tile loop and spilling them)
+      asm volatile("" : "+f"(wa), "+f"(wb));
+      {
+        const float wl = 0.25f + wa, wh = 0.25f - wa;
+        z[0] = pk(wl * s[0], wl * s[kB]);
+        z[16] = pk(wh * s[16], wh * s[16 + kB]);
+      }
+#pragma unroll
+      for (int n2 = 1; n2 < 16; ++n2) {              // phi and 2 pi - phi share the cosine
+        const float c = static_cast<float>(kCosPhi[n2]), sn = static_cast<float>(kSinPhi[n2]);
+        const float t = fmaf(wa, c, 0.25f);
+        const float wl = fmaf(wb, sn, t), wh = fmaf(wb, -sn, t);
+        z[n2] = pk(wl * s[n2], wl * s[n2 + kB]);
+        z[32 - n2] = pk(wh * s[32 - n2], wh * s[32 - n2 + kB]);
       }
     }
-    // every warp has its samples in registers -> the next tile's copy may overwrite s_wave
+    // every warp has its samples in registers (and is done with the previous tile) -> warp 0 flushes the
+    // previous tile's statistics, then the next tile's copy may overwrite s_wave
     if (a.bulk_ok) {
       if (warp == 0) {
         asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory");
+        if (a.tile_sums && prev_tile >= 0) flush_stats(prev_tile, (it - 1) & 1);
         if (lane == 0 && tile + static_cast<int>(gridDim.x) < a.total_tiles) issue_tile(tile + gridDim.x);
       } else {
         asm volatile("bar.arrive 1, %0;" ::"n"(kThreads) : "memory");
       }
     }
-    if (have) {
-      fft32(re, im);                               // over n2 -> k2, this lane is n1
+    prev_tile = tile;
+    if (!have) continue;                             // warp-uniform
+
+    fft32p(z);                                       // over n2 -> k2, this lane is n1
+    {   // inter-stage twiddles W^(n1 k2), k2 = 8a + b: z * t = z * t.re + (i z) * t.im
+      const ulonglong2* tl = reinterpret_cast<const ulonglong2*>(s_tw + lane * kTwStride);
+      c32 t[10];                                     // w^8, w^16, w^24, w^1 .. w^7
 #pragma unroll
-      for (int k2 = 1; k2 < 32; ++k2) {
-        const float2 t = s_tw[k2 * 32 + lane];
-        const float r = re[k2] * t.x - im[k2] * t.y;
-        const float i = re[k2] * t.y + im[k2] * t.x;
-        re[k2] = r; im[k2] = i;
+      for (int q = 0; q < 5; ++q) { const ulonglong2 v = tl[q]; t[2 * q] = v.x; t[2 * q + 1] = v.y; }
+      auto rot = [](c32 v, c32 w) { return fma2(pj(v), bc(hi_of(w)), mul2(v, bc(lo_of(w)))); };
+#pragma unroll
+      for (int b = 1; b < 8; ++b) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) z[8 * g + b] = rot(z[8 * g + b], t[2 + b]);
+      }
+#pragma unroll
+      for (int g = 1; g < 4; ++g) {
+#pragma unroll
+        for (int b = 0; b < 8; ++b) z[8 * g + b] = rot(z[8 * g + b], t[g - 1]);
       }
     }
-    if (it > 0) mbar_wait(bar_mel, (it - 1) & 1);   // previous tile's power spectra are consumed
-    if (have) {
+    __syncwarp();                                    // the previous pair's interval sums have been read
+    {
+      ulonglong2* row = reinterpret_cast<ulonglong2*>(ex + lane * kExStride);
 #pragma unroll
-      for (int k2 = 0; k2 < 32; ++k2) ex[lane * kExStride + k2] = make_float2(re[k2], im[k2]);
-      __syncwarp();
+      for (int q = 0; q < 16; ++q) row[q] = make_ulonglong2(z[2 * q], z[2 * q + 1]);
+    }
+    __syncwarp();
 #pragma unroll
-      for (int n1 = 0; n1 < 32; ++n1) { const float2 v = ex[n1 * kExStride + lane]; re[n1] = v.x; im[n1] = v.y; }
-      fft32(re, im);                               // over n1 -> k1, this lane is k2: Z[lane + 32*k1]
+    for (int n1 = 0; n1 < 32; ++n1) z[n1] = ex[n1 * kExStride + lane];
+    fft32p(z);                                       // over n1 -> k1, this lane is k2: Z[lane + 32*k1]
 
-      // unpack: X1[k] = (Z[k] + conj Z[N-k]) / 2, X2[k] = (Z[k] - conj Z[N-k]) / 2i  (the 1/2 sits in the window)
+    // unpack: X1[k] = (Z[k] + conj Z[N-k]) / 2, X2[k] = (Z[k] - conj Z[N-k]) / 2i  (the 1/2 sits in the window)
+    // with b = Z[N-k]:  |X1|^2 = (re+br)^2 + (im-bi)^2,  |X2|^2 = (im+bi)^2 + (re-br)^2
+    {
       const int partner = (32 - lane) & 31;
-      float p1[16], p2[16];
+      const bool self = lane == 0;                   // bins 32 k1 pair with 32 (32 - k1): same lane, other register
+      c32 pw2[16];
 #pragma unroll
       for (int k1 = 0; k1 < 16; ++k1) {
-        float br = __shfl_sync(0xffffffffu, re[31 - k1], partner);
-        float bi = __shfl_sync(0xffffffffu, im[31 - k1], partner);
-        if (lane == 0) { br = re[(32 - k1) & 31]; bi = im[(32 - k1) & 31]; }
-        const float sr = re[k1] + br, di = im[k1] - bi;
-        const float si = im[k1] + bi, dr = re[k1] - br;
-        p1[k1] = sr * sr + di * di;
-        p2[k1] = si * si + dr * dr;
+        const c32 src = self ? z[(32 - k1) & 31] : z[31 - k1];
+        const c32 b = pk(__shfl_sync(0xffffffffu, lo_of(src), partner), __shfl_sync(0xffffffffu, hi_of(src), partner));
+        const c32 u = add2(z[k1], b), v = swp(sub2(z[k1], b));
+        pw2[k1] = fma2(u, u, mul2(v, v));
       }
-      __syncwarp();                                // everyone is done reading the exchange buffer
+      __syncwarp();                                  // everyone is done reading the exchange buffer
 #pragma unroll
-      for (int k1 = 0; k1 < 16; ++k1) ex[lane + 32 * k1] = make_float2(p1[k1], p2[k1]);
-      if (lane == 0) {                             // Nyquist bin: its own partner
-        const float nr = 2.f * re[16], ni = 2.f * im[16];
-        ex[512] = make_float2(nr * nr, ni * ni);
+      for (int k1 = 0; k1 < 16; ++k1) ex[lane + 32 * k1] = pw2[k1];
+      if (lane == 0) {                               // Nyquist bin: its own partner; bin 513 is tap padding
+        const c32 n2 = add2(z[16], z[16]);
+        ex[512] = mul2(n2, n2);
+        ex[513] = pk(0.f, 0.f);
       }
     }
-    __syncthreads();                               // power spectra of the whole tile are in shared memory
+    __syncwarp();                                    // both power spectra are in the warp's buffer
 
-    // flush the previous tile's statistics (all warps wrote them before reaching the barrier above)
-    if (a.tile_sums && warp == 0 && prev_tile >= 0) flush_stats(prev_tile, (it - 1) & 1);
+    // ---- filterbank, interval form.  Interval j = bins between the centres of bands j-1 and j; its bins feed
+    //      the falling edge of band j-1 (weight .x) and the rising edge of band j (weight .y).
+    //      Interval totals {Sd(j), Su(j)} live behind the power spectra, one 16-byte entry each at a
+    //      plan-chosen position; band m = Su(m) + Sd(m+1).
+    c32* scratch = ex + kScratch;
+    for (int s = 0; s < a.n_slots; ++s) {
+      const int4 iv = s_lane[s * 32 + lane];         // the same interval parts for the whole launch
+      const ulonglong2* wv = reinterpret_cast<const ulonglong2*>(s_ivw + iv.z);
+      const ulonglong2* pv = reinterpret_cast<const ulonglong2*>(ex + iv.x);
+      c32 d0 = pk(0.f, 0.f), u0 = d0, d1 = d0, u1 = d0;   // {frame 2q, frame 2q+1}; even / odd bins apart
+#pragma unroll
+      for (int j = 0; j < kPartBins / 2; ++j) {      // every part has kPartBins bins (zero weights pad it)
+        const ulonglong2 w = wv[j];
+        const ulonglong2 p = pv[j];
+        d0 = fma2(bc(lo_of(w.x)), p.x, d0);
+        u0 = fma2(bc(hi_of(w.x)), p.x, u0);
+        d1 = fma2(bc(lo_of(w.y)), p.y, d1);
+        u1 = fma2(bc(hi_of(w.y)), p.y, u1);
+      }
+      if (iv.w >= 0) {                               // parts of one interval sit in different slots: fixed order
+        ulonglong2* tot = reinterpret_cast<ulonglong2*>(scratch) + (iv.w & 0xffff);
+        c32 sd = add2(d0, d1), su = add2(u0, u1);
+        if (!(iv.w >> 16)) { const ulonglong2 o = *tot; sd = add2(o.x, sd); su = add2(o.y, su); }
+        *tot = make_ulonglong2(sd, su);
+      }
+      __syncwarp();
+    }
 
-    // ---- sparse filterbank + log: thread = (band, frame pair); 32 bands per pass
-    const int fp = tid & 7;                         // frame pair = the warp that produced it
-    const int fseg = fp >= n0 ? 1 : 0;
-    const int ta = 2 * (fseg ? fp - n0 : seg[0].q0 + fp);
-    const int fclip = seg[0].clip + fseg;
-    const bool fhave = fp < np && ta < a.T;
-    const bool fhave2 = fhave && ta + 1 < a.T;
-    const float2* pw = s_ex + fp * kExWarp;
-    float* out = a.lms + ring_slot(a.slot0, fclip, a.cap) * (static_cast<long long>(a.n_mels) * a.T) + ta;
+    // ---- bands: add the two edges, fold eps and gain, log, store, statistics
+    const int ta = 2 * wpair;
+    const int clip = seg[0].clip + wseg;
+    const bool two = ta + 1 < a.T;                   // the last pair of an odd-length clip has one frame
+    long long slot = a.slot0 + clip;
+    if (a.cap > 0 && slot >= a.cap) slot -= a.cap;
+    float* out = a.lms + slot * (static_cast<long long>(a.n_mels) * a.T) + ta;
     float g2 = 1.f;
-    if (a.gain && fhave) { const float g = a.gain[fclip]; g2 = g * g; }   // |g x|^2 = g^2 |x|^2: per-clip gain applied here
+    if (a.gain) { const float g = a.gain[clip]; g2 = g * g; }   // |g x|^2 = g^2 |x|^2: per-clip gain applied here
     float s1 = 0.f, s2 = 0.f;
-    for (int mb = 0, pass = 0; mb < a.n_mels; mb += 32, ++pass) {
-      // odd passes walk their 32 bands backwards so wide and narrow bands share a warp's time
-      const int m = (pass & 1) ? mb + 31 - (tid >> 3) : mb + (tid >> 3);
-      if (m < a.n_mels && fhave) {
-        const int cnt = s_mcnt[m];
-        const float* wgt = s_mw + s_moff[m];
-        const float2* pk = pw + s_mk0[m];
-        float acc0 = 0.f, acc1 = 0.f;
-#pragma unroll 4
-        for (int j = 0; j < cnt; ++j) {
-          const float w = wgt[j];
-          const float2 p = pk[j];
-          acc0 = fmaf(w, p.x, acc0);
-          acc1 = fmaf(w, p.y, acc1);
-        }
-        const float c = s_mconst[m];
-        acc0 = fmaf(acc0, g2, c);
-        acc1 = fmaf(acc1, g2, c);
-        const float l0 = a.out_kind ? acc0 : __logf(acc0 + kLogEps);
-        const float l1 = a.out_kind ? acc1 : __logf(acc1 + kLogEps);
-        float* o = out + m * a.T;
-        o[0] = l0;
-        s1 += l0; s2 = fmaf(l0, l0, s2);
-        if (fhave2) { o[1] = l1; s1 += l1; s2 = fmaf(l1, l1, s2); }
+    for (int m = lane; m < a.n_mels; m += 32) {
+      const c32 su = scratch[2 * s_pos[m] + 1], sd = scratch[2 * s_pos[m + 1]];   // rising edge + falling edge
+      float acc0, acc1;
+      upk(add2(su, sd), acc0, acc1);
+      const float c = s_mconst[m];
+      acc0 = fmaf(acc0, g2, c);
+      acc1 = fmaf(acc1, g2, c);
+      const float l0 = a.out_kind ? acc0 : __logf(acc0 + kLogEps);
+      const float l1 = a.out_kind ? acc1 : __logf(acc1 + kLogEps);
+      float* dst = out + m * a.T;
+      dst[0] = l0;
+      s1 += l0; s2 = fmaf(l0, l0, s2);
+      if (two) { dst[1] = l1; s1 += l1; s2 = fmaf(l1, l1, s2); }
+    }
+    if (a.tile_sums) {                               // per frame pair (sum, sum^2), fixed butterfly order
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
       }
+      if (lane == 0) s_red[(it & 1) * kWarps + warp] = make_float2(s1, s2);
     }
-    mbar_arrive(bar_mel);                          // this thread no longer reads the power buffers
-    if (a.tile_sums) {                             // per (warp, frame pair) partial sums; lanes with equal fp combine
-      s1 += __shfl_xor_sync(0xffffffffu, s1, 8);  s2 += __shfl_xor_sync(0xffffffffu, s2, 8);
-      s1 += __shfl_xor_sync(0xffffffffu, s1, 16); s2 += __shfl_xor_sync(0xffffffffu, s2, 16);
-      if (lane < kWarps) s_red[((it & 1) * kWarps + warp) * kWarps + lane] = make_float2(s1, s2);
-    }
-    prev_tile = tile;
   }
   __syncthreads();
   if (a.tile_sums && warp == 0 && prev_tile >= 0) flush_stats(prev_tile, (it - 1) & 1);
@@ -436,12 +510,21 @@ extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const floa
   a.total_tiles = a.straddle ? static_cast<int>((total_pairs + kWarps - 1) / kWarps) : static_cast<int>(B);
   // two spans per tile at most: (16 - 2) hops + 2 windows, each span start rounded to 4 floats
   a.wave_floats = 2 * kWarps * p->cfg.hop + 2 * kNfft + 8;
-  a.nnz = p->nnz; a.out_kind = out_kind;
+  a.n_iw = p->n_iw; a.n_slots = p->n_slots; a.out_kind = out_kind;
+  {   // n / ppc by multiply-high (Granlund-Montgomery, exact for every 32-bit n)
+    const unsigned d = static_cast<unsigned>(a.ppc);
+    int l = 0;
+    while ((1ull << l) < d) ++l;
+    a.ppc_mul = static_cast<unsigned>(((1ull << 32) * ((1ull << l) - d)) / d + 1);
+    a.ppc_sh1 = l < 1 ? l : 1;
+    a.ppc_sh2 = l > 1 ? l - 1 : 0;
+  }
   // the bulk (TMA) copy needs 16-byte aligned global addresses: clip starts and span starts (2*q*hop - 512)
   a.bulk_ok = (reinterpret_cast<uintptr_t>(wave) % 16 == 0) && (ld % 4 == 0) && (p->cfg.hop % 2 == 0);
-  a.win = p->d_win_half; a.tw = p->d_twiddle;
-  a.mk0 = p->d_mel_k0; a.mcnt = p->d_mel_cnt; a.moff = p->d_mel_off; a.mw = p->d_mel_w; a.mconst = p->d_mel_const;
-  const size_t smem = logmel_smem_bytes(a.wave_floats, a.nnz);
+  a.tw = p->d_twiddle;
+  a.iv_w = p->d_iv_w;
+  a.lane_iv = p->d_lane_iv; a.iv_pos = p->d_iv_pos; a.mconst = p->d_mel_const;
+  const size_t smem = logmel_smem_bytes(a.wave_floats, a.n_iw);
   if (smem > 227 * 1024) return ASSL_ERR_UNSUPPORTED;
   // parts of tile_sums no tile writes (a clip touches at most n_parts tiles, usually fewer) must read as zero
   if (tile_sums && cudaMemsetAsync(tile_sums, 0, sizeof(double) * 2 * B * a.n_parts, as_stream(stream)) != cudaSuccess)

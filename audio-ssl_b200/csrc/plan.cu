@@ -1,5 +1,6 @@
 // Plan construction: the host-side restatement of librosa.filters.mel as the reference calls it
 // (/root/reference/src/utils/utils.py:24) plus the window / twiddle tables of the FFT kernel.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <new>
@@ -94,30 +95,154 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
       p->h_fb[static_cast<size_t>(m) * n_bins + k] = static_cast<float>(static_cast<double>(w32) * enorm);
     }
   }
-  // sparse form: each band's support is one contiguous run of bins
-  std::vector<int> k0(n_mels), cnt(n_mels), off(n_mels);
-  std::vector<float> w;
-  for (int m = 0; m < n_mels; ++m) {
+  // sparse "interval" form.  Interval j (0..n_mels) = bins with centre(j-1) < f_k <= centre(j); a bin there
+  // has weight only in band j-1 (falling edge, .x) and band j (rising edge, .y).  Each interval keeps a private
+  // weight run trimmed to its non-zero bins and widened with zero weights to an even first bin and an even
+  // length, so the kernel reads two bins and two weight pairs per 128-bit load; a run may then end on index
+  // 513, one past Nyquist, which the kernel keeps at zero power.
+  const int n_iv = n_mels + 1;
+  std::vector<int> bin_iv(n_bins);
+  for (int k = 0; k < n_bins; ++k) {
+    const double fk = linspace_at(0.0, sr / 2, n_bins, k);
+    int j = 0;
+    while (j < n_mels && fk > mel_f[j + 1]) ++j;
+    bin_iv[k] = j;
+    for (int m = 0; m < n_mels; ++m)     // the triangles must overlap only with their neighbours
+      if (m != j && m != j - 1 && p->h_fb[static_cast<size_t>(m) * n_bins + k] != 0.f) { delete p; return ASSL_ERR_UNSUPPORTED; }
+  }
+  std::vector<int> k0(n_iv, 0), cnt(n_iv, 0), off(n_iv, 0);
+  std::vector<float2> w;
+  for (int j = 0; j < n_iv; ++j) {
+    auto wd = [&](int k) { return j >= 1 ? p->h_fb[static_cast<size_t>(j - 1) * n_bins + k] : 0.f; };
+    auto wu = [&](int k) { return j < n_mels ? p->h_fb[static_cast<size_t>(j) * n_bins + k] : 0.f; };
     int lo = n_bins, hi = -1;
     for (int k = 0; k < n_bins; ++k)
-      if (p->h_fb[static_cast<size_t>(m) * n_bins + k] != 0.f) { lo = lo < k ? lo : k; hi = k; }
-    k0[m] = hi >= 0 ? lo : 0;
-    cnt[m] = hi >= 0 ? hi - lo + 1 : 0;
-    off[m] = static_cast<int>(w.size());
-    for (int k = 0; k < cnt[m]; ++k) w.push_back(p->h_fb[static_cast<size_t>(m) * n_bins + k0[m] + k]);
+      if (bin_iv[k] == j && (wd(k) != 0.f || wu(k) != 0.f)) { lo = lo < k ? lo : k; hi = k; }
+    if (hi < 0) { off[j] = static_cast<int>(w.size()); continue; }
+    const int first = lo & ~1;
+    int n = hi - first + 1;
+    n = (n + assl::kPartBins - 1) / assl::kPartBins * assl::kPartBins;   // whole parts, see below
+    k0[j] = first;
+    cnt[j] = n;
+    // a lane reads 16 bytes of power (bins k0 + 2i, k0 + 2i + 1) and 16 bytes of weights per step: start the
+    // weight run in the same 16-byte bank group (mod 128 bytes) as the power run, so lanes whose power reads
+    // do not collide do not collide on the weights either
+    while (((w.size() / 2) & 7) != ((static_cast<size_t>(first) / 2) & 7)) { w.push_back(make_float2(0.f, 0.f)); w.push_back(make_float2(0.f, 0.f)); }
+    off[j] = static_cast<int>(w.size());
+    for (int k = first; k < first + n; ++k) {
+      const bool in = k < n_bins && bin_iv[k] == j;
+      w.push_back(in ? make_float2(wd(k), wu(k)) : make_float2(0.f, 0.f));
+    }
+  }
+  // Lanes of the log-mel kernel own pieces of intervals for the whole launch.  Every interval is cut into
+  // parts of exactly kPartBins bins (its weight run is zero-padded to whole parts), so all lanes run the
+  // same straight-line code; a lane owns one part per slot.  Two parts of one interval never share a slot:
+  // their sums are added to the interval's total slot after slot, in a fixed order.  A 128-bit shared load
+  // is served a quarter-warp at a time, conflict-free when its eight 16-byte accesses fall in eight different
+  // bank groups: parts are dealt to the quarter-warps round-robin in order of bank group, so a quarter sees
+  // a group twice only when more parts share it than there are quarters.
+  {
+    struct Part { int k0, off, iv; };
+    std::vector<Part> parts;
+    const int zero_off = static_cast<int>(w.size());           // a zero weight run for idle lanes
+    for (int i = 0; i < assl::kPartBins; ++i) w.push_back(make_float2(0.f, 0.f));
+    for (int j = 0; j < n_iv; ++j)
+      for (int c = 0; c < (cnt[j] > 0 ? cnt[j] : 1); c += assl::kPartBins)
+        parts.push_back({cnt[j] > 0 ? k0[j] + c : 0, cnt[j] > 0 ? off[j] + c : zero_off, j});
+    const int n_slots = (static_cast<int>(parts.size()) + 31) / 32;
+    if (n_slots > assl::kIvSlots) { delete p; return ASSL_ERR_UNSUPPORTED; }
+    while (static_cast<int>(parts.size()) < 32 * n_slots) parts.push_back({0, zero_off, -1});
+    auto group = [](const Part& x) { return (x.k0 / 2) & 7; };
+    std::stable_sort(parts.begin(), parts.end(), [&](const Part& x, const Part& y) { return group(x) < group(y); });
+    const int n_q = 4 * n_slots;                                 // quarter-warps over all slots
+    std::vector<std::vector<Part>> quarter(n_q);
+    for (size_t i = 0; i < parts.size(); ++i) quarter[i % n_q].push_back(parts[i]);   // 8 each
+    auto slot_of = [&](int q) { return q % n_slots; };
+    // repair: two parts of one interval in one slot -> swap one with a part of the same bank group elsewhere
+    for (int pass = 0; pass < 64; ++pass) {
+      bool clash = false;
+      for (int q = 0; q < n_q; ++q)
+        for (size_t i = 0; i < quarter[q].size(); ++i) {
+          const Part x = quarter[q][i];
+          if (x.iv < 0) continue;
+          auto in_slot = [&](int sl, int iv, int skip_q, size_t skip_i) {
+            for (int r = 0; r < n_q; ++r)
+              if (slot_of(r) == sl)
+                for (size_t t = 0; t < quarter[r].size(); ++t)
+                  if (!(r == skip_q && t == skip_i) && quarter[r][t].iv == iv) return true;
+            return false;
+          };
+          if (!in_slot(slot_of(q), x.iv, q, i)) continue;
+          clash = true;
+          bool done = false;
+          for (int r = 0; r < n_q && !done; ++r) {
+            if (slot_of(r) == slot_of(q)) continue;
+            for (size_t t = 0; t < quarter[r].size() && !done; ++t) {
+              const Part y = quarter[r][t];
+              if (group(y) != group(x)) continue;
+              if (in_slot(slot_of(r), x.iv, r, t)) continue;                    // x would clash there
+              if (y.iv >= 0 && in_slot(slot_of(q), y.iv, q, i)) continue;      // y would clash here
+              quarter[q][i] = y; quarter[r][t] = x; done = true;
+            }
+          }
+        }
+      if (!clash) break;
+      if (pass == 63) { delete p; return ASSL_ERR_UNSUPPORTED; }
+    }
+    std::vector<int> first_slot(n_iv, 1 << 30);
+    for (int q = 0; q < n_q; ++q)
+      for (const Part& x : quarter[q])
+        if (x.iv >= 0 && slot_of(q) < first_slot[x.iv]) first_slot[x.iv] = slot_of(q);
+    // where an interval's running total lives in the warp's scratch (16-byte entries): a quarter-warp's eight
+    // read-modify-writes are conflict-free when their entries differ mod 8, so intervals get one of 8 colours,
+    // greedily, least clashes with the intervals they share a quarter with first
+    std::vector<int> colour(n_iv, -1), pos(n_iv, 0);
+    {
+      std::vector<std::vector<int>> mates(n_iv);
+      for (int q = 0; q < n_q; ++q)
+        for (const Part& x : quarter[q])
+          for (const Part& y : quarter[q])
+            if (x.iv >= 0 && y.iv >= 0 && x.iv != y.iv) mates[x.iv].push_back(y.iv);
+      std::vector<int> by_deg(n_iv);
+      for (int j = 0; j < n_iv; ++j) by_deg[j] = j;
+      std::stable_sort(by_deg.begin(), by_deg.end(), [&](int x, int y) { return mates[x].size() > mates[y].size(); });
+      int used_per_colour[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      for (int j : by_deg) {
+        int clash[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int m : mates[j]) if (colour[m] >= 0) ++clash[colour[m]];
+        int best = 0;
+        for (int c = 1; c < 8; ++c)
+          if (clash[c] < clash[best] || (clash[c] == clash[best] && used_per_colour[c] < used_per_colour[best])) best = c;
+        colour[j] = best;
+        pos[j] = best + 8 * used_per_colour[best]++;
+      }
+    }
+    int n_pos = 0;
+    for (int j = 0; j < n_iv; ++j) n_pos = n_pos > pos[j] + 1 ? n_pos : pos[j] + 1;
+    if (n_pos > assl::kScratchEntries) { delete p; return ASSL_ERR_UNSUPPORTED; }
+    std::vector<int4> lane_iv(static_cast<size_t>(32) * assl::kIvSlots, make_int4(0, 0, zero_off, -1));
+    for (int q = 0; q < n_q; ++q)
+      for (size_t i = 0; i < quarter[q].size(); ++i) {
+        const Part& x = quarter[q][i];
+        const int sl = slot_of(q), lane = (q / n_slots) * 8 + static_cast<int>(i);
+        const int tag = x.iv < 0 ? -1 : (pos[x.iv] | ((first_slot[x.iv] == sl ? 1 : 0) << 16));   // bit 16: starts the total
+        lane_iv[static_cast<size_t>(sl) * 32 + lane] = make_int4(x.k0, assl::kPartBins / 2, x.off, tag);
+      }
+    p->h_iv_pos = pos;
+    p->n_slots = n_slots;
+    p->h_lane_iv = lane_iv;
   }
   std::vector<float> mconst(n_mels);
   for (int m = 0; m < n_mels; ++m) {
     float acc = 0.f;
-    for (int k = 0; k < cnt[m]; ++k) acc += w[off[m] + k] * assl::kPowerEps;
+    for (int k = 0; k < n_bins; ++k) acc += p->h_fb[static_cast<size_t>(m) * n_bins + k] * assl::kPowerEps;
     mconst[m] = acc;
   }
-  if (w.empty()) w.push_back(0.f);
-  p->nnz = static_cast<int>(w.size());
+  if (w.empty()) w.push_back(make_float2(0.f, 0.f));
+  p->n_iw = static_cast<int>(w.size());
 
-  // ---- window (scipy get_window('hann', fftbins=True), fp64 -> fp32) with the unpack's 1/2 folded in
-  std::vector<float> win(n_fft);
-  for (int n = 0; n < n_fft; ++n) win[n] = static_cast<float>(0.5 * (0.5 - 0.5 * std::cos(2.0 * kPi * n / n_fft)));
+  // ---- window: scipy get_window('hann', fftbins=True) = 0.5 - 0.5 cos(2 pi n / n_fft) needs no table; the
+  //      kernel evaluates it (times the 1/2 of the two-frame unpack) from one sin/cos pair per lane
   // ---- inter-stage twiddles of the 32 x 32 decomposition
   std::vector<float2> tw(32 * 32);
   for (int k2 = 0; k2 < 32; ++k2)
@@ -126,12 +251,10 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
       tw[k2 * 32 + n1] = make_float2(static_cast<float>(std::cos(ang)), static_cast<float>(std::sin(ang)));
     }
 
-  int rc = upload(&p->d_win_half, win);
-  if (rc == ASSL_OK) rc = upload(&p->d_twiddle, tw);
-  if (rc == ASSL_OK) rc = upload(&p->d_mel_k0, k0);
-  if (rc == ASSL_OK) rc = upload(&p->d_mel_cnt, cnt);
-  if (rc == ASSL_OK) rc = upload(&p->d_mel_off, off);
-  if (rc == ASSL_OK) rc = upload(&p->d_mel_w, w);
+  int rc = upload(&p->d_twiddle, tw);
+  if (rc == ASSL_OK) rc = upload(&p->d_iv_w, w);
+  if (rc == ASSL_OK) rc = upload(&p->d_lane_iv, p->h_lane_iv);
+  if (rc == ASSL_OK) rc = upload(&p->d_iv_pos, p->h_iv_pos);
   if (rc == ASSL_OK) rc = upload(&p->d_mel_const, mconst);
   if (rc != ASSL_OK) { assl_plan_destroy(p); return rc; }
   *out = p;
@@ -140,12 +263,10 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
 
 extern "C" int assl_plan_destroy(assl_plan* p) {
   if (!p) return ASSL_OK;
-  cudaFree(p->d_win_half);
   cudaFree(p->d_twiddle);
-  cudaFree(p->d_mel_k0);
-  cudaFree(p->d_mel_cnt);
-  cudaFree(p->d_mel_off);
-  cudaFree(p->d_mel_w);
+  cudaFree(p->d_iv_w);
+  cudaFree(p->d_lane_iv);
+  cudaFree(p->d_iv_pos);
   cudaFree(p->d_mel_const);
   if (p->aux_ready) {
     cudaStreamDestroy(p->s_in); cudaStreamDestroy(p->s_out);
