@@ -68,19 +68,20 @@ __device__ __forceinline__ void tap_weights(float t, int bilinear, float w[4]) {
   }
 }
 
-__host__ __device__ inline size_t views_smem_bytes(int canvas_h, int src_w, int tw, int n_freq) {
-  return sizeof(float) * (static_cast<size_t>(canvas_h) * src_w + static_cast<size_t>(canvas_h) * tw) +
+__host__ __device__ inline size_t views_smem_bytes(int canvas_h, int src_w, int n_freq) {
+  return sizeof(float) * static_cast<size_t>(canvas_h) * src_w +
          (sizeof(float) + sizeof(int)) * 4 * static_cast<size_t>(n_freq);
 }
 
-template <int TW>
-__global__ void __launch_bounds__(kViewThreads, 3) two_views_kernel(const ViewArgs a) {
+// TW = output frames per tile; CG = 32-column groups of the staged crop span a warp loads per row
+template <int TW, int CG>
+__global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int F = a.c.n_freq, T = a.c.n_time;
   float4* s_wy = reinterpret_cast<float4*>(smem_raw);                // [F]         frequency tap weights
   int4* s_ya = reinterpret_cast<int4*>(s_wy + F);                    // [F]         frequency tap rows
-  float* s_src = reinterpret_cast<float*>(s_ya + F);                 // [h][src_w]  mixed crop span
-  float* s_h = s_src + static_cast<size_t>(a.c.canvas_h) * a.src_w;  // [h][TW]     time-resampled rows
+  float* s_src = reinterpret_cast<float*>(s_ya + F);                 // [h][src_w]  mixed crop span, then (in place,
+                                                                     //             row by row) the time-resampled rows
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   long long blk = blockIdx.x;
@@ -140,7 +141,7 @@ __global__ void __launch_bounds__(kViewThreads, 3) two_views_kernel(const ViewAr
     // Rows are taken kRowBatch at a time per warp and ALL their global loads are issued before any
     // arithmetic, so a warp keeps 2 * kRowBatch * ceil(nsx/32) loads in flight instead of 2.
     constexpr int kRowBatch = 2;
-    constexpr int kColGroups = (TW * 3 / 2 + 16 + 31) / 32;     // covers span() for virtual_crop_scale <= 1.5
+    constexpr int kColGroups = CG;                              // 32 * CG >= src_w - 1 (checked at launch)
     for (int yb = warp * kRowBatch; yb < h; yb += (kViewThreads / 32) * kRowBatch) {
       float xv[kRowBatch][kColGroups], zv[kRowBatch][kColGroups];
 #pragma unroll
@@ -203,19 +204,20 @@ __global__ void __launch_bounds__(kViewThreads, 3) two_views_kernel(const ViewAr
 #pragma unroll
       for (int q = 0; q < 4; ++q) xi[c][q] = min(max(min(max(ix - 1 + q, 0), w - 1) - xs_lo, 0), nsx - 1);
     }
-    for (int y = warp; y < h; y += kViewThreads / 32) {
-      const float* row = s_src + y * a.src_w;
-      float* hrow = s_h + y * TW + lane;
+    for (int y = warp; y < h; y += kViewThreads / 32) {      // a warp owns the row: read every tap, then overwrite
+      float* row = s_src + y * a.src_w;
+      float acc[NC];
 #pragma unroll
       for (int c = 0; c < NC; ++c) {
-        if (32 * c < ncol) {                                   // warp-uniform
-          float acc = row[xi[c][0]] * wt[c][0];
-          acc = fmaf(row[xi[c][1]], wt[c][1], acc);
-          acc = fmaf(row[xi[c][2]], wt[c][2], acc);
-          acc = fmaf(row[xi[c][3]], wt[c][3], acc);
-          hrow[32 * c] = acc;
-        }
+        acc[c] = row[xi[c][0]] * wt[c][0];
+        acc[c] = fmaf(row[xi[c][1]], wt[c][1], acc[c]);
+        acc[c] = fmaf(row[xi[c][2]], wt[c][2], acc[c]);
+        acc[c] = fmaf(row[xi[c][3]], wt[c][3], acc[c]);
       }
+      __syncwarp();
+#pragma unroll
+      for (int c = 0; c < NC; ++c)
+        if (lane + 32 * c < ncol) row[lane + 32 * c] = acc[c];
     }
   }
   __syncthreads();
@@ -226,10 +228,10 @@ __global__ void __launch_bounds__(kViewThreads, 3) two_views_kernel(const ViewAr
     for (int oy = warp; oy < F; oy += kViewThreads / 32) {
       const float4 wy = s_wy[oy];
       const int4 ya = s_ya[oy];
-      const float* r0 = s_h + ya.x * TW + lane;
-      const float* r1 = s_h + ya.y * TW + lane;
-      const float* r2 = s_h + ya.z * TW + lane;
-      const float* r3 = s_h + ya.w * TW + lane;
+      const float* r0 = s_src + ya.x * a.src_w + lane;
+      const float* r1 = s_src + ya.y * a.src_w + lane;
+      const float* r2 = s_src + ya.z * a.src_w + lane;
+      const float* r3 = s_src + ya.w * a.src_w + lane;
       float* orow = outp + static_cast<long long>(oy) * T;
 #pragma unroll
       for (int c = 0; c < NC; ++c) {
@@ -245,19 +247,28 @@ __global__ void __launch_bounds__(kViewThreads, 3) two_views_kernel(const ViewAr
   }
 }
 
-template <int TW>
-int launch_views(ViewArgs& a, cudaStream_t st) {
-  a.tiles_t = (a.c.n_time + TW - 1) / TW;
-  constexpr int kColGroups = (TW * 3 / 2 + 16 + 31) / 32;       // must match stage A of the kernel
-  if (a.src_w - 1 > 32 * kColGroups) return ASSL_ERR_UNSUPPORTED;   // virtual_crop_scale[1] well above 1.5
-  const size_t smem = views_smem_bytes(a.c.canvas_h, a.src_w, TW, a.c.n_freq);
+template <int TW, int CG>
+int launch_views_cg(ViewArgs& a, cudaStream_t st) {
+  const size_t smem = views_smem_bytes(a.c.canvas_h, a.src_w, a.c.n_freq);
   if (smem > 227 * 1024) return ASSL_ERR_UNSUPPORTED;
-  if (cudaFuncSetAttribute(two_views_kernel<TW>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
+  if (cudaFuncSetAttribute(two_views_kernel<TW, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
     return ASSL_ERR_CUDA;
   const long long grid = a.B * 2 * a.tiles_t;
   if (grid > 0x7fffffffll) return ASSL_ERR_UNSUPPORTED;
-  two_views_kernel<TW><<<static_cast<unsigned>(grid), kViewThreads, smem, st>>>(a);
+  two_views_kernel<TW, CG><<<static_cast<unsigned>(grid), kViewThreads, smem, st>>>(a);
   return launch_status();
+}
+
+template <int TW>
+int launch_views(ViewArgs& a, cudaStream_t st) {
+  a.tiles_t = (a.c.n_time + TW - 1) / TW;
+  if (a.src_w < (a.c.n_time < TW ? a.c.n_time : TW)) return ASSL_ERR_UNSUPPORTED;   // rows are reused for the outputs
+  constexpr int kMaxCG = (TW * 3 / 2 + 16 + 31) / 32;            // covers span() for virtual_crop_scale <= 1.5
+  const int need = (a.src_w - 1 + 31) / 32;                      // stage A loads 32 columns per group
+  if (need > kMaxCG) return ASSL_ERR_UNSUPPORTED;                 // virtual_crop_scale[1] well above 1.5
+  if (need <= kMaxCG - 2) return launch_views_cg<TW, (kMaxCG - 2 > 0 ? kMaxCG - 2 : 1)>(a, st);
+  if (need <= kMaxCG - 1) return launch_views_cg<TW, kMaxCG - 1>(a, st);
+  return launch_views_cg<TW, kMaxCG>(a, st);
 }
 
 }  // namespace assl
