@@ -9,7 +9,8 @@ from . import _native
 from .augmentations import (MixupBYOLA, NormalizeBatch, PrecomputedNorm, RandomResizeCrop,  # noqa: F401
                             RunningNorm)
 from .engine import ViewEngine, shard_bounds  # noqa: F401
-from .frontend import MelSpectrogramLibrosa, Plan, extract_log_mel_spectrogram  # noqa: F401
+from .frontend import (MelSpectrogramLibrosa, Plan, extract_log_mel_spectrogram, extract_window,  # noqa: F401
+                       extract_windows)
 from .module import AugmentationModule, UpstreamInputPipeline  # noqa: F401
 from .sampler import FastSampler, ReferenceSampler, ViewParams  # noqa: F401
 

@@ -123,3 +123,49 @@ def extract_log_mel_spectrogram(waveform, to_mel_spec):
     if not isinstance(to_mel_spec, MelSpectrogramLibrosa):
         raise TypeError("to_mel_spec must be audiossl_b200.MelSpectrogramLibrosa")
     return to_mel_spec.log_mel(waveform)
+
+
+def extract_windows(waves, unit_length, starts=None, with_gain=False, device=None):
+    """Batched ``extract_window`` (utils.py:166-182) on the GPU.
+
+    waves: a sequence of 1-D waveforms of any lengths (tensors or arrays).  Clips shorter than
+    ``unit_length`` are centre zero-padded, longer ones cropped at ``starts[b]`` (the reference draws it
+    with ``random.randint(0, len - unit_length)``; None = 0).  Returns ``[B, unit_length]`` fp32 on the
+    GPU and, with ``with_gain``, also ``1 / max(||window||_2, 1e-12)`` per clip -- the reduction of
+    ``F.normalize(p=2)`` (upstream_dataset.py:62-63) from the same pass, to be handed to the log-mel kernel.
+    """
+    if not torch.cuda.is_available():
+        raise RuntimeError("audiossl_b200 needs a CUDA device: the CUDA kernels are the only implementation")
+    unit_length = int(unit_length)
+    ws = [w if isinstance(w, torch.Tensor) else torch.as_tensor(np.asarray(w)) for w in waves]
+    if any(w.dim() != 1 for w in ws):
+        raise ValueError("extract_windows takes 1-D waveforms")
+    if device is None:
+        device = next((w.device for w in ws if w.is_cuda), torch.device("cuda", torch.cuda.current_device()))
+    lengths = np.array([w.shape[0] for w in ws], np.int64)
+    offsets = np.concatenate(([0], np.cumsum(lengths)[:-1])).astype(np.int64) if len(ws) else np.zeros(0, np.int64)
+    b = len(ws)
+    with torch.cuda.device(device):
+        raw = torch.cat([w.to(device=device, dtype=torch.float32, non_blocking=True) for w in ws]) if b else \
+            torch.empty(0, dtype=torch.float32, device=device)
+        if raw.numel() == 0:
+            raw = torch.zeros(1, dtype=torch.float32, device=device)
+        meta = np.stack([offsets, lengths, np.zeros(b, np.int64) if starts is None else np.asarray(starts, np.int64)])
+        meta_d = torch.from_numpy(meta).to(device)
+        out = torch.empty((b, unit_length), dtype=torch.float32, device=device)
+        gain = torch.empty(b, dtype=torch.float32, device=device) if with_gain else None
+        _native.check(_native.lib().assl_extract_windows_f32(
+            _ptr(raw), _ptr(meta_d[0]), _ptr(meta_d[1]), _ptr(meta_d[2]), b, unit_length, _ptr(out), unit_length,
+            _ptr(gain), _stream_ptr()), "assl_extract_windows_f32")
+    return (out, gain) if with_gain else out
+
+
+def extract_window(wav, duration=16000, data_size=None, start=None):
+    """utils.py:166-182 for one clip, same arguments; the crop offset comes from python's ``random`` like the
+    reference's unless ``start`` is given."""
+    import random
+    unit_length = int(data_size * 16000) if data_size else int(duration)
+    adj = int(wav.shape[0]) - unit_length
+    if start is None:
+        start = random.randint(0, adj) if adj > 0 else 0
+    return extract_windows([wav], unit_length, starts=[start])[0]

@@ -98,20 +98,29 @@ class AugmentationModule:
 class UpstreamInputPipeline:
     """Waveforms in, two augmented views out, everything on the GPU:
 
-        log-mel (fused kernel, written straight into the bank ring, per-tile sums on the side)
+        [extract_window + L2 gain, one pass, for raw clips of any length]
+        -> log-mel (fused kernel, written straight into the bank ring, per-tile sums on the side)
         -> running-statistics scan -> two-view kernel.
 
-    This is the batched equivalent of ``BaseDataset.__getitem__`` lines :62-65, :82, :86
-    (/root/reference/src/dataset/upstream_dataset.py) for a whole batch.
+    This is the batched equivalent of ``BaseDataset.__getitem__`` lines :60-65, :82, :86
+    (/root/reference/src/dataset/upstream_dataset.py) for a whole batch.  Call it with a ``[B, L]`` batch
+    of equal-length windows, or with a list of raw 1-D clips of different lengths: those go through
+    ``extract_window`` first (``config["pretrain"]["input"]["length_wave"]`` seconds, or ``unit_length``
+    samples), their crop offsets drawn by the sampler in the reference's order.
     """
 
-    def __init__(self, config, len_of_files, *, to_mel_spec=None, **kw):
+    def __init__(self, config, len_of_files, *, to_mel_spec=None, unit_length=None, **kw):
         self.tfms = AugmentationModule(config, len_of_files, **kw)
         self.plan = to_mel_spec.plan if to_mel_spec is not None else Plan()
         self.l2 = config["pretrain"].get("normalization") == "l2"
+        length_wave = config["pretrain"].get("input", {}).get("length_wave")
+        self.unit_length = int(unit_length) if unit_length is not None else \
+            (int(length_wave * 16000) if length_wave else None)          # utils.py:168-169
         self.last_lms = None
 
     def __call__(self, waveforms, params: ViewParams = None):
+        if isinstance(waveforms, (list, tuple)):
+            return self._ragged(list(waveforms), params)
         wave = as_cuda_f32(waveforms)
         if wave.dim() == 1:
             wave = wave.unsqueeze(0)
@@ -120,22 +129,53 @@ class UpstreamInputPipeline:
         from .frontend import _ptr, _stream_ptr
         v1s, v2s = [], []
         with torch.cuda.device(wave.device):
-            t = self.plan.num_frames(wave.shape[1])
-            tiles = self.plan.num_tiles(wave.shape[1])
-            eng.ensure(self.plan.n_mels, t, wave.device)
+            eng.ensure(self.plan.n_mels, self.plan.num_frames(wave.shape[1]), wave.device)
             for lo, hi in _chunks(wave.shape[0], eng.max_batch):
                 part = wave[lo:hi]
-                b = hi - lo
                 gain = None
                 if self.l2:
-                    gain = torch.empty(b, dtype=torch.float32, device=wave.device)
-                    _native.check(_native.lib().assl_wave_l2_gain_f32(_ptr(part), b, part.shape[1], part.stride(0),
+                    gain = torch.empty(hi - lo, dtype=torch.float32, device=wave.device)
+                    _native.check(_native.lib().assl_wave_l2_gain_f32(_ptr(part), hi - lo, part.shape[1], part.stride(0),
                                                                       _ptr(gain), _stream_ptr()))
-                sums = torch.empty((b, tiles, 2), dtype=torch.float64, device=wave.device) if tf.pre_norm else None
-                self.plan.logmel_into(part, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain)
-                if tf.pre_norm:
-                    eng.update_stats(sums, tiles)
-                a, c = eng.launch_views(tf._params(params, lo, hi), b, wave.device)
+                a, c = self._windows_to_views(part, gain, lambda lo=lo, hi=hi: tf._params(params, lo, hi))
+                v1s.append(a); v2s.append(c)
+        v1 = v1s[0] if len(v1s) == 1 else torch.cat(v1s)
+        v2 = v2s[0] if len(v2s) == 1 else torch.cat(v2s)
+        return v1, v2
+
+    def _windows_to_views(self, part, gain, draw):
+        """[b, L] windows on the GPU -> log-mel into the ring -> statistics -> two views."""
+        eng, tf = self.tfms.engine, self.tfms
+        b = part.shape[0]
+        tiles = self.plan.num_tiles(part.shape[1])
+        sums = torch.empty((b, tiles, 2), dtype=torch.float64, device=part.device) if tf.pre_norm else None
+        self.plan.logmel_into(part, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain)
+        if tf.pre_norm:
+            eng.update_stats(sums, tiles)
+        return eng.launch_views(draw(), b, part.device)
+
+    def _ragged(self, clips, params):
+        """Raw clips of any length: extract_window (+ L2 gain in the same pass) feeds the front end."""
+        from .frontend import extract_windows
+        if self.unit_length is None:
+            raise ValueError("raw clips need a window length: config['pretrain']['input']['length_wave'] or unit_length=")
+        eng, tf = self.tfms.engine, self.tfms
+        device = next((c.device for c in clips if isinstance(c, torch.Tensor) and c.is_cuda),
+                      torch.device("cuda", torch.cuda.current_device()))
+        v1s, v2s = [], []
+        with torch.cuda.device(device):
+            eng.ensure(self.plan.n_mels, self.plan.num_frames(self.unit_length), device)
+            for lo, hi in _chunks(len(clips), eng.max_batch):
+                adj = np.array([int(c.shape[0]) - self.unit_length for c in clips[lo:hi]], np.int64)
+                if params is None:       # the window offset of a clip is drawn before its view parameters
+                    p = tf.sampler.draw(eng.clips_done, hi - lo, eng.f, eng.t, window_adj=adj)
+                else:
+                    p = ViewParams(params.alpha[lo:hi], params.src_clip[lo:hi], params.bank_index[lo:hi],
+                                   params.crop[lo:hi], None if params.start is None else params.start[lo:hi])
+                tf.last_params = p
+                win = extract_windows(clips[lo:hi], self.unit_length, starts=p.start, with_gain=self.l2, device=device)
+                part, gain = win if self.l2 else (win, None)
+                a, c = self._windows_to_views(part, gain, lambda p=p: p)
                 v1s.append(a); v2s.append(c)
         v1 = v1s[0] if len(v1s) == 1 else torch.cat(v1s)
         v2 = v2s[0] if len(v2s) == 1 else torch.cat(v2s)

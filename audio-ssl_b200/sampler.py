@@ -12,6 +12,10 @@ bit-identical crop boxes and mixup selections:
                random.randint(0, ch - h)     -> i          (:36, skipped when ch == h)
                random.randint(0, cw - w)     -> j          (:37, skipped when cw == w)
 
+When the raw clips go through ``extract_window`` first (BaseDataset.__getitem__, upstream_dataset.py:60),
+its ``random.randint(0, len - unit)`` (utils.py:179, skipped when the clip is not longer than the window)
+comes BEFORE the clip's view draws on the same ``random`` stream; pass ``window_adj`` to ``draw``.
+
 ``FastSampler`` draws the same distributions from a vectorised ``numpy.random.Generator`` (not
 sequence-compatible with the reference; for throughput runs).
 
@@ -34,6 +38,7 @@ class ViewParams:
     src_clip: np.ndarray    # [B, 2] int64   process-local clip id of the bank entry, -1 = no mix
     bank_index: np.ndarray  # [B, 2] int32   index drawn into the FIFO (-1 when it was empty)
     crop: np.ndarray        # [B, 2, 4] int32 (i, j, h, w)
+    start: np.ndarray = None  # [B] int64 extract_window crop offsets, when the sampler drew them
 
 
 def canvas_size(f, t, virtual_crop_scale):
@@ -58,7 +63,8 @@ class ReferenceSampler:
         self.np_rng = np_rng if np_rng is not None else np.random
         self.py_rng = py_rng if py_rng is not None else _pyrandom
 
-    def draw(self, clips_done: int, batch: int, f: int, t: int) -> ViewParams:
+    def draw(self, clips_done: int, batch: int, f: int, t: int, window_adj=None) -> ViewParams:
+        """``window_adj[b]`` = len(clip b) - unit_length: also draw the extract_window offsets, in place."""
         ch, cw = canvas_size(f, t, self.vscale)
         nv = self.pushes_per_clip
         alpha = np.zeros((batch, 2), np.float32)
@@ -67,9 +73,12 @@ class ReferenceSampler:
         crop = np.zeros((batch, 2, 4), np.int32)
         crop[:, :, 2], crop[:, :, 3] = f, t
         crop[:, :, 0], crop[:, :, 1] = (ch - f) // 2, (cw - t) // 2     # identity box when cropping is off
+        start = np.zeros(batch, np.int64) if window_adj is not None else None
         rnd, rint, uni, pint = self.np_rng.random, self.np_rng.randint, self.np_rng.uniform, self.py_rng.randint
         for b in range(batch):
             g = clips_done + b
+            if window_adj is not None and window_adj[b] > 0:
+                start[b] = pint(0, int(window_adj[b]))
             for v in range(nv):
                 if self.mixup:
                     alpha[b, v] = self.ratio * rnd()
@@ -84,7 +93,7 @@ class ReferenceSampler:
                     i = pint(0, ch - h) if ch > h else 0
                     j = pint(0, cw - w) if cw > w else 0
                     crop[b, v] = (i, j, h, w)
-        return ViewParams(alpha, src, bidx, crop)
+        return ViewParams(alpha, src, bidx, crop, start)
 
 
 class FastSampler:
@@ -98,10 +107,14 @@ class FastSampler:
         self.mixup, self.crop = mixup, crop
         self.rng = np.random.default_rng(seed)
 
-    def draw(self, clips_done: int, batch: int, f: int, t: int) -> ViewParams:
+    def draw(self, clips_done: int, batch: int, f: int, t: int, window_adj=None) -> ViewParams:
         ch, cw = canvas_size(f, t, self.vscale)
         nv = self.pushes_per_clip
         rng = self.rng
+        start = None
+        if window_adj is not None:
+            adj = np.maximum(np.asarray(window_adj, np.int64), 0)
+            start = np.minimum(np.floor(rng.random(batch) * (adj + 1)).astype(np.int64), adj)
         alpha = np.zeros((batch, 2), np.float32)
         src = np.full((batch, 2), -1, np.int64)
         bidx = np.full((batch, 2), -1, np.int32)
@@ -123,7 +136,7 @@ class FastSampler:
             j = np.floor(rng.random((batch, 2)) * (cw - w + 1)).astype(np.int64)
             crop[:, :, 0], crop[:, :, 1] = np.minimum(i, ch - h), np.minimum(j, cw - w)
             crop[:, :, 2], crop[:, :, 3] = h, w
-        return ViewParams(alpha, src, bidx, crop)
+        return ViewParams(alpha, src, bidx, crop, start)
 
 
 def validate_crops(crop: np.ndarray, ch: int, cw: int) -> None:

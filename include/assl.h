@@ -98,6 +98,18 @@ int assl_logmel_f32(const assl_plan* plan, const float* wave, const float* wave_
 int assl_wave_l2_gain_f32(const float* wave, int64_t B, int64_t L, int64_t ld, float* gain,
                           void* stream);
 
+/* -- waveform window (the step before the front end) ---------------------------------------
+ * Replaces extract_window (src/utils/utils.py:166-182) for B raw clips of different lengths stored
+ * back to back in ``raw``: clip b = raw[offsets[b] .. offsets[b] + lengths[b]).  A clip shorter than
+ * unit_length is zero-padded, (unit_length - len) // 2 samples on the left; a longer one is cropped
+ * at starts[b], the value the reference draws with random.randint(0, len - unit_length)
+ * (starts == NULL: 0).  out [B, ld] fp32 receives the windows.  gain, when not NULL, receives
+ * 1 / max(||window_b||_2, 1e-12) -- the reduction of F.normalize(p=2)
+ * (src/dataset/upstream_dataset.py:62-63) in the same pass; hand it to assl_logmel_f32. */
+int assl_extract_windows_f32(const float* raw, const int64_t* offsets, const int64_t* lengths,
+                             const int64_t* starts, int64_t B, int64_t unit_length, float* out,
+                             int64_t ld, float* gain, void* stream);
+
 /* -- running pre-normalisation -------------------------------------------------------------
  * Replaces RunningMean.put / RunningVariance.put / RunningNorm.forward's statistics update
  * (src/augmentations/augmentations.py:222-228, 249-256, 275-281), including the divisor that
