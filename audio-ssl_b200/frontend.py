@@ -143,11 +143,23 @@ def extract_windows(waves, unit_length, starts=None, with_gain=False, device=Non
     if device is None:
         device = next((w.device for w in ws if w.is_cuda), torch.device("cuda", torch.cuda.current_device()))
     lengths = np.array([w.shape[0] for w in ws], np.int64)
-    offsets = np.concatenate(([0], np.cumsum(lengths)[:-1])).astype(np.int64) if len(ws) else np.zeros(0, np.int64)
-    b = len(ws)
     with torch.cuda.device(device):
-        raw = torch.cat([w.to(device=device, dtype=torch.float32, non_blocking=True) for w in ws]) if b else \
+        raw = torch.cat([w.to(device=device, dtype=torch.float32, non_blocking=True) for w in ws]) if ws else \
             torch.empty(0, dtype=torch.float32, device=device)
+    return extract_windows_packed(raw, lengths, unit_length, starts=starts, with_gain=with_gain)
+
+
+def extract_windows_packed(raw, lengths, unit_length, starts=None, with_gain=False):
+    """``extract_windows`` for clips already back to back in one CUDA buffer ``raw`` (clip b has ``lengths[b]``
+    samples and starts where clip b-1 ends)."""
+    unit_length = int(unit_length)
+    lengths = np.asarray(lengths, np.int64)
+    b = int(lengths.shape[0])
+    offsets = np.concatenate(([0], np.cumsum(lengths)[:-1])).astype(np.int64) if b else np.zeros(0, np.int64)
+    if b and int(lengths.sum()) > raw.numel():
+        raise ValueError("clip lengths exceed the packed buffer")
+    device = raw.device
+    with torch.cuda.device(device):
         if raw.numel() == 0:
             raw = torch.zeros(1, dtype=torch.float32, device=device)
         meta = np.stack([offsets, lengths, np.zeros(b, np.int64) if starts is None else np.asarray(starts, np.int64)])

@@ -15,6 +15,7 @@ import numpy as np
 import torch
 
 from .augmentations import _as_batch, _chunks
+from .datamodule import PackedClips
 from .engine import ViewEngine
 from .frontend import Plan, as_cuda_f32
 from .sampler import FastSampler, ReferenceSampler, ViewParams
@@ -119,6 +120,8 @@ class UpstreamInputPipeline:
         self.last_lms = None
 
     def __call__(self, waveforms, params: ViewParams = None):
+        if isinstance(waveforms, PackedClips):
+            return self._ragged(waveforms, params)
         if isinstance(waveforms, (list, tuple)):
             return self._ragged(list(waveforms), params)
         wave = as_cuda_f32(waveforms)
@@ -156,24 +159,34 @@ class UpstreamInputPipeline:
 
     def _ragged(self, clips, params):
         """Raw clips of any length: extract_window (+ L2 gain in the same pass) feeds the front end."""
-        from .frontend import extract_windows
+        from .frontend import extract_windows, extract_windows_packed
         if self.unit_length is None:
             raise ValueError("raw clips need a window length: config['pretrain']['input']['length_wave'] or unit_length=")
         eng, tf = self.tfms.engine, self.tfms
-        device = next((c.device for c in clips if isinstance(c, torch.Tensor) and c.is_cuda),
-                      torch.device("cuda", torch.cuda.current_device()))
+        packed = clips if isinstance(clips, PackedClips) else None
+        if packed is not None:
+            device, lengths = packed.raw.device, packed.lengths
+            offsets = np.concatenate((packed.offsets, [int(lengths.sum())]))
+        else:
+            device = next((c.device for c in clips if isinstance(c, torch.Tensor) and c.is_cuda),
+                          torch.device("cuda", torch.cuda.current_device()))
+            lengths = np.array([int(c.shape[0]) for c in clips], np.int64)
         v1s, v2s = [], []
         with torch.cuda.device(device):
             eng.ensure(self.plan.n_mels, self.plan.num_frames(self.unit_length), device)
-            for lo, hi in _chunks(len(clips), eng.max_batch):
-                adj = np.array([int(c.shape[0]) - self.unit_length for c in clips[lo:hi]], np.int64)
+            for lo, hi in _chunks(len(lengths), eng.max_batch):
+                adj = lengths[lo:hi] - self.unit_length
                 if params is None:       # the window offset of a clip is drawn before its view parameters
                     p = tf.sampler.draw(eng.clips_done, hi - lo, eng.f, eng.t, window_adj=adj)
                 else:
                     p = ViewParams(params.alpha[lo:hi], params.src_clip[lo:hi], params.bank_index[lo:hi],
                                    params.crop[lo:hi], None if params.start is None else params.start[lo:hi])
                 tf.last_params = p
-                win = extract_windows(clips[lo:hi], self.unit_length, starts=p.start, with_gain=self.l2, device=device)
+                if packed is not None:
+                    win = extract_windows_packed(packed.raw[offsets[lo]:offsets[hi]], lengths[lo:hi], self.unit_length,
+                                                 starts=p.start, with_gain=self.l2)
+                else:
+                    win = extract_windows(clips[lo:hi], self.unit_length, starts=p.start, with_gain=self.l2, device=device)
                 part, gain = win if self.l2 else (win, None)
                 a, c = self._windows_to_views(part, gain, lambda p=p: p)
                 v1s.append(a); v2s.append(c)

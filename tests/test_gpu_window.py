@@ -110,3 +110,30 @@ def test_empty_and_invalid():
         A.extract_windows([torch.zeros(2, 3)], 100)
     with pytest.raises(ValueError):
         A.UpstreamInputPipeline({"pretrain": {"normalization": "mean_var", "augmentations": {}}}, 4)([torch.zeros(10)])
+
+
+def test_device_batch_loader_matches_reference_epoch():
+    """One seeded epoch through DeviceBatchLoader == the reference's DataLoader(num_workers=0) order of clips and
+    of random draws (window offset, then both views, clip by clip), views compared with the oracle."""
+    import audiossl_b200 as A
+    unit, bs = 8000, 4
+    lengths = [8000, 12000, 3000, 8001, 20000, 8000, 9500, 16000, 100, 11000, 8000, 30000, 7000, 9000]
+    clips = [c.numpy() for c in _raw_clips(lengths, 21)]
+    torch.manual_seed(7); np.random.seed(31); random.seed(31)
+    pipe = A.UpstreamInputPipeline(CFG, len(clips), max_batch=8)
+    dm = A.BaselineDataModule(CFG, None, pipe, data_csv=clips, batch_size=bs, num_workers=2)
+    dm.setup()
+    assert dm.dataset_sizes["train"] == len(clips)
+    got = [(a.cpu(), b.cpu()) for a, b in dm.train_dataloader()]
+    assert len(got) == len(clips) // bs and tuple(got[0][0].shape) == (bs, 1, 64, 51)
+
+    torch.manual_seed(7); np.random.seed(31); random.seed(31)
+    order = A.DeviceBatchLoader(A.WaveformDataset(clips), None, batch_size=bs).batches()
+    oracle = ov.TwoViewOracle(len(clips))
+    for k, idx in enumerate(order):
+        for r, i in enumerate(idx):
+            w, _ = ofe.extract_window(clips[i], unit, rng=random)
+            a, b = oracle(torch.from_numpy(ofe.log_mel(w)).unsqueeze(0))
+            for have, ref in ((got[k][0][r], a), (got[k][1][r], b)):
+                d = np.abs(have.numpy() - ref.numpy())
+                assert (d <= 5e-5 + 1e-4 * np.abs(ref.numpy())).all(), (k, r, d.max())
