@@ -415,7 +415,9 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
     const bool two = ta + 1 < a.T;                   // the last pair of an odd-length clip has one frame
     long long slot = a.slot0 + clip;
     if (a.cap > 0 && slot >= a.cap) slot -= a.cap;
-    float* out = a.lms + slot * (static_cast<long long>(a.n_mels) * a.T) + ta;
+    const bool power = a.out_kind & 1, tmajor = a.out_kind & 2;      // [n_mels, T] rows, or time-major [T, n_mels]
+    float* out = a.lms + slot * (static_cast<long long>(a.n_mels) * a.T) + (tmajor ? ta * a.n_mels : ta);
+    const int band_stride = tmajor ? 1 : a.T, frame_stride = tmajor ? a.n_mels : 1;
     float g2 = 1.f;
     if (a.gain) { const float g = a.gain[clip]; g2 = g * g; }   // |g x|^2 = g^2 |x|^2: per-clip gain applied here
     float s1 = 0.f, s2 = 0.f;
@@ -426,12 +428,12 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
       const float c = s_mconst[m];
       acc0 = fmaf(acc0, g2, c);
       acc1 = fmaf(acc1, g2, c);
-      const float l0 = a.out_kind ? acc0 : __logf(acc0 + kLogEps);
-      const float l1 = a.out_kind ? acc1 : __logf(acc1 + kLogEps);
-      float* dst = out + m * a.T;
+      const float l0 = power ? acc0 : __logf(acc0 + kLogEps);
+      const float l1 = power ? acc1 : __logf(acc1 + kLogEps);
+      float* dst = out + m * band_stride;
       dst[0] = l0;
       s1 += l0; s2 = fmaf(l0, l0, s2);
-      if (two) { dst[1] = l1; s1 += l1; s2 = fmaf(l1, l1, s2); }
+      if (two) { dst[frame_stride] = l1; s1 += l1; s2 = fmaf(l1, l1, s2); }
     }
     if (a.tile_sums) {                               // per frame pair (sum, sum^2), fixed butterfly order
 #pragma unroll
@@ -494,7 +496,7 @@ extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const floa
                                int64_t L, int64_t ld, float* lms, int64_t slot0, int64_t cap,
                                double* tile_sums, int32_t out_kind, void* stream) {
   using namespace assl;
-  if (out_kind != 0 && out_kind != 1) return ASSL_ERR_INVALID_ARG;
+  if (out_kind < 0 || out_kind > 3) return ASSL_ERR_INVALID_ARG;
   if (!p || !wave || !lms || B < 0 || ld < L || slot0 < 0 || cap < 0) return ASSL_ERR_INVALID_ARG;
   if (L <= p->cfg.n_fft / 2) return ASSL_ERR_INVALID_ARG;       // np.pad(reflect) needs L > n_fft/2
   if (cap > 0 && (B > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;

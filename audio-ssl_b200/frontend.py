@@ -60,12 +60,13 @@ class Plan:
         _native.check(_native.lib().assl_plan_filterbank(self.handle, out.ctypes.data_as(C.c_void_p)))
         return out
 
-    def logmel_into(self, wave, out, slot0=0, cap=0, tile_sums=None, gain=None, power=False):
-        """wave [B, L] cuda fp32 -> out (ring or [B, n_mels, T]); all on the current stream."""
+    def logmel_into(self, wave, out, slot0=0, cap=0, tile_sums=None, gain=None, power=False, time_major=False):
+        """wave [B, L] cuda fp32 -> out (ring or [B, n_mels, T]; [B, T, n_mels] with time_major); all on the
+        current stream."""
         b, n = wave.shape
         _native.check(_native.lib().assl_logmel_f32(
             self.handle, _ptr(wave), _ptr(gain), b, n, wave.stride(0), _ptr(out), int(slot0), int(cap),
-            _ptr(tile_sums), 1 if power else 0, _stream_ptr()), "assl_logmel_f32")
+            _ptr(tile_sums), (1 if power else 0) | (2 if time_major else 0), _stream_ptr()), "assl_logmel_f32")
 
     def __del__(self):
         try:
@@ -92,7 +93,7 @@ class MelSpectrogramLibrosa:
     def mfb(self):
         return self.plan.filterbank()
 
-    def _run(self, audio, power, l2_normalize=False):
+    def _run(self, audio, power, l2_normalize=False, time_major=False):
         wave = as_cuda_f32(audio)
         single = wave.dim() == 1
         if single:
@@ -101,21 +102,24 @@ class MelSpectrogramLibrosa:
             raise ValueError("expected a waveform [L] or a batch [B, L]")
         with torch.cuda.device(wave.device):
             t = self.plan.num_frames(wave.shape[1])
-            out = torch.empty((wave.shape[0], self.n_mels, t), dtype=torch.float32, device=wave.device)
+            shape = (wave.shape[0], t, self.n_mels) if time_major else (wave.shape[0], self.n_mels, t)
+            out = torch.empty(shape, dtype=torch.float32, device=wave.device)
             gain = None
             if l2_normalize:
                 gain = torch.empty(wave.shape[0], dtype=torch.float32, device=wave.device)
                 _native.check(_native.lib().assl_wave_l2_gain_f32(
                     _ptr(wave), wave.shape[0], wave.shape[1], wave.stride(0), _ptr(gain), _stream_ptr()))
-            self.plan.logmel_into(wave, out, gain=gain, power=power)
+            self.plan.logmel_into(wave, out, gain=gain, power=power, time_major=time_major)
         return out[0] if single else out
 
     def __call__(self, audio):
         return self._run(audio, power=True)
 
-    def log_mel(self, audio, l2_normalize=False):
-        """Fused log-mel; ``l2_normalize`` folds ``F.normalize(waveform, p=2)`` (upstream_dataset.py:62-63) in."""
-        return self._run(audio, power=False, l2_normalize=l2_normalize)
+    def log_mel(self, audio, l2_normalize=False, time_major=False):
+        """Fused log-mel; ``l2_normalize`` folds ``F.normalize(waveform, p=2)`` (upstream_dataset.py:62-63) in;
+        ``time_major`` writes ``[T, n_mels]`` per clip, the layout of the MAST variant
+        (extras/mast_new/mast/moco_dataset.py:105-106), straight from the kernel."""
+        return self._run(audio, power=False, l2_normalize=l2_normalize, time_major=time_major)
 
 
 def extract_log_mel_spectrogram(waveform, to_mel_spec):

@@ -88,7 +88,9 @@ int assl_plan_filterbank(const assl_plan* plan, float* host_out);
  * tile_sums optional [B, num_tiles, 2] fp64: per tile (sum x, sum x^2) of the values written,
  *           input of assl_running_stats; NULL to skip
  * out_kind  0 = log-mel (extract_log_mel_spectrogram), 1 = mel power (MelSpectrogramLibrosa.__call__
- *           alone, i.e. without the final log(. + eps))                                        */
+ *           alone, i.e. without the final log(. + eps)); add 2 for time-major slots [T, n_mels], the
+ *           layout the MAST variant feeds its transforms (extras/mast_new/mast/moco_dataset.py:105-106
+ *           permutes to [1, T, F]); the rings of the two-view path use the default [n_mels, T]    */
 int assl_logmel_f32(const assl_plan* plan, const float* wave, const float* wave_gain, int64_t B,
                     int64_t L, int64_t ld, float* lms, int64_t slot0, int64_t cap,
                     double* tile_sums, int32_t out_kind, void* stream);

@@ -125,3 +125,16 @@ def test_other_plan_parameters():
     w = families(3, 12000, 21)
     want = np.stack([ofe.log_mel(x, mfb=ofe.mel_filterbank(n_mels=128, fmin=0, fmax=8000), hop=256) for x in w.numpy()])
     _close(A.extract_log_mel_spectrogram(w.cuda(), m).cpu().numpy(), want)
+
+
+def test_mast_variant_128_mels_time_major():
+    """extras/mast_new/mast/utils.py:251-259 (n_mels=128) and the [1, T, F] layout of moco_dataset.py:105-106."""
+    import audiossl_b200 as A
+    m = A.MelSpectrogramLibrosa(n_mels=128)
+    w = families(6, 16000, 77)
+    mfb = ofe.mel_filterbank(n_mels=128)
+    want = np.stack([ofe.log_mel(x, mfb=mfb) for x in w.numpy()])
+    got_t = m.log_mel(w.cuda(), time_major=True)
+    assert tuple(got_t.shape) == (6, 101, 128)
+    _close(got_t.permute(0, 2, 1).cpu().numpy(), want)
+    assert torch.equal(got_t.permute(0, 2, 1), m.log_mel(w.cuda()))      # same values, only the layout differs
