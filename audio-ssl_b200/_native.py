@@ -11,7 +11,7 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(CSRC, "libassl.so")
+LIB_PATH = os.environ.get("ASSL_LIB") or os.path.join(CSRC, "libassl.so")   # ASSL_LIB: an experimental build
 SOURCES = ["plan.cu", "logmel.cu", "window.cu", "stats.cu", "views.cu", "pipeline.cu"]
 HEADERS = ["common.cuh", "fft32_gen.cuh", "fft32p_gen.cuh", "f32x2.cuh", os.path.join("..", "..", "include", "assl.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
