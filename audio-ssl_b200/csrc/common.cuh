@@ -44,11 +44,11 @@ struct assl_plan {
   float2* d_iv_w;               // [n_iw]       {falling-edge weight of band j-1, rising-edge weight of band j}
   int4* d_lane_iv;              // [slots][32]  interval owned by (slot, lane) in the log-mel kernel:
                                 //              {first bin (even), bin pairs, offset into d_iv_w (even),
-                                //               scratch entry of the part's sums, or -1}
+                                //               scratch entry | starts-the-total << 16, or -1}
   float* d_mel_const;           // [n_mels]     2.22e-16 * sum of the band's weights (folded "+ eps" of utils.py:28)
   std::vector<float> h_fb;      // dense [n_mels][513] copy for assl_plan_filterbank
   std::vector<int4> h_lane_iv;  // host copy of d_lane_iv
-  std::vector<int> h_iv_pos;    // [n_mels+1] first scratch entry of an interval | its number of parts << 16
+  std::vector<int> h_iv_pos;    // [n_mels+1] scratch entry of every interval's total
   int* d_iv_pos = nullptr;
   // Copy streams + events of assl_pipeline_host_f32 (created on first use; that entry point is
   // single-caller per plan, everything else on a plan is read-only and thread-safe).

@@ -69,8 +69,8 @@ struct LogmelArgs {
   int n_slots;        // rows of lane_iv in use
   const float2* tw;
   const float2* iv_w;    // {falling-edge weight of band j-1, rising-edge weight of band j} per bin
-  const int4* lane_iv;   // [kIvSlots][32] part owned by (slot, lane): {first bin, bin pairs, offset in iv_w, scratch entry or -1}
-  const int* iv_pos;     // [n_mels + 1] first scratch entry of interval j | its number of parts << 16
+  const int4* lane_iv;   // [kIvSlots][32] interval owned by (slot, lane): {first bin, bin pairs, offset in iv_w, id or -1}
+  const int* iv_pos;     // [n_mels + 1] scratch entry holding interval j's total
   const float* mconst;   // [n_mels] 2.22e-16 * sum of the band's weights (the "+ eps" of utils.py:28, folded)
 };
 
@@ -215,9 +215,7 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
     for (int s = 0; s < 2; ++s)
       if (bytes[s]) bulk_g2s(s_wave + seg[s].off + lo[s], a.wave + seg[s].clip * a.ld + seg[s].base + lo[s], bytes[s], bar_wave);
   };
-#ifndef ASSL_ABL_NO_SYNC
   if (a.bulk_ok && tid == 0 && static_cast<int>(blockIdx.x) < a.total_tiles) issue_tile(blockIdx.x);
-#endif
 
   // flush the statistics a tile left in s_red (one (sum, sum^2) per frame pair): one pair of doubles per
   // clip segment, fixed summation order.  Called by warp 0 once every warp is done with that tile.
@@ -250,46 +248,32 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
     tile_segments(a, tile, seg);
     const int n0 = seg[0].n, np = n0 + seg[1].n;
 
-    // ---- waveform spans: wait for the bulk copies
-#ifdef ASSL_ABL_NO_SYNC
-    if (a.bulk_ok) {
-    } else {
-#else
+    // ---- waveform spans: wait for the bulk copies, patch what they could not cover (reflect padding of
+    //      np.pad(mode='reflect'): p<0 -> -p, p>L-1 -> 2(L-1)-p; tail remainder when L % 4 != 0)
     if (a.bulk_ok) {
       mbar_wait(bar_wave, it & 1);
     } else {
-#endif
       __syncthreads();                               // previous tile's input reads are done
       if (a.tile_sums && warp == 0 && prev_tile >= 0) flush_stats(prev_tile, (it - 1) & 1);
     }
-    // ---- patch what the bulk copies could not cover: librosa's reflect padding (np.pad(mode='reflect'): p < 0 ->
-    //      -p, p > L-1 -> 2(L-1) - p) at the first / last tiles of a clip, and the tail when L % 4 != 0.  The
-    //      reflected sample is normally already in shared memory (inside the delivered part of the span), so the
-    //      patch is a short shared-to-shared copy by the whole CTA; without bulk copies everything comes from global.
     bool fixed = false;
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
       if (seg[s].n > 0) {
         int lo = 0, hi = 0;
         if (a.bulk_ok) bulk_range(seg[s], a.L, &lo, &hi);
-#ifdef ASSL_ABL_NO_FIX
-        if (false) {
-#else
         if (lo > 0 || hi < seg[s].span) {             // CTA-uniform
-#endif
           const int last = static_cast<int>(a.L - 1);
           const int n_fix = lo + (seg[s].span - hi);
           const float* src = a.wave + seg[s].clip * a.ld;
           float* dst = s_wave + seg[s].off;
-          const int base = static_cast<int>(seg[s].base);
           for (int q = tid; q < n_fix; q += kThreads) {
             const int i = q < lo ? q : hi + (q - lo);
-            int p = base + i;
+            long long p = seg[s].base + i;
             if (p < 0) p = -p;
-            if (p > last) p = 2 * last - p;
+            if (p > last) p = 2ll * last - p;
             p = p < 0 ? 0 : (p > last ? last : p);    // only frames >= T can land here; never read back
-            const int r = p - base;
-            dst[i] = (r >= lo && r < hi) ? dst[r] : __ldg(src + p);
+            dst[i] = __ldg(src + p);
           }
           fixed = true;
         }
@@ -332,7 +316,6 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
     }
     // every warp has its samples in registers (and is done with the previous tile) -> warp 0 flushes the
     // previous tile's statistics, then the next tile's copy may overwrite s_wave
-#ifndef ASSL_ABL_NO_SYNC
     if (a.bulk_ok) {
       if (warp == 0) {
         asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory");
@@ -342,14 +325,10 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
         asm volatile("bar.arrive 1, %0;" ::"n"(kThreads) : "memory");
       }
     }
-#endif
     prev_tile = tile;
     if (!have) continue;                             // warp-uniform
 
-#ifndef ASSL_ABL_NO_FFT1
     fft32p(z);                                       // over n2 -> k2, this lane is n1
-#endif
-#ifndef ASSL_ABL_NO_TW
     {   // inter-stage twiddles W^(n1 k2), k2 = 8a + b: z * t = z * t.re + (i z) * t.im
       const ulonglong2* tl = reinterpret_cast<const ulonglong2*>(s_tw + lane * kTwStride);
       c32 t[10];                                     // w^8, w^16, w^24, w^1 .. w^7
@@ -367,9 +346,7 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
         for (int b = 0; b < 8; ++b) z[8 * g + b] = rot(z[8 * g + b], t[g - 1]);
       }
     }
-#endif
     __syncwarp();                                    // the previous pair's interval sums have been read
-#ifndef ASSL_ABL_NO_XPOSE
     {
       ulonglong2* row = reinterpret_cast<ulonglong2*>(ex + lane * kExStride);
 #pragma unroll
@@ -378,10 +355,7 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
     __syncwarp();
 #pragma unroll
     for (int n1 = 0; n1 < 32; ++n1) z[n1] = ex[n1 * kExStride + lane];
-#endif
-#ifndef ASSL_ABL_NO_FFT2
     fft32p(z);                                       // over n1 -> k1, this lane is k2: Z[lane + 32*k1]
-#endif
 
     // unpack: X1[k] = (Z[k] + conj Z[N-k]) / 2, X2[k] = (Z[k] - conj Z[N-k]) / 2i  (the 1/2 sits in the window)
     // with b = Z[N-k]:  |X1|^2 = (re+br)^2 + (im-bi)^2,  |X2|^2 = (im+bi)^2 + (re-br)^2
@@ -391,14 +365,10 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
       c32 pw2[16];
 #pragma unroll
       for (int k1 = 0; k1 < 16; ++k1) {
-#ifdef ASSL_ABL_NO_UNPACK
-        pw2[k1] = add2(z[k1], z[31 - k1]);
-#else
         const c32 src = self ? z[(32 - k1) & 31] : z[31 - k1];
         const c32 b = pk(__shfl_sync(0xffffffffu, lo_of(src), partner), __shfl_sync(0xffffffffu, hi_of(src), partner));
         const c32 u = add2(z[k1], b), v = swp(sub2(z[k1], b));
         pw2[k1] = fma2(u, u, mul2(v, v));
-#endif
       }
       __syncwarp();                                  // everyone is done reading the exchange buffer
 #pragma unroll
@@ -413,33 +383,31 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
 
     // ---- filterbank, interval form.  Interval j = bins between the centres of bands j-1 and j; its bins feed
     //      the falling edge of band j-1 (weight .x) and the rising edge of band j (weight .y).
-    //      Every part writes its two sums {Sd, Su} to its own 16-byte entry behind the power spectra (no
-    //      read-modify-write, no ordering between slots); a band then adds the entries of its two intervals.
-    ulonglong2* scratch = reinterpret_cast<ulonglong2*>(ex + kScratch);
-#ifndef ASSL_ABL_NO_MEL
-#ifndef ASSL_ABL_SLOT_PLAIN
-#pragma unroll 1
-#endif
-    for (int s = 0; s < a.n_slots; ++s) {            // one copy of the body: instruction-cache footprint matters
-      {
-        const int4 iv = s_lane[s * 32 + lane];       // the same interval parts for the whole launch
-        const ulonglong2* wv = reinterpret_cast<const ulonglong2*>(s_ivw + iv.z);
-        const ulonglong2* pv = reinterpret_cast<const ulonglong2*>(ex + iv.x);
-        c32 d0 = pk(0.f, 0.f), u0 = d0, d1 = d0, u1 = d0;   // {frame 2q, frame 2q+1}; even / odd bins apart
+    //      Interval totals {Sd(j), Su(j)} live behind the power spectra, one 16-byte entry each at a
+    //      plan-chosen position; band m = Su(m) + Sd(m+1).
+    c32* scratch = ex + kScratch;
+    for (int s = 0; s < a.n_slots; ++s) {
+      const int4 iv = s_lane[s * 32 + lane];         // the same interval parts for the whole launch
+      const ulonglong2* wv = reinterpret_cast<const ulonglong2*>(s_ivw + iv.z);
+      const ulonglong2* pv = reinterpret_cast<const ulonglong2*>(ex + iv.x);
+      c32 d0 = pk(0.f, 0.f), u0 = d0, d1 = d0, u1 = d0;   // {frame 2q, frame 2q+1}; even / odd bins apart
 #pragma unroll
-        for (int j = 0; j < kPartBins / 2; ++j) {    // every part has kPartBins bins (zero weights pad it)
-          const ulonglong2 w = wv[j];
-          const ulonglong2 p = pv[j];
-          d0 = fma2(bc(lo_of(w.x)), p.x, d0);
-          u0 = fma2(bc(hi_of(w.x)), p.x, u0);
-          d1 = fma2(bc(lo_of(w.y)), p.y, d1);
-          u1 = fma2(bc(hi_of(w.y)), p.y, u1);
-        }
-        if (iv.w >= 0) scratch[iv.w] = make_ulonglong2(add2(d0, d1), add2(u0, u1));
+      for (int j = 0; j < kPartBins / 2; ++j) {      // every part has kPartBins bins (zero weights pad it)
+        const ulonglong2 w = wv[j];
+        const ulonglong2 p = pv[j];
+        d0 = fma2(bc(lo_of(w.x)), p.x, d0);
+        u0 = fma2(bc(hi_of(w.x)), p.x, u0);
+        d1 = fma2(bc(lo_of(w.y)), p.y, d1);
+        u1 = fma2(bc(hi_of(w.y)), p.y, u1);
       }
+      if (iv.w >= 0) {                               // parts of one interval sit in different slots: fixed order
+        ulonglong2* tot = reinterpret_cast<ulonglong2*>(scratch) + (iv.w & 0xffff);
+        c32 sd = add2(d0, d1), su = add2(u0, u1);
+        if (!(iv.w >> 16)) { const ulonglong2 o = *tot; sd = add2(o.x, sd); su = add2(o.y, su); }
+        *tot = make_ulonglong2(sd, su);
+      }
+      __syncwarp();
     }
-#endif
-    __syncwarp();
 
     // ---- bands: add the two edges, fold eps and gain, log, store, statistics
     const int ta = 2 * wpair;
@@ -453,16 +421,8 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
     float g2 = 1.f;
     if (a.gain) { const float g = a.gain[clip]; g2 = g * g; }   // |g x|^2 = g^2 |x|^2: per-clip gain applied here
     float s1 = 0.f, s2 = 0.f;
-#ifdef ASSL_ABL_NO_BANDS
-    if (lane == 0 && scratch[1].x == 12345ull) out[0] = 1.f;
-    for (int m = a.n_mels + lane; m < a.n_mels; m += 32) {
-#else
     for (int m = lane; m < a.n_mels; m += 32) {
-#endif
-      const int2 pp = make_int2(s_pos[m], s_pos[m + 1]);     // entry | parts << 16 of intervals m and m + 1
-      c32 su = scratch[pp.x & 0xffff].y, sd = scratch[pp.y & 0xffff].x;   // rising edge + falling edge
-      for (int r = 1; r < (pp.x >> 16); ++r) su = add2(su, scratch[(pp.x & 0xffff) + r].y);
-      for (int r = 1; r < (pp.y >> 16); ++r) sd = add2(sd, scratch[(pp.y & 0xffff) + r].x);
+      const c32 su = scratch[2 * s_pos[m] + 1], sd = scratch[2 * s_pos[m + 1]];   // rising edge + falling edge
       float acc0, acc1;
       upk(add2(su, sd), acc0, acc1);
       const float c = s_mconst[m];
@@ -476,13 +436,11 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
       if (two) { dst[frame_stride] = l1; s1 += l1; s2 = fmaf(l1, l1, s2); }
     }
     if (a.tile_sums) {                               // per frame pair (sum, sum^2), fixed butterfly order
-#ifndef ASSL_ABL_NO_STATS
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         s1 += __shfl_xor_sync(0xffffffffu, s1, o);
         s2 += __shfl_xor_sync(0xffffffffu, s2, o);
       }
-#endif
       if (lane == 0) s_red[(it & 1) * kWarps + warp] = make_float2(s1, s2);
     }
   }

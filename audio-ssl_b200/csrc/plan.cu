@@ -136,8 +136,8 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
   }
   // Lanes of the log-mel kernel own pieces of intervals for the whole launch.  Every interval is cut into
   // parts of exactly kPartBins bins (its weight run is zero-padded to whole parts), so all lanes run the
-  // same straight-line code; a lane owns one part per slot and writes that part's two sums to a scratch entry
-  // of its own (a band later adds the entries of its two intervals in a fixed order).  A 128-bit shared load
+  // same straight-line code; a lane owns one part per slot.  Two parts of one interval never share a slot:
+  // their sums are added to the interval's total slot after slot, in a fixed order.  A 128-bit shared load
   // is served a quarter-warp at a time, conflict-free when its eight 16-byte accesses fall in eight different
   // bank groups: parts are dealt to the quarter-warps round-robin in order of bank group, so a quarter sees
   // a group twice only when more parts share it than there are quarters.
@@ -158,23 +158,75 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
     std::vector<std::vector<Part>> quarter(n_q);
     for (size_t i = 0; i < parts.size(); ++i) quarter[i % n_q].push_back(parts[i]);   // 8 each
     auto slot_of = [&](int q) { return q % n_slots; };
-    // every part owns one 16-byte scratch entry {falling-edge sum, rising-edge sum}; the entries of an interval
-    // are consecutive (ascending bins), so a band adds its intervals' entries in a fixed order
-    std::vector<int> pos(n_iv + 1, 0), n_parts_iv(n_iv, 0);
+    // repair: two parts of one interval in one slot -> swap one with a part of the same bank group elsewhere
+    for (int pass = 0; pass < 64; ++pass) {
+      bool clash = false;
+      for (int q = 0; q < n_q; ++q)
+        for (size_t i = 0; i < quarter[q].size(); ++i) {
+          const Part x = quarter[q][i];
+          if (x.iv < 0) continue;
+          auto in_slot = [&](int sl, int iv, int skip_q, size_t skip_i) {
+            for (int r = 0; r < n_q; ++r)
+              if (slot_of(r) == sl)
+                for (size_t t = 0; t < quarter[r].size(); ++t)
+                  if (!(r == skip_q && t == skip_i) && quarter[r][t].iv == iv) return true;
+            return false;
+          };
+          if (!in_slot(slot_of(q), x.iv, q, i)) continue;
+          clash = true;
+          bool done = false;
+          for (int r = 0; r < n_q && !done; ++r) {
+            if (slot_of(r) == slot_of(q)) continue;
+            for (size_t t = 0; t < quarter[r].size() && !done; ++t) {
+              const Part y = quarter[r][t];
+              if (group(y) != group(x)) continue;
+              if (in_slot(slot_of(r), x.iv, r, t)) continue;                    // x would clash there
+              if (y.iv >= 0 && in_slot(slot_of(q), y.iv, q, i)) continue;      // y would clash here
+              quarter[q][i] = y; quarter[r][t] = x; done = true;
+            }
+          }
+        }
+      if (!clash) break;
+      if (pass == 63) { delete p; return ASSL_ERR_UNSUPPORTED; }
+    }
+    std::vector<int> first_slot(n_iv, 1 << 30);
     for (int q = 0; q < n_q; ++q)
-      for (const Part& x : quarter[q]) if (x.iv >= 0) ++n_parts_iv[x.iv];
-    int n_entries = 0;
-    for (int j = 0; j < n_iv; ++j) { pos[j] = n_entries | (n_parts_iv[j] << 16); n_entries += n_parts_iv[j]; }
-    pos[n_iv] = 0;
-    if (n_entries > assl::kScratchEntries) { delete p; return ASSL_ERR_UNSUPPORTED; }
+      for (const Part& x : quarter[q])
+        if (x.iv >= 0 && slot_of(q) < first_slot[x.iv]) first_slot[x.iv] = slot_of(q);
+    // where an interval's running total lives in the warp's scratch (16-byte entries): a quarter-warp's eight
+    // read-modify-writes are conflict-free when their entries differ mod 8, so intervals get one of 8 colours,
+    // greedily, least clashes with the intervals they share a quarter with first
+    std::vector<int> colour(n_iv, -1), pos(n_iv, 0);
+    {
+      std::vector<std::vector<int>> mates(n_iv);
+      for (int q = 0; q < n_q; ++q)
+        for (const Part& x : quarter[q])
+          for (const Part& y : quarter[q])
+            if (x.iv >= 0 && y.iv >= 0 && x.iv != y.iv) mates[x.iv].push_back(y.iv);
+      std::vector<int> by_deg(n_iv);
+      for (int j = 0; j < n_iv; ++j) by_deg[j] = j;
+      std::stable_sort(by_deg.begin(), by_deg.end(), [&](int x, int y) { return mates[x].size() > mates[y].size(); });
+      int used_per_colour[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      for (int j : by_deg) {
+        int clash[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int m : mates[j]) if (colour[m] >= 0) ++clash[colour[m]];
+        int best = 0;
+        for (int c = 1; c < 8; ++c)
+          if (clash[c] < clash[best] || (clash[c] == clash[best] && used_per_colour[c] < used_per_colour[best])) best = c;
+        colour[j] = best;
+        pos[j] = best + 8 * used_per_colour[best]++;
+      }
+    }
+    int n_pos = 0;
+    for (int j = 0; j < n_iv; ++j) n_pos = n_pos > pos[j] + 1 ? n_pos : pos[j] + 1;
+    if (n_pos > assl::kScratchEntries) { delete p; return ASSL_ERR_UNSUPPORTED; }
     std::vector<int4> lane_iv(static_cast<size_t>(32) * assl::kIvSlots, make_int4(0, 0, zero_off, -1));
     for (int q = 0; q < n_q; ++q)
       for (size_t i = 0; i < quarter[q].size(); ++i) {
         const Part& x = quarter[q][i];
         const int sl = slot_of(q), lane = (q / n_slots) * 8 + static_cast<int>(i);
-        int entry = -1;
-        if (x.iv >= 0) entry = (pos[x.iv] & 0xffff) + (cnt[x.iv] > 0 ? (x.k0 - k0[x.iv]) / assl::kPartBins : 0);
-        lane_iv[static_cast<size_t>(sl) * 32 + lane] = make_int4(x.k0, assl::kPartBins / 2, x.off, entry);
+        const int tag = x.iv < 0 ? -1 : (pos[x.iv] | ((first_slot[x.iv] == sl ? 1 : 0) << 16));   // bit 16: starts the total
+        lane_iv[static_cast<size_t>(sl) * 32 + lane] = make_int4(x.k0, assl::kPartBins / 2, x.off, tag);
       }
     p->h_iv_pos = pos;
     p->n_slots = n_slots;
