@@ -6,7 +6,7 @@ hand-written sm_100a CUDA kernels behind the C ABI in ``include/assl.h``.  There
     from audiossl_b200 import MelSpectrogramLibrosa, extract_log_mel_spectrogram, AugmentationModule
 """
 from . import _native
-from .augmentations import (MixupBYOLA, NormalizeBatch, PrecomputedNorm, RandomResizeCrop,  # noqa: F401
+from .augmentations import (Kmix, MixupBYOLA, NormalizeBatch, PrecomputedNorm, RandomResizeCrop,  # noqa: F401
                             RunningNorm)
 from .datamodule import BaselineDataModule, DeviceBatchLoader, PackedClips, WaveformDataset  # noqa: F401
 from .engine import ViewEngine, shard_bounds  # noqa: F401

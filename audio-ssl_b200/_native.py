@@ -12,7 +12,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.environ.get("ASSL_LIB") or os.path.join(CSRC, "libassl.so")   # ASSL_LIB: an experimental build
-SOURCES = ["plan.cu", "logmel.cu", "window.cu", "stats.cu", "views.cu", "pipeline.cu"]
+SOURCES = ["plan.cu", "logmel.cu", "window.cu", "stats.cu", "views.cu", "kmix.cu", "pipeline.cu"]
 HEADERS = ["common.cuh", "fft32_gen.cuh", "fft32p_gen.cuh", "f32x2.cuh", os.path.join("..", "..", "include", "assl.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC"]
@@ -70,6 +70,7 @@ SIGNATURES = {
     "assl_running_stats": (C.c_int, [_P, _P, _I64, _I64, _I64, _I64, _I64, _I64, _P, _I64, _I64, _P]),
     "assl_clip_sums": (C.c_int, [_P, _I64, _I64, _P, _P]),
     "assl_two_views_f32": (C.c_int, [C.POINTER(ViewCfg), _P, _P, _I64, _P, _P, _P, _P, _I64, _P, _P, _P]),
+    "assl_clip_clusters_f32": (C.c_int, [_P, _I64, C.c_int32, C.c_int32, _P, C.c_int32, _P, _P, _P]),
     "assl_batch_sums": (C.c_int, [_P, _I64, _P, _P]),
     "assl_normalize_apply_f32": (C.c_int, [_P, _P, _I64, _P, _P]),
     "assl_affine_norm_f32": (C.c_int, [_P, _P, _I64, _F, _F, _P]),

@@ -226,3 +226,117 @@ class MixupBYOLA(nn.Module):
         format_string = self.__class__.__name__ + f'(ratio={self.ratio},n={self.n}'
         format_string += f',log_mixup_exp={self.log_mixup_exp})'
         return format_string
+
+
+class Kmix(nn.Module):
+    """K-mix (augmentations.py:119-189): MixupBYOLA whose bank entry is drawn from the cluster FARTHEST from the
+    incoming clip's (clusters = nearest of the given centroids to the per-band mean over time).
+
+    Same constructor as the reference; ``centroid_path`` is loaded with ``torch.load`` like there, or pass the
+    ``[K, F]`` tensor as ``centroids=``.  The cluster features and ids are computed on the GPU for a whole batch
+    (``assl_clip_clusters_f32``), come back to the host once per call (K small integers per clip), and the
+    selection replays the reference's loop and its draws (``np.random.random()`` for alpha, then
+    ``np.random.randint(len(candidates))`` -- ``len(bank)`` while the bank holds fewer than 128 entries) clip by
+    clip in batch order; the mix itself is the MixupBYOLA kernel path.  ``top_k`` must be an integer <= 128: for
+    anything else the reference raises on its first full bank (``len(bank) < None`` / ``bank[None]``, :143, :178).
+    """
+
+    def __init__(self, ratio=0.4, n_memory=2048, log_mixup_exp=True, top_k=None, centroid_path=None, centroids=None,
+                 max_batch=4096):
+        super().__init__()
+        if not isinstance(top_k, int) or top_k > 128:
+            raise ValueError("Kmix needs an integer top_k <= 128 (the reference cannot run otherwise)")
+        if centroids is None:
+            if centroid_path is None:
+                raise ValueError("Kmix needs centroids: centroid_path (a torch-saved [K, F] tensor) or centroids=")
+            centroids = torch.load(centroid_path)                 # Centroid path must be in torch tensor format
+        c = torch.as_tensor(centroids, dtype=torch.float32).cpu()
+        if c.dim() != 2:
+            raise ValueError("centroids must be [K, F]")
+        self.ratio, self.n, self.log_mixup_exp, self.top_k = ratio, n_memory, log_mixup_exp, top_k
+        self.centroids = c
+        self._unit = c / c.norm(dim=-1, keepdim=True)                                        # :146
+        k = c.shape[0]
+        self._order = torch.topk(torch.cdist(self._unit, self._unit, p=2), k=k, dim=1).indices.numpy()   # :152
+        self._unit_dev = None
+        self._engine = ViewEngine(n_memory=n_memory, pushes_per_clip=1, ratio=ratio, log_mixup=log_mixup_exp,
+                                  virtual_crop_scale=(1.0, 1.0), normalize=False, max_batch=max_batch)
+        self._bank_cluster = np.zeros(0, np.int32)            # cluster of every bank entry, FIFO order
+        self.last_params = None
+        self.last_candidates = None
+
+    @property
+    def memory_bank_size(self):
+        return int(self._bank_cluster.shape[0])
+
+    def _clusters(self, xb):
+        lib = _native.lib()
+        b, f, t = xb.shape
+        if f != self.centroids.shape[1]:
+            raise ValueError(f"centroids have {self.centroids.shape[1]} bands, the clips {f}")
+        if self._unit_dev is None or self._unit_dev.device != xb.device:
+            self._unit_dev = self._unit.to(xb.device).contiguous()
+        ids = torch.empty((2, b), dtype=torch.int32, device=xb.device)
+        _native.check(lib.assl_clip_clusters_f32(_ptr(xb), b, f, t, _ptr(self._unit_dev), self._unit_dev.shape[0],
+                                                 _ptr(ids[0]), _ptr(ids[1]), _stream_ptr()), "assl_clip_clusters_f32")
+        ids = ids.cpu().numpy()                                # the one device -> host read of the call
+        return ids[0], ids[1]
+
+    def _draw(self, g0, mem, point):
+        """Replay Kmix.forward's draws for clips g0 .. g0+b-1 (:168-182); returns ViewParams + candidate counts."""
+        b = mem.shape[0]
+        alpha = np.zeros((b, 2), np.float32)
+        src = np.full((b, 2), -1, np.int64)
+        bidx = np.full((b, 2), -1, np.int32)
+        ncand = np.zeros(b, np.int32)
+        bank = self._bank_cluster
+        for i in range(b):
+            alpha[i, 0] = self.ratio * np.random.random()
+            n = bank.shape[0]
+            if n:
+                if n >= 128:
+                    cand = np.zeros(0, np.int64)
+                    for tgt in self._order[point[i]]:
+                        cand = np.nonzero(bank == tgt)[0]
+                        if cand.size:
+                            break
+                    cand = cand[:128]
+                    j = int(cand[np.random.randint(len(cand))])
+                    ncand[i] = len(cand)
+                else:
+                    j = int(np.random.randint(n))
+                    ncand[i] = n
+                bidx[i, 0] = j
+                src[i, 0] = g0 + i - n + j                    # bank position j holds clip (g0 + i) - n + j
+            bank = np.concatenate((bank, mem[i:i + 1]))[-self.n:]
+        self._bank_cluster = bank
+        f, t = self._engine.f, self._engine.t
+        crop = np.zeros((b, 2, 4), np.int32)
+        crop[:, :, 2], crop[:, :, 3] = f, t                   # identity box: no resampling
+        return ViewParams(alpha, src, bidx, crop), ncand
+
+    def forward(self, x, params: ViewParams = None):
+        xb, single = _as_batch(x)
+        eng = self._engine
+        outs = []
+        with torch.cuda.device(xb.device):
+            eng.ensure(xb.shape[1], xb.shape[2], xb.device)
+            for lo, hi in _chunks(xb.shape[0], eng.max_batch):
+                part = xb[lo:hi].contiguous()
+                eng.ring_put(part)
+                mem, point = self._clusters(part)
+                if params is None:
+                    p, self.last_candidates = self._draw(eng.clips_done, mem, point)
+                else:
+                    p = ViewParams(params.alpha[lo:hi], params.src_clip[lo:hi], params.bank_index[lo:hi], params.crop[lo:hi])
+                    self._bank_cluster = np.concatenate((self._bank_cluster, mem))[-self.n:]
+                self.last_params = p
+                v1, _ = eng.launch_views(p, hi - lo, xb.device)
+                outs.append(v1)
+        out = outs[0] if len(outs) == 1 else torch.cat(outs)
+        return out[:, 0] if single else out
+
+    def __repr__(self):
+        format_string = self.__class__.__name__ + f'(ratio={self.ratio},n={self.n}'
+        format_string += f',log_mixup_exp={self.log_mixup_exp})'
+        return format_string

@@ -161,6 +161,18 @@ int assl_two_views_f32(const assl_view_cfg* vcfg, const float* lms, const float*
                        const float* alpha, const int32_t* crop, int64_t B, float* view1,
                        float* view2, void* stream);
 
+/* -- Kmix cluster features ------------------------------------------------------------------
+ * The data-dependent half of Kmix.get_index (src/augmentations/augmentations.py:142-165): per clip, the
+ * per-band mean over time is assigned to the nearest of K centroids, once L2-normalised
+ * (a bank entry's role, :148-151, 153 -> mem_cluster) and once raw (the incoming clip's role, :154 ->
+ * point_cluster).  centroids_unit [K, n_freq] holds the centroids already divided by their L2 norms (:146).
+ * x [B, n_freq, n_time] fp32; outputs [B] int32, ties to the lowest index.  The choice among the bank entries
+ * of the farthest non-empty cluster, the random draws and the bank bookkeeping stay on the host; the mix is
+ * the MixupBYOLA arithmetic (assl_two_views_f32 with an identity crop). */
+int assl_clip_clusters_f32(const float* x, int64_t B, int32_t n_freq, int32_t n_time,
+                           const float* centroids_unit, int32_t K, int32_t* mem_cluster,
+                           int32_t* point_cluster, void* stream);
+
 /* -- batch post-normalisation --------------------------------------------------------------
  * Replaces NormalizeBatch.forward (src/augmentations/augmentations.py:321-324).
  * assl_batch_sums accumulates {count, sum x, sum x^2} of x[n] into sums[3] (fp64; the caller zeroes
