@@ -56,11 +56,15 @@ __global__ void __launch_bounds__(kScanThreads) running_stats_kernel(
     const long long k = n0 + idx;                     // put index of this clip
     double m = 0.0, q = 0.0;
     if (valid) {
+      // same left-to-right order as clip_sums_kernel; loads batched four parts at a time (one latency, not four)
+      const double2* sp = reinterpret_cast<const double2*>(sums) + idx * n_parts;
       double sx = 0.0, sxx = 0.0;
-      for (long long p = 0; p < n_parts; ++p) {
-        sx += sums[(idx * n_parts + p) * 2];
-        sxx += sums[(idx * n_parts + p) * 2 + 1];
+      long long p = 0;
+      for (; p + 4 <= n_parts; p += 4) {
+        const double2 a = sp[p], b = sp[p + 1], c = sp[p + 2], d = sp[p + 3];
+        sx += a.x; sxx += a.y; sx += b.x; sxx += b.y; sx += c.x; sxx += c.y; sx += d.x; sxx += d.y;
       }
+      for (; p < n_parts; ++p) { const double2 a = sp[p]; sx += a.x; sxx += a.y; }
       m = sx * inv_elems;
       q = sxx * inv_elems;
     }
@@ -192,6 +196,7 @@ extern "C" int assl_running_stats(double* state, const double* sums, int64_t n_c
   if (!state || !sums || !mean_std || n_clips < 0 || n_parts < 1 || elems < 1 || max_update < 1) return ASSL_ERR_INVALID_ARG;
   if (first < 0 || count < 0 || first + count > n_clips || slot0 < 0 || cap < 0) return ASSL_ERR_INVALID_ARG;
   if (cap > 0 && (count > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
+  if (reinterpret_cast<uintptr_t>(sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;   // (sum, sum^2) pairs are read as one 16-byte word
   if (n_clips == 0) return ASSL_OK;
   running_stats_kernel<<<1, kScanThreads, 0, as_stream(stream)>>>(state, sums, n_clips, n_parts, 1.0 / static_cast<double>(elems),
                                                                   max_update, first, count, mean_std, slot0, cap);

@@ -118,7 +118,7 @@ int assl_extract_windows_f32(const float* raw, const int64_t* offsets, const int
  * makes the 2nd sample overwrite the 1st, for ``n_clips`` clips in sequence order.
  * state      [8] fp64, caller-owned, zero-filled = fresh: {n_put, sum_mean, sum_var, mean, std, ...}
  * sums       [n_clips, n_parts, 2] fp64 (sum x, sum x^2) per clip part (tile_sums, or the
- *            all-gathered per-clip sums with n_parts = 1)
+ *            all-gathered per-clip sums with n_parts = 1); 16-byte aligned
  * elems      elements per clip (F*T)
  * max_update RunningNorm.max_update = epoch_samples * max_update_epochs (augmentations.py:271)
  * mean_std   ring/array of [2] fp32 (mean, std) slots; written for clips [first, first+count)
