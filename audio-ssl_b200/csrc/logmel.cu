@@ -4,14 +4,15 @@
 // extract_log_mel_spectrogram (/root/reference/src/utils/utils.py:43-49).
 //
 // Work decomposition
-//   persistent CTAs (2 per SM) loop over tiles of 8 consecutive frame pairs; the tile's waveform span is
-//   brought into shared memory by ONE bulk async copy (TMA, cp.async.bulk + mbarrier) issued a tile
-//   ahead, so the 6.4x overlap between hop-160 frames never goes back to L2/HBM and the global latency
-//   hides behind the previous tile's FFTs; librosa's reflect padding only touches the first/last tiles
-//   of a clip and is patched in by a short scalar fix-up.
-//   Each WARP then takes one frame pair from samples to log-mel values on its own, with no CTA-wide
-//   barrier in between (the only hand-off per tile is a non-blocking named-barrier arrive that lets
-//   warp 0 launch the next copy):
+//   One persistent CTA per SM; every WARP is its own pipeline over frame pairs (pair p of the flattened
+//   (clip, pair) list goes to warp p mod #warps, so neighbouring warps work on neighbouring frames and the
+//   6.4x overlap between hop-160 frames is served by L2).  There is no CTA-wide barrier after the prologue:
+//   the warps drift apart, so while some sit in the FFTs (FP32 pipe) others are in the transposition or
+//   the filterbank (shared-memory pipe) instead of all of them queueing for the same unit.
+//     * staging: the pair's waveform span (n_fft + hop samples) is brought into the warp's own buffer by a
+//       bulk async copy (TMA, cp.async.bulk + the warp's mbarrier) issued by lane 0 as soon as the previous
+//       span is in registers, so it lands behind a whole pair of compute; librosa's reflect padding only
+//       touches the first/last pairs of a clip and is patched in by the same warp;
 //     * the two real frames are the real and imaginary part of one 1024-point complex FFT laid out
 //       32 x 32: lane n1 holds samples n1 + 32*n2 (stride-32, conflict-free LDS; when hop is a multiple
 //       of 32 the second frame is the first shifted by hop/32 registers, so 37 loads feed both);
@@ -28,10 +29,11 @@
 #include "common.cuh"
 #include "fft32p_gen.cuh"
 
+#include <cstdlib>
+
 namespace assl {
 
-constexpr int kWarps = 8;
-constexpr int kThreads = kWarps * 32;
+constexpr int kMaxWarps = 16;                       // per CTA (128 registers x 512 threads = the register file)
 constexpr int kExStride = 34;                       // float2 units: lane-major rows of 32 + 2 pad (272 B: 128-bit
                                                     // row stores of a quarter warp hit 8 distinct 16-byte bank groups)
 constexpr int kExWarp = 32 * kExStride + 2;         // 1090 float2 = 8720 B per warp
@@ -57,14 +59,14 @@ struct LogmelArgs {
   const float* wave;
   const float* gain;
   float* lms;
-  double* tile_sums;
+  double* pair_sums;  // [B, ppc, 2] (sum, sum^2) of what each frame pair wrote, or null
   long long L, ld, slot0, cap;
   int B, T, hop, n_mels, out_kind, bulk_ok;
   int ppc;            // frame pairs per clip = ceil(T / 2)
   unsigned ppc_mul;   // n / ppc == (t + ((n - t) >> ppc_sh1)) >> ppc_sh2 with t = umulhi(ppc_mul, n)
   int ppc_sh1, ppc_sh2;
-  int straddle;       // 1: a tile is 8 consecutive pairs of the flattened (clip, pair) list and may span two clips
-  int total_tiles, n_parts, wave_floats;
+  int total_pairs;
+  int wave_floats;    // per-warp staging buffer (n_fft + hop, rounded up to 4)
   int n_iw;           // float2 entries of iv_w
   int n_slots;        // rows of lane_iv in use
   const float2* tw;
@@ -74,17 +76,16 @@ struct LogmelArgs {
   const float* mconst;   // [n_mels] 2.22e-16 * sum of the band's weights (the "+ eps" of utils.py:28, folded)
 };
 
-__host__ __device__ inline size_t logmel_smem_bytes(int wave_floats, int n_iw) {
+__host__ __device__ inline size_t logmel_smem_bytes(int warps, int wave_floats, int n_iw) {
   size_t b = 0;
-  b += sizeof(float2) * kWarps * kExWarp;   // exchange / power / interval-sum buffers
+  b += sizeof(float2) * warps * kExWarp;    // exchange / power / interval-sum buffers
   b += sizeof(float2) * 32 * kTwStride;     // twiddles
-  b += sizeof(float) * ((wave_floats + 3) & ~3);
+  b += sizeof(float) * warps * wave_floats; // staging
   b += sizeof(float2) * ((n_iw + 1) & ~1);
   b += sizeof(float) * kMaxMels;            // per-band folded eps
   b += sizeof(int4) * kIvSlots * 32;        // interval ownership
   b += sizeof(int) * (kMaxMels + 4);        // scratch entry per interval
-  b += sizeof(float2) * 2 * kWarps;         // per (tile parity, warp) (sum, sum^2)
-  b += 2 * sizeof(unsigned long long);      // mbarrier
+  b += sizeof(unsigned long long) * kMaxWarps;   // one mbarrier per warp
   return b;
 }
 
@@ -95,9 +96,6 @@ __device__ __forceinline__ void mbar_init(void* bar, unsigned count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(void* bar, unsigned bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(void* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(void* bar, unsigned parity) {
   asm volatile(
@@ -113,70 +111,51 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-// A tile = up to 8 frame pairs; its pairs belong to one clip, or (straddle mode) to two consecutive clips.
-struct Segment {
-  int clip;      // clip index in the batch
-  int q0;        // first pair of the clip in this tile
-  int n;         // pairs of this clip in the tile (0 = segment absent)
-  int off;       // where the segment's waveform span starts in s_wave (floats, multiple of 4)
-  int span;      // samples the segment's frames touch: (2n - 1) * hop + 1024
-  long long base;   // clip-relative sample index of the span start: 2*q0*hop - 512 (may be negative)
+// Frame pair p of the flattened list: clip, pair inside the clip, and the part of its span [base, base + span)
+// (clip-relative samples, base = 2 q hop - n_fft/2) a bulk copy can cover: [lo, hi) span-relative, multiples of 4.
+struct PairSpan {
+  int clip, q, lo, hi;
+  long long base;
 };
-
-__device__ __forceinline__ void tile_segments(const LogmelArgs& a, int tile, Segment seg[2]) {
-  int p0, np;
-  if (a.straddle) {
-    p0 = tile * kWarps;
-    const int total = a.B * a.ppc;
-    np = total - p0 < kWarps ? total - p0 : kWarps;
-  } else {                                 // clips shorter than 8 pairs: one clip per tile
-    p0 = tile * a.ppc;
-    np = a.ppc;
-  }
-  const unsigned t = __umulhi(a.ppc_mul, static_cast<unsigned>(p0));
-  const int b0 = static_cast<int>((t + ((static_cast<unsigned>(p0) - t) >> a.ppc_sh1)) >> a.ppc_sh2);
-  const int q0 = p0 - b0 * a.ppc;
-  const int n0 = np < a.ppc - q0 ? np : a.ppc - q0;
-  seg[0].clip = b0; seg[0].q0 = q0; seg[0].n = n0; seg[0].off = 0;
-  seg[0].span = (2 * n0 - 1) * a.hop + kNfft;
-  seg[0].base = 2ll * q0 * a.hop - kNfft / 2;
-  seg[1].clip = b0 + 1; seg[1].q0 = 0; seg[1].n = np - n0; seg[1].off = (seg[0].span + 3) & ~3;
-  seg[1].span = (2 * seg[1].n - 1) * a.hop + kNfft;
-  seg[1].base = -kNfft / 2;
-}
-
-// part of a segment's span the bulk copy covers (in range of the clip), span-relative [lo, hi), multiples of 4
-__device__ __forceinline__ void bulk_range(const Segment& g, long long L, int* lo, int* hi) {
-  const long long l = g.base < 0 ? -g.base : 0;
-  long long h = L - g.base;
-  h = h > g.span ? g.span : h;
+__device__ __forceinline__ PairSpan pair_span(const LogmelArgs& a, int p, int span) {
+  PairSpan s;
+  const unsigned t = __umulhi(a.ppc_mul, static_cast<unsigned>(p));
+  s.clip = static_cast<int>((t + ((static_cast<unsigned>(p) - t) >> a.ppc_sh1)) >> a.ppc_sh2);
+  s.q = p - s.clip * a.ppc;
+  s.base = 2ll * s.q * a.hop - kNfft / 2;
+  const long long l = s.base < 0 ? -s.base : 0;
+  long long h = a.L - s.base;
+  h = h > span ? span : h;
   h &= ~3ll;
-  *lo = static_cast<int>(l);
-  *hi = static_cast<int>(h > l ? h : l);
+  s.lo = a.bulk_ok ? static_cast<int>(l) : 0;
+  s.hi = a.bulk_ok ? static_cast<int>(h > l ? h : l) : 0;      // no bulk copy: the whole span goes through the patch loop
+  return s;
 }
 
 // H32 = hop / 32 when hop is a multiple of 32 (both frames of a pair share registers), else 0
 template <int H32>
-__global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a) {
+__global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int n_warps = blockDim.x >> 5;
   float2* s_ex = reinterpret_cast<float2*>(smem_raw);
-  float2* s_tw = s_ex + kWarps * kExWarp;
+  float2* s_tw = s_ex + n_warps * kExWarp;
   float* s_wave = reinterpret_cast<float*>(s_tw + 32 * kTwStride);
-  float2* s_ivw = reinterpret_cast<float2*>(s_wave + ((a.wave_floats + 3) & ~3));
+  float2* s_ivw = reinterpret_cast<float2*>(s_wave + n_warps * a.wave_floats);
   float* s_mconst = reinterpret_cast<float*>(s_ivw + ((a.n_iw + 1) & ~1));
   int4* s_lane = reinterpret_cast<int4*>(s_mconst + kMaxMels);             // [kIvSlots][32]
   int* s_pos = reinterpret_cast<int*>(s_lane + kIvSlots * 32);              // [n_mels + 1]
-  float2* s_red = reinterpret_cast<float2*>(s_pos + kMaxMels + 4);          // [2][kWarps]
-  unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_red + 2 * kWarps);
-  void* bar_wave = s_bar;        // tile's waveform spans have landed (tx bytes)
+  unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_pos + kMaxMels + 4);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n_threads = blockDim.x;
+  void* bar = s_bar + warp;                  // this warp's span has landed (tx bytes)
+  float* buf = s_wave + warp * a.wave_floats;
 
-  if (tid == 0) mbar_init(bar_wave, 1);
+  if (lane == 0) mbar_init(bar, 1);
   // Inter-stage twiddles w^k2 (w = W_1024^lane): only w^8, w^16, w^24 and w^1..w^7 are kept per lane; the
   // other 21 are applied as two rotations, (z * w^b) * w^(8a), trading 42 FFMA2/FMUL2 per transform for two
   // thirds of the table's shared-memory traffic
-  for (int i = tid; i < 32 * kTwStride; i += kThreads) {
+  for (int i = tid; i < 32 * kTwStride; i += n_threads) {
     const int n1 = i / kTwStride, e = i - n1 * kTwStride;
     const int k2 = e < 3 ? 8 * (e + 1) : e - 2;
     s_tw[i] = a.tw[k2 * 32 + n1];
@@ -187,108 +166,54 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
   float wa, wb;
   sincospif(static_cast<float>(lane) * (1.0f / 512.0f), &wb, &wa);
   wa *= -0.25f; wb *= 0.25f;
-  for (int i = tid; i < a.n_iw; i += kThreads) s_ivw[i] = a.iv_w[i];
-  for (int i = tid; i < a.n_mels; i += kThreads) s_mconst[i] = a.mconst[i];
-  for (int i = tid; i < kIvSlots * 32; i += kThreads) s_lane[i] = a.lane_iv[i];
-  for (int i = tid; i <= a.n_mels; i += kThreads) s_pos[i] = a.iv_pos[i];
+  for (int i = tid; i < a.n_iw; i += n_threads) s_ivw[i] = a.iv_w[i];
+  for (int i = tid; i < a.n_mels; i += n_threads) s_mconst[i] = a.mconst[i];
+  for (int i = tid; i < kIvSlots * 32; i += n_threads) s_lane[i] = a.lane_iv[i];
+  for (int i = tid; i <= a.n_mels; i += n_threads) s_pos[i] = a.iv_pos[i];
   // padded power reads (zero weights) must see finite values: the row padding of s_ex is never written again
-  for (int i = tid; i < kWarps * kExWarp; i += kThreads) s_ex[i] = make_float2(0.f, 0.f);
+  for (int i = tid; i < n_warps * kExWarp; i += n_threads) s_ex[i] = make_float2(0.f, 0.f);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  __syncthreads();
+  __syncthreads();                                   // the only CTA-wide barrier
 
-  // producer: bulk-copy the in-range spans of a tile into s_wave (one elected thread)
-  auto issue_tile = [&](int tile) {
-    Segment seg[2];
-    tile_segments(a, tile, seg);
-    unsigned bytes[2] = {0u, 0u};
-    int lo[2] = {0, 0};
-#pragma unroll
-    for (int s = 0; s < 2; ++s) {
-      if (seg[s].n > 0) {
-        int hi;
-        bulk_range(seg[s], a.L, &lo[s], &hi);
-        bytes[s] = static_cast<unsigned>(hi - lo[s]) * 4u;
-      }
-    }
-    mbar_expect_tx(bar_wave, bytes[0] + bytes[1]);
-#pragma unroll
-    for (int s = 0; s < 2; ++s)
-      if (bytes[s]) bulk_g2s(s_wave + seg[s].off + lo[s], a.wave + seg[s].clip * a.ld + seg[s].base + lo[s], bytes[s], bar_wave);
+  const int span = kNfft + a.hop;                    // samples the two frames of a pair touch
+  const int stride = static_cast<int>(gridDim.x) * n_warps;
+  // producer side of the warp's pipeline (lane 0): bulk-copy the in-range part of a pair's span
+  auto issue = [&](int p) {
+    const PairSpan s = pair_span(a, p, span);
+    const unsigned bytes = static_cast<unsigned>(s.hi - s.lo) * 4u;
+    mbar_expect_tx(bar, bytes);
+    if (bytes) bulk_g2s(buf + s.lo, a.wave + s.clip * a.ld + s.base + s.lo, bytes, bar);
   };
-  if (a.bulk_ok && tid == 0 && static_cast<int>(blockIdx.x) < a.total_tiles) issue_tile(blockIdx.x);
+  const int first = static_cast<int>(blockIdx.x) * n_warps + warp;
+  if (a.bulk_ok && lane == 0 && first < a.total_pairs) issue(first);
 
-  // flush the statistics a tile left in s_red (one (sum, sum^2) per frame pair): one pair of doubles per
-  // clip segment, fixed summation order.  Called by warp 0 once every warp is done with that tile.
-  auto flush_stats = [&](int tile, unsigned parity) {
-    Segment seg[2];
-    tile_segments(a, tile, seg);
-    double r1 = 0.0, r2 = 0.0;
-    if (lane < kWarps) { const float2 v = s_red[parity * kWarps + lane]; r1 = v.x; r2 = v.y; }
-    const int n0 = seg[0].n, np = n0 + seg[1].n;
-    double a1 = lane < n0 ? r1 : 0.0, a2 = lane < n0 ? r2 : 0.0;            // segment 0
-    double b1 = (lane >= n0 && lane < np) ? r1 : 0.0, b2 = (lane >= n0 && lane < np) ? r2 : 0.0;   // segment 1
-#pragma unroll
-    for (int o = 4; o > 0; o >>= 1) {
-      a1 += __shfl_xor_sync(0xffffffffu, a1, o); a2 += __shfl_xor_sync(0xffffffffu, a2, o);
-      b1 += __shfl_xor_sync(0xffffffffu, b1, o); b2 += __shfl_xor_sync(0xffffffffu, b2, o);
-    }
-    if (lane < 2 && (lane == 0 ? n0 : seg[1].n) > 0) {
-      const int clip = seg[0].clip + lane;
-      const int first_tile = a.straddle ? (clip * a.ppc) / kWarps : tile;
-      double* dst = a.tile_sums + (static_cast<long long>(clip) * a.n_parts + (tile - first_tile)) * 2;
-      dst[0] = lane == 0 ? a1 : b1;
-      dst[1] = lane == 0 ? a2 : b2;
-    }
-  };
-
+  c32* ex = reinterpret_cast<c32*>(s_ex + warp * kExWarp);
   unsigned it = 0;
-  int prev_tile = -1;
-  for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
-    Segment seg[2];
-    tile_segments(a, tile, seg);
-    const int n0 = seg[0].n, np = n0 + seg[1].n;
+  for (int pair = first; pair < a.total_pairs; pair += stride, ++it) {
+    const PairSpan sp = pair_span(a, pair, span);
+    const int clip = sp.clip, wpair = sp.q;
 
-    // ---- waveform spans: wait for the bulk copies, patch what they could not cover (reflect padding of
+    // ---- waveform span: wait for the bulk copy, patch what it could not cover (reflect padding of
     //      np.pad(mode='reflect'): p<0 -> -p, p>L-1 -> 2(L-1)-p; tail remainder when L % 4 != 0)
-    if (a.bulk_ok) {
-      mbar_wait(bar_wave, it & 1);
-    } else {
-      __syncthreads();                               // previous tile's input reads are done
-      if (a.tile_sums && warp == 0 && prev_tile >= 0) flush_stats(prev_tile, (it - 1) & 1);
-    }
-    bool fixed = false;
-#pragma unroll
-    for (int s = 0; s < 2; ++s) {
-      if (seg[s].n > 0) {
-        int lo = 0, hi = 0;
-        if (a.bulk_ok) bulk_range(seg[s], a.L, &lo, &hi);
-        if (lo > 0 || hi < seg[s].span) {             // CTA-uniform
-          const int last = static_cast<int>(a.L - 1);
-          const int n_fix = lo + (seg[s].span - hi);
-          const float* src = a.wave + seg[s].clip * a.ld;
-          float* dst = s_wave + seg[s].off;
-          for (int q = tid; q < n_fix; q += kThreads) {
-            const int i = q < lo ? q : hi + (q - lo);
-            long long p = seg[s].base + i;
-            if (p < 0) p = -p;
-            if (p > last) p = 2ll * last - p;
-            p = p < 0 ? 0 : (p > last ? last : p);    // only frames >= T can land here; never read back
-            dst[i] = __ldg(src + p);
-          }
-          fixed = true;
-        }
+    if (a.bulk_ok) mbar_wait(bar, it & 1);
+    if (sp.lo > 0 || sp.hi < span) {                 // warp-uniform: ~5 of 51 pairs of a 1-s clip
+      const int last = static_cast<int>(a.L - 1);
+      const int n_fix = sp.lo + (span - sp.hi);
+      const float* src = a.wave + clip * a.ld;
+      for (int q = lane; q < n_fix; q += 32) {
+        const int i = q < sp.lo ? q : sp.hi + (q - sp.lo);
+        long long p = sp.base + i;
+        if (p < 0) p = -p;
+        if (p > last) p = 2ll * last - p;
+        p = p < 0 ? 0 : (p > last ? last : p);       // only frames >= T can land here; never read back
+        buf[i] = __ldg(src + p);
       }
+      __syncwarp();
     }
-    if (fixed) __syncthreads();
 
-    // this warp's pair: which clip, which frames, where its samples start
-    const bool have = warp < np;                      // warp-uniform
-    const int wseg = warp >= n0 ? 1 : 0;
-    const int wpair = wseg ? warp - n0 : seg[0].q0 + warp;        // pair index inside its clip
-    c32* ex = reinterpret_cast<c32*>(s_ex + warp * kExWarp);
     c32 z[32];                                       // {frame 2q, frame 2q+1} = {re, im} of one complex transform
-    if (have) {
-      const float* w0 = s_wave + (wseg ? seg[1].off + wpair * 2 * a.hop : warp * 2 * a.hop) + lane;
+    {
+      const float* w0 = buf + lane;
       float s[32 + (H32 > 0 ? H32 : 32)];              // frame 2q: s[n2]; frame 2q+1: s[n2 + H32] (or the second half)
       constexpr int kB = H32 > 0 ? H32 : 32;
 #pragma unroll
@@ -298,7 +223,7 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
 #pragma unroll
         for (int j = 0; j < 32; ++j) s[32 + j] = w1[32 * j];
       }
-      // (the asm keeps the compiler from hoisting 32 window values out of the tile loop and spilling them)
+      // (the asm keeps the compiler from hoisting 32 window values out of the pair loop and spilling them)
       asm volatile("" : "+f"(wa), "+f"(wb));
       {
         const float wl = 0.25f + wa, wh = 0.25f - wa;
@@ -314,19 +239,9 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
         z[32 - n2] = pk(wh * s[32 - n2], wh * s[32 - n2 + kB]);
       }
     }
-    // every warp has its samples in registers (and is done with the previous tile) -> warp 0 flushes the
-    // previous tile's statistics, then the next tile's copy may overwrite s_wave
-    if (a.bulk_ok) {
-      if (warp == 0) {
-        asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory");
-        if (a.tile_sums && prev_tile >= 0) flush_stats(prev_tile, (it - 1) & 1);
-        if (lane == 0 && tile + static_cast<int>(gridDim.x) < a.total_tiles) issue_tile(tile + gridDim.x);
-      } else {
-        asm volatile("bar.arrive 1, %0;" ::"n"(kThreads) : "memory");
-      }
-    }
-    prev_tile = tile;
-    if (!have) continue;                             // warp-uniform
+    // the span is in registers: the next pair's copy may overwrite the buffer and lands behind this pair's compute
+    __syncwarp();
+    if (a.bulk_ok && lane == 0 && pair + stride < a.total_pairs) issue(pair + stride);
 
     fft32p(z);                                       // over n2 -> k2, this lane is n1
     {   // inter-stage twiddles W^(n1 k2), k2 = 8a + b: z * t = z * t.re + (i z) * t.im
@@ -411,7 +326,6 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
 
     // ---- bands: add the two edges, fold eps and gain, log, store, statistics
     const int ta = 2 * wpair;
-    const int clip = seg[0].clip + wseg;
     const bool two = ta + 1 < a.T;                   // the last pair of an odd-length clip has one frame
     long long slot = a.slot0 + clip;
     if (a.cap > 0 && slot >= a.cap) slot -= a.cap;
@@ -435,17 +349,15 @@ __global__ void __launch_bounds__(kThreads, 2) logmel_kernel(const LogmelArgs a)
       s1 += l0; s2 = fmaf(l0, l0, s2);
       if (two) { dst[frame_stride] = l1; s1 += l1; s2 = fmaf(l1, l1, s2); }
     }
-    if (a.tile_sums) {                               // per frame pair (sum, sum^2), fixed butterfly order
+    if (a.pair_sums) {                               // per frame pair (sum, sum^2), fixed butterfly order
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         s1 += __shfl_xor_sync(0xffffffffu, s1, o);
         s2 += __shfl_xor_sync(0xffffffffu, s2, o);
       }
-      if (lane == 0) s_red[(it & 1) * kWarps + warp] = make_float2(s1, s2);
+      if (lane == 0) reinterpret_cast<double2*>(a.pair_sums)[pair] = make_double2(s1, s2);
     }
   }
-  __syncthreads();
-  if (a.tile_sums && warp == 0 && prev_tile >= 0) flush_stats(prev_tile, (it - 1) & 1);
 }
 
 // gain[b] = 1 / max(||wave_b||_2, 1e-12): F.normalize(p=2), upstream_dataset.py:62-63
@@ -466,30 +378,19 @@ __global__ void __launch_bounds__(256) wave_l2_gain_kernel(const float* wave, lo
 }
 
 template <int H32>
-int launch_logmel(const LogmelArgs& a, size_t smem, unsigned grid, cudaStream_t st) {
+int launch_logmel(const LogmelArgs& a, size_t smem, unsigned grid, int warps, cudaStream_t st) {
   if (cudaFuncSetAttribute(logmel_kernel<H32>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
     return ASSL_ERR_CUDA;
-  logmel_kernel<H32><<<grid, kThreads, smem, st>>>(a);
+  logmel_kernel<H32><<<grid, warps * 32, smem, st>>>(a);
   return launch_status();
 }
 
 }  // namespace assl
 
-namespace {
-// frame pairs per clip, and how many tiles (parts of tile_sums) can touch one clip
-inline void tiling(int64_t T, int* ppc, int* straddle, int* n_parts) {
-  *ppc = static_cast<int>((T + 1) / 2);
-  *straddle = *ppc >= assl::kWarps ? 1 : 0;
-  *n_parts = *straddle ? (*ppc - 1) / assl::kWarps + 2 : 1;
-}
-}  // namespace
-
 extern "C" int64_t assl_plan_num_tiles(const assl_plan* p, int64_t n_samples) {
   const int64_t t = assl_plan_num_frames(p, n_samples);
   if (t < 0) return -1;
-  int ppc, straddle, n_parts;
-  tiling(t, &ppc, &straddle, &n_parts);
-  return n_parts;
+  return (t + 1) / 2;                 // one (sum, sum^2) entry per frame pair
 }
 
 extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const float* wave_gain, int64_t B,
@@ -500,18 +401,18 @@ extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const floa
   if (!p || !wave || !lms || B < 0 || ld < L || slot0 < 0 || cap < 0) return ASSL_ERR_INVALID_ARG;
   if (L <= p->cfg.n_fft / 2) return ASSL_ERR_INVALID_ARG;       // np.pad(reflect) needs L > n_fft/2
   if (cap > 0 && (B > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
+  if (tile_sums && reinterpret_cast<uintptr_t>(tile_sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;
   if (B == 0) return ASSL_OK;
   const int64_t T = 1 + L / p->cfg.hop;
   LogmelArgs a;
-  tiling(T, &a.ppc, &a.straddle, &a.n_parts);
+  a.ppc = static_cast<int>((T + 1) / 2);
   const int64_t total_pairs = B * a.ppc;
   if (T > (1ll << 24) || total_pairs > (1ll << 30) || L > (1ll << 31) - 4096) return ASSL_ERR_UNSUPPORTED;
-  a.wave = wave; a.gain = wave_gain; a.lms = lms; a.tile_sums = tile_sums;
+  a.wave = wave; a.gain = wave_gain; a.lms = lms; a.pair_sums = tile_sums;
   a.B = static_cast<int>(B); a.L = L; a.ld = ld; a.slot0 = slot0; a.cap = cap;
   a.T = static_cast<int>(T); a.hop = p->cfg.hop; a.n_mels = p->cfg.n_mels;
-  a.total_tiles = a.straddle ? static_cast<int>((total_pairs + kWarps - 1) / kWarps) : static_cast<int>(B);
-  // two spans per tile at most: (16 - 2) hops + 2 windows, each span start rounded to 4 floats
-  a.wave_floats = 2 * kWarps * p->cfg.hop + 2 * kNfft + 8;
+  a.total_pairs = static_cast<int>(total_pairs);
+  a.wave_floats = (kNfft + a.hop + 3) & ~3;
   a.n_iw = p->n_iw; a.n_slots = p->n_slots; a.out_kind = out_kind;
   {   // n / ppc by multiply-high (Granlund-Montgomery, exact for every 32-bit n)
     const unsigned d = static_cast<unsigned>(a.ppc);
@@ -526,14 +427,16 @@ extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const floa
   a.tw = p->d_twiddle;
   a.iv_w = p->d_iv_w;
   a.lane_iv = p->d_lane_iv; a.iv_pos = p->d_iv_pos; a.mconst = p->d_mel_const;
-  const size_t smem = logmel_smem_bytes(a.wave_floats, a.n_iw);
+  // as many warps per CTA (one CTA per SM) as shared memory allows
+  int warps = kMaxWarps;
+  if (const char* e = getenv("ASSL_LOGMEL_WARPS")) { const int w = atoi(e); if (w >= 1 && w <= kMaxWarps) warps = w; }
+  while (warps > 1 && logmel_smem_bytes(warps, a.wave_floats, a.n_iw) > 227 * 1024) --warps;
+  const size_t smem = logmel_smem_bytes(warps, a.wave_floats, a.n_iw);
   if (smem > 227 * 1024) return ASSL_ERR_UNSUPPORTED;
-  // parts of tile_sums no tile writes (a clip touches at most n_parts tiles, usually fewer) must read as zero
-  if (tile_sums && cudaMemsetAsync(tile_sums, 0, sizeof(double) * 2 * B * a.n_parts, as_stream(stream)) != cudaSuccess)
-    return ASSL_ERR_CUDA;
-  const unsigned grid = static_cast<unsigned>(a.total_tiles < 2 * p->sm_count ? a.total_tiles : 2 * p->sm_count);
-  if (a.hop == 160) return launch_logmel<5>(a, smem, grid, as_stream(stream));
-  return launch_logmel<0>(a, smem, grid, as_stream(stream));
+  const int64_t ctas = (total_pairs + warps - 1) / warps;
+  const unsigned grid = static_cast<unsigned>(ctas < p->sm_count ? ctas : p->sm_count);
+  if (a.hop == 160) return launch_logmel<5>(a, smem, grid, warps, as_stream(stream));
+  return launch_logmel<0>(a, smem, grid, warps, as_stream(stream));
 }
 
 extern "C" int assl_wave_l2_gain_f32(const float* wave, int64_t B, int64_t L, int64_t ld, float* gain, void* stream) {

@@ -6,11 +6,14 @@
 // k >= 1 updates  mu_k = mean(m_1..m_k)  (sample 0 is overwritten) and the variance tracker does
 // the same with v_j = mean((x_j - mu_j)^2) = q_j - 2 mu_j m_j + mu_j^2.  Both are prefix means, so the
 // recurrence becomes two block-wide scans over per-clip (m_j, q_j) = (sum x, sum x^2) / elems in fp64.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace assl {
 
 constexpr int kScanThreads = 1024;
+constexpr int kStatCtas = 8;               // CTAs of the running-statistics cluster: 128 clips of a 1024-clip chunk each
 
 // inclusive scan over the block; returns this thread's prefix, *total gets the block total
 __device__ inline double block_scan_incl(double v, double* s_warp, double* total) {
@@ -38,63 +41,98 @@ __device__ inline double block_scan_incl(double v, double* s_warp, double* total
   return v;
 }
 
-// state: [0] n_put  [1] sum of m_j (j>=1)  [2] sum of v_j (j>=1)  [3] mean  [4] std  [5..7] reserved
-__global__ void __launch_bounds__(kScanThreads) running_stats_kernel(
-    double* state, const double* sums, long long n_clips, long long n_parts, double inv_elems,
-    long long max_update, long long first, long long count, float* mean_std, long long slot0, long long cap) {
-  __shared__ double s_warp[32];
-  __shared__ float s_frozen[2];
-  const int tid = threadIdx.x;
-  const long long n0 = static_cast<long long>(state[0]);
-  double carry_m = state[1], carry_v = state[2];
-  if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); }
-  __syncthreads();
-
-  for (long long base = 0; base < n_clips; base += kScanThreads) {
-    const long long idx = base + tid;
-    const bool valid = idx < n_clips;
-    const long long k = n0 + idx;                     // put index of this clip
-    double m = 0.0, q = 0.0;
-    if (valid) {
-      // same left-to-right order as clip_sums_kernel; loads batched four parts at a time (one latency, not four)
-      const double2* sp = reinterpret_cast<const double2*>(sums) + idx * n_parts;
-      double sx = 0.0, sxx = 0.0;
-      long long p = 0;
-      for (; p + 4 <= n_parts; p += 4) {
-        const double2 a = sp[p], b = sp[p + 1], c = sp[p + 2], d = sp[p + 3];
-        sx += a.x; sxx += a.y; sx += b.x; sxx += b.y; sx += c.x; sxx += c.y; sx += d.x; sxx += d.y;
-      }
-      for (; p < n_parts; ++p) { const double2 a = sp[p]; sx += a.x; sxx += a.y; }
-      m = sx * inv_elems;
-      q = sxx * inv_elems;
-    }
-    const bool active = valid && k < max_update;
-    const bool counted = active && k >= 1;
-    double tot;
-    const double pm = block_scan_incl(counted ? m : 0.0, s_warp, &tot) + carry_m;
-    carry_m += tot;
-    const double mu = (k == 0) ? m : pm / static_cast<double>(k);
-    double v = q - 2.0 * mu * m + mu * mu;
-    v = v > 0.0 ? v : 0.0;
-    const double pv = block_scan_incl(counted ? v : 0.0, s_warp, &tot) + carry_v;
-    carry_v += tot;
-    const double s2 = (k == 0) ? v : pv / static_cast<double>(k);
-    float my_mean = 0.f, my_std = 1.f;
-    if (active) {
-      my_mean = static_cast<float>(mu);
-      my_std = fminf(fmaxf(sqrtf(static_cast<float>(s2)), kLogEps), kF32Max);   // clamp(std, eps, max) :281
-      if (k == max_update - 1 || idx == n_clips - 1) { s_frozen[0] = my_mean; s_frozen[1] = my_std; }
-    }
-    __syncthreads();
-    if (valid && !active) { my_mean = s_frozen[0]; my_std = s_frozen[1]; }     // statistics frozen :276
-    if (valid && idx >= first && idx < first + count) {
-      const long long s = ring_slot(slot0, idx - first, cap);
-      mean_std[2 * s] = my_mean;
-      mean_std[2 * s + 1] = my_std;
+// (sum x, sum x^2) of clip ``idx`` over its ``n_parts`` entries, computed by 8 consecutive lanes: lane g adds parts
+// g, g+8, ... in order, then a fixed xor tree.  Every path to a clip total goes through here (the single-GPU scan
+// and the per-rank reduction before the all-gather), so the statistics do not depend on the number of GPUs.
+// All 32 lanes of the warp must call it; clips past n_clips give zeros.
+__device__ inline void clip_total8(const double* sums, long long idx, long long n_clips, long long n_parts, int g,
+                                   double* sx, double* sxx) {
+  double a = 0.0, b = 0.0;
+  if (idx < n_clips) {
+    const double2* sp = reinterpret_cast<const double2*>(sums) + idx * n_parts;
+    const double2 zero = make_double2(0.0, 0.0);
+    for (long long p = g; p < n_parts; p += 32) {  // four loads in flight
+      const double2 v0 = sp[p];
+      const double2 v1 = p + 8 < n_parts ? sp[p + 8] : zero;
+      const double2 v2 = p + 16 < n_parts ? sp[p + 16] : zero;
+      const double2 v3 = p + 24 < n_parts ? sp[p + 24] : zero;
+      a += v0.x; b += v0.y; a += v1.x; b += v1.y; a += v2.x; b += v2.y; a += v3.x; b += v3.y;
     }
   }
-  __syncthreads();
-  if (tid == 0) {
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    b += __shfl_xor_sync(0xffffffffu, b, o);
+  }
+  *sx = a; *sxx = b;
+}
+
+// state: [0] n_put  [1] sum of m_j (j>=1)  [2] sum of v_j (j>=1)  [3] mean  [4] std  [5..7] reserved
+//
+// Launched as ONE thread-block cluster of kStatCtas CTAs: all of them reduce the per-pair sums of their share of
+// the clips (that read is the bulk of the bytes and a single SM cannot keep enough of it in flight), drop the
+// per-clip (m, q) into CTA 0's shared memory through DSMEM, and CTA 0 runs the two block-wide scans.
+__global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads) running_stats_kernel(
+    double* state, const double* sums, long long n_clips, long long n_parts, double inv_elems,
+    long long max_update, long long first, long long count, float* mean_std, long long slot0, long long cap) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned rank = cluster.block_rank();
+  __shared__ double s_warp[32];
+  __shared__ double s_m[kScanThreads], s_q[kScanThreads];
+  __shared__ float s_frozen[2];
+  double* lead_m = cluster.map_shared_rank(s_m, 0);
+  double* lead_q = cluster.map_shared_rank(s_q, 0);
+  const int tid = threadIdx.x;
+  long long n0 = 0;
+  double carry_m = 0.0, carry_v = 0.0;
+  if (rank == 0) {
+    n0 = static_cast<long long>(state[0]);
+    carry_m = state[1]; carry_v = state[2];
+    if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); }
+  }
+
+  for (long long base = 0; base < n_clips; base += kScanThreads) {
+    {   // per-clip totals: 8 lanes per clip read the clip's parts side by side, 128 clips per CTA
+      const long long c = rank * (kScanThreads / 8) + (tid >> 3);
+      double sx, sxx;
+      clip_total8(sums, base + c, n_clips, n_parts, tid & 7, &sx, &sxx);
+      if ((tid & 7) == 0) { lead_m[c] = sx * inv_elems; lead_q[c] = sxx * inv_elems; }
+    }
+    cluster.sync();
+    if (rank == 0) {
+      const long long idx = base + tid;
+      const bool valid = idx < n_clips;
+      const long long k = n0 + idx;                     // put index of this clip
+      const double m = valid ? s_m[tid] : 0.0, q = valid ? s_q[tid] : 0.0;
+      const bool active = valid && k < max_update;
+      const bool counted = active && k >= 1;
+      double tot;
+      const double pm = block_scan_incl(counted ? m : 0.0, s_warp, &tot) + carry_m;
+      carry_m += tot;
+      const double mu = (k == 0) ? m : pm / static_cast<double>(k);
+      double v = q - 2.0 * mu * m + mu * mu;
+      v = v > 0.0 ? v : 0.0;
+      const double pv = block_scan_incl(counted ? v : 0.0, s_warp, &tot) + carry_v;
+      carry_v += tot;
+      const double s2 = (k == 0) ? v : pv / static_cast<double>(k);
+      float my_mean = 0.f, my_std = 1.f;
+      if (active) {
+        my_mean = static_cast<float>(mu);
+        my_std = fminf(fmaxf(sqrtf(static_cast<float>(s2)), kLogEps), kF32Max);   // clamp(std, eps, max) :281
+        if (k == max_update - 1 || idx == n_clips - 1) { s_frozen[0] = my_mean; s_frozen[1] = my_std; }
+      }
+      __syncthreads();
+      if (valid && !active) { my_mean = s_frozen[0]; my_std = s_frozen[1]; }     // statistics frozen :276
+      if (valid && idx >= first && idx < first + count) {
+        const long long s = ring_slot(slot0, idx - first, cap);
+        mean_std[2 * s] = my_mean;
+        mean_std[2 * s + 1] = my_std;
+      }
+    }
+    cluster.sync();       // CTA 0 is done with (m, q) before the next chunk lands; nobody leaves while peers still write
+  }
+  if (rank == 0 && tid == 0) {
     long long n1 = n0;
     if (n0 < max_update) n1 = (n0 + n_clips < max_update) ? n0 + n_clips : max_update;
     state[0] = static_cast<double>(n1);
@@ -105,13 +143,11 @@ __global__ void __launch_bounds__(kScanThreads) running_stats_kernel(
   }
 }
 
-__global__ void clip_sums_kernel(const double* tile_sums, long long B, long long n_parts, double* clip_sums) {
-  const long long b = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
-  if (b >= B) return;
-  double sx = 0.0, sxx = 0.0;
-  for (long long p = 0; p < n_parts; ++p) { sx += tile_sums[(b * n_parts + p) * 2]; sxx += tile_sums[(b * n_parts + p) * 2 + 1]; }
-  clip_sums[2 * b] = sx;
-  clip_sums[2 * b + 1] = sxx;
+__global__ void __launch_bounds__(256) clip_sums_kernel(const double* tile_sums, long long B, long long n_parts, double* clip_sums) {
+  const long long b = blockIdx.x * 32ll + (threadIdx.x >> 3);          // 8 lanes per clip
+  double sx, sxx;
+  clip_total8(tile_sums, b, B, n_parts, threadIdx.x & 7, &sx, &sxx);
+  if (b < B && (threadIdx.x & 7) == 0) { clip_sums[2 * b] = sx; clip_sums[2 * b + 1] = sxx; }
 }
 
 // per-clip (sum x, sum x^2) in fp64, one CTA per clip
@@ -198,7 +234,7 @@ extern "C" int assl_running_stats(double* state, const double* sums, int64_t n_c
   if (cap > 0 && (count > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
   if (reinterpret_cast<uintptr_t>(sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;   // (sum, sum^2) pairs are read as one 16-byte word
   if (n_clips == 0) return ASSL_OK;
-  running_stats_kernel<<<1, kScanThreads, 0, as_stream(stream)>>>(state, sums, n_clips, n_parts, 1.0 / static_cast<double>(elems),
+  running_stats_kernel<<<kStatCtas, kScanThreads, 0, as_stream(stream)>>>(state, sums, n_clips, n_parts, 1.0 / static_cast<double>(elems),
                                                                   max_update, first, count, mean_std, slot0, cap);
   return launch_status();
 }
@@ -223,8 +259,9 @@ extern "C" int assl_clip_normalize_f32(const float* x, float* y, int64_t B, int6
 
 extern "C" int assl_clip_sums(const double* tile_sums, int64_t B, int64_t n_parts, double* clip_sums, void* stream) {
   if (!tile_sums || !clip_sums || B < 0 || n_parts < 1) return ASSL_ERR_INVALID_ARG;
+  if (reinterpret_cast<uintptr_t>(tile_sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;
   if (B == 0) return ASSL_OK;
-  assl::clip_sums_kernel<<<static_cast<unsigned>((B + 255) / 256), 256, 0, assl::as_stream(stream)>>>(tile_sums, B, n_parts, clip_sums);
+  assl::clip_sums_kernel<<<static_cast<unsigned>((B + 31) / 32), 256, 0, assl::as_stream(stream)>>>(tile_sums, B, n_parts, clip_sums);
   return assl::launch_status();
 }
 
