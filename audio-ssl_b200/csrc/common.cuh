@@ -38,14 +38,12 @@ struct assl_plan {
   assl_cfg cfg;
   int device;
   int sm_count;
-  int n_iw;                     // stored filterbank weight pairs (interval form, see plan.cu)
   int n_slots;                  // interval parts a lane owns in the log-mel kernel (rows of d_lane_iv in use)
   float2* d_twiddle;            // [32][32]     tw[k2][n1] = exp(-2 pi i n1 k2 / 1024)
-  float2* d_iv_w;               // [n_iw]       {falling-edge weight of band j-1, rising-edge weight of band j}
-  int4* d_lane_iv;              // [slots][32]  interval owned by (slot, lane) in the log-mel kernel:
-                                //              {first bin (even), bin pairs, offset into d_iv_w (even),
-                                //               scratch entry | starts-the-total << 16, or -1}
-  float* d_mel_const;           // [n_mels]     2.22e-16 * sum of the band's weights (folded "+ eps" of utils.py:28)
+  int4* d_lane_iv;              // [slots][32]  interval part owned by (slot, lane) in the log-mel kernel:
+                                //              {first bin (even) | valid-bin mask << 10 | scratch entry << 18 |
+                                //               starts-the-total << 26 | owns-a-part << 27, alpha, beta, 0}
+  float2* d_mel_const;          // [n_mels]     {enorm, 2.22e-16 * sum of the band's weights (folded "+ eps" of utils.py:28)}
   std::vector<float> h_fb;      // dense [n_mels][513] copy for assl_plan_filterbank
   std::vector<int4> h_lane_iv;  // host copy of d_lane_iv
   std::vector<int> h_iv_pos;    // [n_mels+1] scratch entry of every interval's total

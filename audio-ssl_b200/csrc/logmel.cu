@@ -67,22 +67,19 @@ struct LogmelArgs {
   int ppc_sh1, ppc_sh2;
   int total_pairs;
   int wave_floats;    // per-warp staging buffer (n_fft + hop, rounded up to 4)
-  int n_iw;           // float2 entries of iv_w
   int n_slots;        // rows of lane_iv in use
   const float2* tw;
-  const float2* iv_w;    // {falling-edge weight of band j-1, rising-edge weight of band j} per bin
-  const int4* lane_iv;   // [kIvSlots][32] interval owned by (slot, lane): {first bin, bin pairs, offset in iv_w, id or -1}
+  const int4* lane_iv;   // [kIvSlots][32] interval part owned by (slot, lane), see assl_plan::d_lane_iv
   const int* iv_pos;     // [n_mels + 1] scratch entry holding interval j's total
-  const float* mconst;   // [n_mels] 2.22e-16 * sum of the band's weights (the "+ eps" of utils.py:28, folded)
+  const float2* mconst;  // [n_mels] {enorm, 2.22e-16 * sum of the band's weights (the "+ eps" of utils.py:28, folded)}
 };
 
-__host__ __device__ inline size_t logmel_smem_bytes(int warps, int wave_floats, int n_iw) {
+__host__ __device__ inline size_t logmel_smem_bytes(int warps, int wave_floats) {
   size_t b = 0;
   b += sizeof(float2) * warps * kExWarp;    // exchange / power / interval-sum buffers
   b += sizeof(float2) * 32 * kTwStride;     // twiddles
   b += sizeof(float) * warps * wave_floats; // staging
-  b += sizeof(float2) * ((n_iw + 1) & ~1);
-  b += sizeof(float) * kMaxMels;            // per-band folded eps
+  b += sizeof(float2) * kMaxMels;           // per-band {enorm, folded eps}
   b += sizeof(int4) * kIvSlots * 32;        // interval ownership
   b += sizeof(int) * (kMaxMels + 4);        // scratch entry per interval
   b += sizeof(unsigned long long) * kMaxWarps;   // one mbarrier per warp
@@ -105,6 +102,11 @@ __device__ __forceinline__ void mbar_wait(void* bar, unsigned parity) {
       "@p bra DONE_%=;\n\t"
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ ulonglong2 lds128(unsigned addr) {
+  ulonglong2 v;
+  asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(addr) : "memory");
+  return v;
 }
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, void* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -140,8 +142,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   float2* s_ex = reinterpret_cast<float2*>(smem_raw);
   float2* s_tw = s_ex + n_warps * kExWarp;
   float* s_wave = reinterpret_cast<float*>(s_tw + 32 * kTwStride);
-  float2* s_ivw = reinterpret_cast<float2*>(s_wave + n_warps * a.wave_floats);
-  float* s_mconst = reinterpret_cast<float*>(s_ivw + ((a.n_iw + 1) & ~1));
+  float2* s_mconst = reinterpret_cast<float2*>(s_wave + n_warps * a.wave_floats);
   int4* s_lane = reinterpret_cast<int4*>(s_mconst + kMaxMels);             // [kIvSlots][32]
   int* s_pos = reinterpret_cast<int*>(s_lane + kIvSlots * 32);              // [n_mels + 1]
   unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_pos + kMaxMels + 4);
@@ -166,11 +167,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   float wa, wb;
   sincospif(static_cast<float>(lane) * (1.0f / 512.0f), &wb, &wa);
   wa *= -0.25f; wb *= 0.25f;
-  for (int i = tid; i < a.n_iw; i += n_threads) s_ivw[i] = a.iv_w[i];
   for (int i = tid; i < a.n_mels; i += n_threads) s_mconst[i] = a.mconst[i];
   for (int i = tid; i < kIvSlots * 32; i += n_threads) s_lane[i] = a.lane_iv[i];
   for (int i = tid; i <= a.n_mels; i += n_threads) s_pos[i] = a.iv_pos[i];
-  // padded power reads (zero weights) must see finite values: the row padding of s_ex is never written again
+  // (the row padding of s_ex is never written again; bins a part does not own are masked out, not multiplied)
   for (int i = tid; i < n_warps * kExWarp; i += n_threads) s_ex[i] = make_float2(0.f, 0.f);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();                                   // the only CTA-wide barrier
@@ -296,29 +296,30 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
     }
     __syncwarp();                                    // both power spectra are in the warp's buffer
 
-    // ---- filterbank, interval form.  Interval j = bins between the centres of bands j-1 and j; its bins feed
-    //      the falling edge of band j-1 (weight .x) and the rising edge of band j (weight .y).
-    //      Interval totals {Sd(j), Su(j)} live behind the power spectra, one 16-byte entry each at a
-    //      plan-chosen position; band m = Su(m) + Sd(m+1).
+    // ---- filterbank, interval form.  Interval j = bins between the centres of bands j-1 and j; bin k there has
+    //      weight enorm(j-1) (1 - t) in band j-1 and enorm(j) t in band j, t linear in k (plan.cu).  A lane owns
+    //      one part (kPartBins bins) of an interval per slot: S0 = sum P, S1 = sum r P over the part's own bins,
+    //      U = sum t P = alpha S1 + beta S0, D = S0 - U.  Interval totals {D(j), U(j)} live behind the power
+    //      spectra, one 16-byte entry each at a plan-chosen position; band m = enorm(m) (U(m) + D(m+1)).
     c32* scratch = ex + kScratch;
     for (int s = 0; s < a.n_slots; ++s) {
       const int4 iv = s_lane[s * 32 + lane];         // the same interval parts for the whole launch
-      const ulonglong2* wv = reinterpret_cast<const ulonglong2*>(s_ivw + iv.z);
-      const ulonglong2* pv = reinterpret_cast<const ulonglong2*>(ex + iv.x);
-      c32 d0 = pk(0.f, 0.f), u0 = d0, d1 = d0, u1 = d0;   // {frame 2q, frame 2q+1}; even / odd bins apart
+      const unsigned pv = smem_u32(ex + (iv.x & 0x3ff));
+      const int vm = iv.x >> 10;                     // bits 0..7: which of the part's bins belong to the interval
+      c32 s0a = pk(0.f, 0.f), s0b = s0a, s1a = s0a, s1b = s0a;   // {frame 2q, frame 2q+1}; even / odd bins apart
 #pragma unroll
-      for (int j = 0; j < kPartBins / 2; ++j) {      // every part has kPartBins bins (zero weights pad it)
-        const ulonglong2 w = wv[j];
-        const ulonglong2 p = pv[j];
-        d0 = fma2(bc(lo_of(w.x)), p.x, d0);
-        u0 = fma2(bc(hi_of(w.x)), p.x, u0);
-        d1 = fma2(bc(lo_of(w.y)), p.y, d1);
-        u1 = fma2(bc(hi_of(w.y)), p.y, u1);
+      for (int j = 0; j < kPartBins / 2; ++j) {
+        const ulonglong2 p = lds128(pv + 16 * j);     // (kept whole: the plan's dealing of parts to quarter-warps makes
+                                                      //  the 128-bit form conflict-free, not the 64-bit halves)
+        if (vm & (1 << (2 * j))) { s0a = add2(s0a, p.x); if (j) s1a = fma2(bc(static_cast<float>(2 * j)), p.x, s1a); }
+        if (vm & (2 << (2 * j))) { s0b = add2(s0b, p.y); s1b = fma2(bc(static_cast<float>(2 * j + 1)), p.y, s1b); }
       }
-      if (iv.w >= 0) {                               // parts of one interval sit in different slots: fixed order
-        ulonglong2* tot = reinterpret_cast<ulonglong2*>(scratch) + (iv.w & 0xffff);
-        c32 sd = add2(d0, d1), su = add2(u0, u1);
-        if (!(iv.w >> 16)) { const ulonglong2 o = *tot; sd = add2(o.x, sd); su = add2(o.y, su); }
+      if (iv.x & (1 << 27)) {                        // parts of one interval sit in different slots: fixed order
+        const c32 S0 = add2(s0a, s0b), S1 = add2(s1a, s1b);
+        c32 su = fma2(bc(__int_as_float(iv.y)), S1, mul2(bc(__int_as_float(iv.z)), S0));
+        c32 sd = sub2(S0, su);
+        ulonglong2* tot = reinterpret_cast<ulonglong2*>(scratch) + ((iv.x >> 18) & 0xff);
+        if (!(iv.x & (1 << 26))) { const ulonglong2 o = *tot; sd = add2(o.x, sd); su = add2(o.y, su); }
         *tot = make_ulonglong2(sd, su);
       }
       __syncwarp();
@@ -339,9 +340,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
       const c32 su = scratch[2 * s_pos[m] + 1], sd = scratch[2 * s_pos[m + 1]];   // rising edge + falling edge
       float acc0, acc1;
       upk(add2(su, sd), acc0, acc1);
-      const float c = s_mconst[m];
-      acc0 = fmaf(acc0, g2, c);
-      acc1 = fmaf(acc1, g2, c);
+      const float2 c = s_mconst[m];                  // {enorm, folded eps}
+      const float e = c.x * g2;
+      acc0 = fmaf(acc0, e, c.y);
+      acc1 = fmaf(acc1, e, c.y);
       const float l0 = power ? acc0 : __logf(acc0 + kLogEps);
       const float l1 = power ? acc1 : __logf(acc1 + kLogEps);
       float* dst = out + m * band_stride;
@@ -413,7 +415,7 @@ extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const floa
   a.T = static_cast<int>(T); a.hop = p->cfg.hop; a.n_mels = p->cfg.n_mels;
   a.total_pairs = static_cast<int>(total_pairs);
   a.wave_floats = (kNfft + a.hop + 3) & ~3;
-  a.n_iw = p->n_iw; a.n_slots = p->n_slots; a.out_kind = out_kind;
+  a.n_slots = p->n_slots; a.out_kind = out_kind;
   {   // n / ppc by multiply-high (Granlund-Montgomery, exact for every 32-bit n)
     const unsigned d = static_cast<unsigned>(a.ppc);
     int l = 0;
@@ -425,13 +427,12 @@ extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const floa
   // the bulk (TMA) copy needs 16-byte aligned global addresses: clip starts and span starts (2*q*hop - 512)
   a.bulk_ok = (reinterpret_cast<uintptr_t>(wave) % 16 == 0) && (ld % 4 == 0) && (p->cfg.hop % 2 == 0);
   a.tw = p->d_twiddle;
-  a.iv_w = p->d_iv_w;
   a.lane_iv = p->d_lane_iv; a.iv_pos = p->d_iv_pos; a.mconst = p->d_mel_const;
   // as many warps per CTA (one CTA per SM) as shared memory allows
   int warps = kMaxWarps;
   if (const char* e = getenv("ASSL_LOGMEL_WARPS")) { const int w = atoi(e); if (w >= 1 && w <= kMaxWarps) warps = w; }
-  while (warps > 1 && logmel_smem_bytes(warps, a.wave_floats, a.n_iw) > 227 * 1024) --warps;
-  const size_t smem = logmel_smem_bytes(warps, a.wave_floats, a.n_iw);
+  while (warps > 1 && logmel_smem_bytes(warps, a.wave_floats) > 227 * 1024) --warps;
+  const size_t smem = logmel_smem_bytes(warps, a.wave_floats);
   if (smem > 227 * 1024) return ASSL_ERR_UNSUPPORTED;
   const int64_t ctas = (total_pairs + warps - 1) / warps;
   const unsigned grid = static_cast<unsigned>(ctas < p->sm_count ? ctas : p->sm_count);

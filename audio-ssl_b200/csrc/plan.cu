@@ -95,11 +95,12 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
       p->h_fb[static_cast<size_t>(m) * n_bins + k] = static_cast<float>(static_cast<double>(w32) * enorm);
     }
   }
-  // sparse "interval" form.  Interval j (0..n_mels) = bins with centre(j-1) < f_k <= centre(j); a bin there
-  // has weight only in band j-1 (falling edge, .x) and band j (rising edge, .y).  Each interval keeps a private
-  // weight run trimmed to its non-zero bins and widened with zero weights to an even first bin and an even
-  // length, so the kernel reads two bins and two weight pairs per 128-bit load; a run may then end on index
-  // 513, one past Nyquist, which the kernel keeps at zero power.
+  // sparse "interval" form.  Interval j (0..n_mels) = bins with centre(j-1) < f_k <= centre(j), centre(j) =
+  // mel_f[j+1]; a bin there has weight only in band j-1 (falling edge) and band j (rising edge), and both are
+  // linear in the bin index:  with t = (f_k - mel_f[j]) / (mel_f[j+1] - mel_f[j])  they are  enorm(j-1) (1 - t)
+  // and  enorm(j) t.  The kernel therefore needs no weight table: a lane adds up  S0 = sum P_k  and
+  // S1 = sum r P_k  over the interval's bins it owns (r = bin index inside its part), forms  U = sum t P =
+  // alpha S1 + beta S0  and  D = S0 - U, and band m = enorm(m) (U(m) + D(m+1)).
   const int n_iv = n_mels + 1;
   std::vector<int> bin_iv(n_bins);
   for (int k = 0; k < n_bins; ++k) {
@@ -110,29 +111,25 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
     for (int m = 0; m < n_mels; ++m)     // the triangles must overlap only with their neighbours
       if (m != j && m != j - 1 && p->h_fb[static_cast<size_t>(m) * n_bins + k] != 0.f) { delete p; return ASSL_ERR_UNSUPPORTED; }
   }
-  std::vector<int> k0(n_iv, 0), cnt(n_iv, 0), off(n_iv, 0);
-  std::vector<float2> w;
+  // an interval's run: trimmed to its non-zero bins, widened to an even first bin (128-bit power loads) and to
+  // whole parts of kPartBins bins; the bins of a part that are not the interval's are masked out in the kernel
+  std::vector<int> k0(n_iv, 0), cnt(n_iv, 0);
+  auto bin_in = [&](int j, int k) {
+    if (k >= n_bins || bin_iv[k] != j) return false;
+    const float wd = j >= 1 ? p->h_fb[static_cast<size_t>(j - 1) * n_bins + k] : 0.f;
+    const float wu = j < n_mels ? p->h_fb[static_cast<size_t>(j) * n_bins + k] : 0.f;
+    return wd != 0.f || wu != 0.f;
+  };
   for (int j = 0; j < n_iv; ++j) {
-    auto wd = [&](int k) { return j >= 1 ? p->h_fb[static_cast<size_t>(j - 1) * n_bins + k] : 0.f; };
-    auto wu = [&](int k) { return j < n_mels ? p->h_fb[static_cast<size_t>(j) * n_bins + k] : 0.f; };
     int lo = n_bins, hi = -1;
     for (int k = 0; k < n_bins; ++k)
-      if (bin_iv[k] == j && (wd(k) != 0.f || wu(k) != 0.f)) { lo = lo < k ? lo : k; hi = k; }
-    if (hi < 0) { off[j] = static_cast<int>(w.size()); continue; }
+      if (bin_in(j, k)) { lo = lo < k ? lo : k; hi = k; }
+    if (hi < 0) continue;
     const int first = lo & ~1;
     int n = hi - first + 1;
-    n = (n + assl::kPartBins - 1) / assl::kPartBins * assl::kPartBins;   // whole parts, see below
+    n = (n + assl::kPartBins - 1) / assl::kPartBins * assl::kPartBins;
     k0[j] = first;
     cnt[j] = n;
-    // a lane reads 16 bytes of power (bins k0 + 2i, k0 + 2i + 1) and 16 bytes of weights per step: start the
-    // weight run in the same 16-byte bank group (mod 128 bytes) as the power run, so lanes whose power reads
-    // do not collide do not collide on the weights either
-    while (((w.size() / 2) & 7) != ((static_cast<size_t>(first) / 2) & 7)) { w.push_back(make_float2(0.f, 0.f)); w.push_back(make_float2(0.f, 0.f)); }
-    off[j] = static_cast<int>(w.size());
-    for (int k = first; k < first + n; ++k) {
-      const bool in = k < n_bins && bin_iv[k] == j;
-      w.push_back(in ? make_float2(wd(k), wu(k)) : make_float2(0.f, 0.f));
-    }
   }
   // Lanes of the log-mel kernel own pieces of intervals for the whole launch.  Every interval is cut into
   // parts of exactly kPartBins bins (its weight run is zero-padded to whole parts), so all lanes run the
@@ -142,16 +139,14 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
   // bank groups: parts are dealt to the quarter-warps round-robin in order of bank group, so a quarter sees
   // a group twice only when more parts share it than there are quarters.
   {
-    struct Part { int k0, off, iv; };
+    struct Part { int k0, iv; };
     std::vector<Part> parts;
-    const int zero_off = static_cast<int>(w.size());           // a zero weight run for idle lanes
-    for (int i = 0; i < assl::kPartBins; ++i) w.push_back(make_float2(0.f, 0.f));
     for (int j = 0; j < n_iv; ++j)
       for (int c = 0; c < (cnt[j] > 0 ? cnt[j] : 1); c += assl::kPartBins)
-        parts.push_back({cnt[j] > 0 ? k0[j] + c : 0, cnt[j] > 0 ? off[j] + c : zero_off, j});
+        parts.push_back({cnt[j] > 0 ? k0[j] + c : 0, j});
     const int n_slots = (static_cast<int>(parts.size()) + 31) / 32;
     if (n_slots > assl::kIvSlots) { delete p; return ASSL_ERR_UNSUPPORTED; }
-    while (static_cast<int>(parts.size()) < 32 * n_slots) parts.push_back({0, zero_off, -1});
+    while (static_cast<int>(parts.size()) < 32 * n_slots) parts.push_back({0, -1});
     auto group = [](const Part& x) { return (x.k0 / 2) & 7; };
     std::stable_sort(parts.begin(), parts.end(), [&](const Part& x, const Part& y) { return group(x) < group(y); });
     const int n_q = 4 * n_slots;                                 // quarter-warps over all slots
@@ -220,26 +215,35 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
     int n_pos = 0;
     for (int j = 0; j < n_iv; ++j) n_pos = n_pos > pos[j] + 1 ? n_pos : pos[j] + 1;
     if (n_pos > assl::kScratchEntries) { delete p; return ASSL_ERR_UNSUPPORTED; }
-    std::vector<int4> lane_iv(static_cast<size_t>(32) * assl::kIvSlots, make_int4(0, 0, zero_off, -1));
+    // {first bin | valid-bin mask << 10 | scratch entry << 18 | starts-the-total << 26 | owns-an-interval << 27,
+    //  alpha, beta (fp32 bits), 0}:  t of the part's bin r is alpha r + beta
+    std::vector<int4> lane_iv(static_cast<size_t>(32) * assl::kIvSlots, make_int4(0, 0, 0, 0));
+    const double df = sr / n_fft;
     for (int q = 0; q < n_q; ++q)
       for (size_t i = 0; i < quarter[q].size(); ++i) {
         const Part& x = quarter[q][i];
         const int sl = slot_of(q), lane = (q / n_slots) * 8 + static_cast<int>(i);
-        const int tag = x.iv < 0 ? -1 : (pos[x.iv] | ((first_slot[x.iv] == sl ? 1 : 0) << 16));   // bit 16: starts the total
-        lane_iv[static_cast<size_t>(sl) * 32 + lane] = make_int4(x.k0, assl::kPartBins / 2, x.off, tag);
+        if (x.iv < 0) continue;
+        int vm = 0;
+        for (int r = 0; r < assl::kPartBins; ++r) vm |= (bin_in(x.iv, x.k0 + r) ? 1 : 0) << r;
+        const double width = mel_f[x.iv + 1] - mel_f[x.iv];
+        const float alpha = static_cast<float>(df / width), beta = static_cast<float>((x.k0 * df - mel_f[x.iv]) / width);
+        int ia, ib;
+        std::memcpy(&ia, &alpha, 4); std::memcpy(&ib, &beta, 4);
+        const int word = x.k0 | (vm << 10) | (pos[x.iv] << 18) | ((first_slot[x.iv] == sl ? 1 : 0) << 26) | (1 << 27);
+        lane_iv[static_cast<size_t>(sl) * 32 + lane] = make_int4(word, ia, ib, 0);
       }
     p->h_iv_pos = pos;
     p->n_slots = n_slots;
     p->h_lane_iv = lane_iv;
   }
-  std::vector<float> mconst(n_mels);
+  // per band {area normalisation enorm(m), 2.22e-16 * sum of the band's weights (the "+ eps" of utils.py:28, folded)}
+  std::vector<float2> mconst(n_mels);
   for (int m = 0; m < n_mels; ++m) {
     float acc = 0.f;
     for (int k = 0; k < n_bins; ++k) acc += p->h_fb[static_cast<size_t>(m) * n_bins + k] * assl::kPowerEps;
-    mconst[m] = acc;
+    mconst[m] = make_float2(static_cast<float>(2.0 / (mel_f[m + 2] - mel_f[m])), acc);
   }
-  if (w.empty()) w.push_back(make_float2(0.f, 0.f));
-  p->n_iw = static_cast<int>(w.size());
 
   // ---- window: scipy get_window('hann', fftbins=True) = 0.5 - 0.5 cos(2 pi n / n_fft) needs no table; the
   //      kernel evaluates it (times the 1/2 of the two-frame unpack) from one sin/cos pair per lane
@@ -252,7 +256,6 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
     }
 
   int rc = upload(&p->d_twiddle, tw);
-  if (rc == ASSL_OK) rc = upload(&p->d_iv_w, w);
   if (rc == ASSL_OK) rc = upload(&p->d_lane_iv, p->h_lane_iv);
   if (rc == ASSL_OK) rc = upload(&p->d_iv_pos, p->h_iv_pos);
   if (rc == ASSL_OK) rc = upload(&p->d_mel_const, mconst);
@@ -264,7 +267,6 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
 extern "C" int assl_plan_destroy(assl_plan* p) {
   if (!p) return ASSL_OK;
   cudaFree(p->d_twiddle);
-  cudaFree(p->d_iv_w);
   cudaFree(p->d_lane_iv);
   cudaFree(p->d_iv_pos);
   cudaFree(p->d_mel_const);
