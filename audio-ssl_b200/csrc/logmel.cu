@@ -311,8 +311,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
       for (int j = 0; j < kPartBins / 2; ++j) {
         const ulonglong2 p = lds128(pv + 16 * j);     // (kept whole: the plan's dealing of parts to quarter-warps makes
                                                       //  the 128-bit form conflict-free, not the 64-bit halves)
-        if (vm & (1 << (2 * j))) { s0a = add2(s0a, p.x); if (j) s1a = fma2(bc(static_cast<float>(2 * j)), p.x, s1a); }
-        if (vm & (2 << (2 * j))) { s0b = add2(s0b, p.y); s1b = fma2(bc(static_cast<float>(2 * j + 1)), p.y, s1b); }
+        const c32 x0 = (vm & (1 << (2 * j))) ? p.x : 0ull, x1 = (vm & (2 << (2 * j))) ? p.y : 0ull;   // foreign bins -> 0
+        s0a = add2(s0a, x0); if (j) s1a = fma2(bc(static_cast<float>(2 * j)), x0, s1a);
+        s0b = add2(s0b, x1); s1b = fma2(bc(static_cast<float>(2 * j + 1)), x1, s1b);
       }
       if (iv.x & (1 << 27)) {                        // parts of one interval sit in different slots: fixed order
         const c32 S0 = add2(s0a, s0b), S1 = add2(s1a, s1b);
