@@ -8,6 +8,9 @@
 // recurrence becomes two block-wide scans over per-clip (m_j, q_j) = (sum x, sum x^2) / elems in fp64.
 #include <cooperative_groups.h>
 
+#include <cstring>
+#include <new>
+
 #include "common.cuh"
 
 namespace assl {
@@ -67,6 +70,28 @@ __device__ inline void clip_total8(const double* sums, long long idx, long long 
   *sx = a; *sxx = b;
 }
 
+// Peer-memory exchange of the per-clip sums (assl_running_stats_exchange): where every rank's buffers of the
+// current parity are, as mapped into this process.
+struct PeerArgs {
+  int world = 0;                 // 0 = single process, no exchange
+  int rank = 0;
+  long long b_local = 0;         // clips of this rank (the same on every rank)
+  long long n_parts_local = 0;
+  const double* pair_sums = nullptr;                          // this rank's [b_local, n_parts_local, 2]
+  unsigned long long seq = 0;                                 // this call's number, what the flags are raised to
+  double2* peer_sums[ASSL_EXCHANGE_MAX_WORLD] = {};           // rank j's gathered [world * b_local] buffer
+  unsigned long long* peer_flags[ASSL_EXCHANGE_MAX_WORLD] = {};   // rank j's flags [world]: slice of rank i has landed
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
 // state: [0] n_put  [1] sum of m_j (j>=1)  [2] sum of v_j (j>=1)  [3] mean  [4] std  [5..7] reserved
 //
 // Launched as ONE thread-block cluster of kStatCtas CTAs: all of them reduce the per-pair sums of their share of
@@ -74,7 +99,8 @@ __device__ inline void clip_total8(const double* sums, long long idx, long long 
 // per-clip (m, q) into CTA 0's shared memory through DSMEM, and CTA 0 runs the two block-wide scans.
 __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads) running_stats_kernel(
     double* state, const double* sums, long long n_clips, long long n_parts, double inv_elems,
-    long long max_update, long long first, long long count, float* mean_std, long long slot0, long long cap) {
+    long long max_update, long long first, long long count, float* mean_std, long long slot0, long long cap,
+    const PeerArgs px) {
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned rank = cluster.block_rank();
@@ -90,6 +116,36 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
     n0 = static_cast<long long>(state[0]);
     carry_m = state[1]; carry_v = state[2];
     if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); }
+  }
+
+  if (px.world > 0) {
+    // ---- exchange: totals of this rank's clips -> the slice [rank * b_local, ...) of EVERY rank's buffer (stores
+    //      over NVLink for the peers), then one flag per peer with system-scope release; then wait until every
+    //      rank's slice has landed here.  The scan below then reads the local buffer (sums, n_parts = 1).
+    __shared__ int s_late;
+    if (tid == 0) s_late = 0;
+    for (long long base = 0; base < px.b_local; base += kScanThreads) {
+      const long long idx = base + rank * (kScanThreads / 8) + (tid >> 3);
+      double sx, sxx;
+      clip_total8(px.pair_sums, idx, px.b_local, px.n_parts_local, tid & 7, &sx, &sxx);
+      if ((tid & 7) == 0 && idx < px.b_local) {
+        const double2 v = make_double2(sx, sxx);
+        for (int j = 0; j < px.world; ++j) px.peer_sums[j][px.rank * px.b_local + idx] = v;
+      }
+    }
+    __threadfence_system();
+    cluster.sync();                                  // every CTA's stores are fenced before the flags go up
+    if (rank == 0 && tid < px.world) st_release_sys(px.peer_flags[tid] + px.rank, px.seq);
+    if (tid < px.world) {
+      const unsigned long long* f = px.peer_flags[px.rank] + tid;
+      const long long t0 = clock64();
+      while (ld_acquire_sys(f) < px.seq) {
+        if (clock64() - t0 > 4000000000ll) { s_late = 1; break; }   // ~2 s: a peer is gone; do not hang the GPU
+        __nanosleep(100);
+      }
+    }
+    __syncthreads();
+    if (rank == 0 && tid == 0 && s_late) state[7] = 1.0;
   }
 
   for (long long base = 0; base < n_clips; base += kScanThreads) {
@@ -235,7 +291,7 @@ extern "C" int assl_running_stats(double* state, const double* sums, int64_t n_c
   if (reinterpret_cast<uintptr_t>(sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;   // (sum, sum^2) pairs are read as one 16-byte word
   if (n_clips == 0) return ASSL_OK;
   running_stats_kernel<<<kStatCtas, kScanThreads, 0, as_stream(stream)>>>(state, sums, n_clips, n_parts, 1.0 / static_cast<double>(elems),
-                                                                  max_update, first, count, mean_std, slot0, cap);
+                                                                  max_update, first, count, mean_std, slot0, cap, PeerArgs());
   return launch_status();
 }
 
@@ -284,4 +340,84 @@ extern "C" int assl_affine_norm_f32(const float* x, float* y, int64_t n, float m
   if (n == 0) return ASSL_OK;
   assl::affine_norm_kernel<<<assl::ew_grid(n), 256, 0, assl::as_stream(stream)>>>(x, y, n, mean, std);
   return assl::launch_status();
+}
+
+// ---- peer-memory exchange object -------------------------------------------------------------------------
+struct assl_exchange {
+  int rank = 0, world = 0;
+  long long max_clips = 0;
+  unsigned char* local = nullptr;                         // this rank's buffer (cudaMalloc: IPC-exportable)
+  unsigned char* peer[ASSL_EXCHANGE_MAX_WORLD] = {};       // every rank's buffer as mapped here (peer[rank] = local)
+  size_t sums_bytes = 0, bytes = 0;                       // per parity: [world * max_clips] double2; then 2 x flags
+  unsigned long long seq = 0;
+  bool connected = false;
+};
+
+extern "C" int assl_exchange_create(assl_exchange** out, int32_t rank, int32_t world, int64_t max_clips, void* handle_out) {
+  if (!out || !handle_out || world < 2 || world > ASSL_EXCHANGE_MAX_WORLD || rank < 0 || rank >= world || max_clips < 1)
+    return ASSL_ERR_INVALID_ARG;
+  static_assert(sizeof(cudaIpcMemHandle_t) == ASSL_EXCHANGE_HANDLE_BYTES, "IPC handle size");
+  *out = nullptr;
+  assl_exchange* x = new (std::nothrow) assl_exchange();
+  if (!x) return ASSL_ERR_CUDA;
+  x->rank = rank; x->world = world; x->max_clips = max_clips;
+  x->sums_bytes = (sizeof(double2) * static_cast<size_t>(world) * max_clips + 255) & ~static_cast<size_t>(255);
+  x->bytes = 2 * x->sums_bytes + 2 * sizeof(unsigned long long) * ASSL_EXCHANGE_MAX_WORLD;
+  cudaIpcMemHandle_t h;
+  if (cudaMalloc(reinterpret_cast<void**>(&x->local), x->bytes) != cudaSuccess || cudaMemset(x->local, 0, x->bytes) != cudaSuccess ||
+      cudaIpcGetMemHandle(&h, x->local) != cudaSuccess) {
+    cudaFree(x->local); delete x; cudaGetLastError();
+    return ASSL_ERR_CUDA;
+  }
+  std::memcpy(handle_out, &h, sizeof(h));
+  x->peer[rank] = x->local;
+  *out = x;
+  return ASSL_OK;
+}
+
+extern "C" int assl_exchange_connect(assl_exchange* x, const void* all_handles) {
+  if (!x || !all_handles) return ASSL_ERR_INVALID_ARG;
+  if (x->connected) return ASSL_OK;
+  for (int r = 0; r < x->world; ++r) {
+    if (r == x->rank) continue;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, static_cast<const unsigned char*>(all_handles) + static_cast<size_t>(r) * sizeof(h), sizeof(h));
+    void* p = nullptr;
+    if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); return ASSL_ERR_CUDA; }
+    x->peer[r] = static_cast<unsigned char*>(p);
+  }
+  x->connected = true;
+  return ASSL_OK;
+}
+
+extern "C" int assl_exchange_destroy(assl_exchange* x) {
+  if (!x) return ASSL_OK;
+  for (int r = 0; r < x->world; ++r)
+    if (r != x->rank && x->peer[r]) cudaIpcCloseMemHandle(x->peer[r]);
+  cudaFree(x->local);
+  delete x;
+  return ASSL_OK;
+}
+
+extern "C" int assl_running_stats_exchange(assl_exchange* x, double* state, const double* pair_sums, int64_t B,
+                                           int64_t n_parts, int64_t elems, int64_t max_update, float* mean_std,
+                                           int64_t slot0, int64_t cap, void* stream) {
+  using namespace assl;
+  if (!x || !x->connected || !state || !pair_sums || !mean_std || B < 1 || B > x->max_clips || n_parts < 1 || elems < 1 ||
+      max_update < 1 || slot0 < 0 || cap < 0)
+    return ASSL_ERR_INVALID_ARG;
+  if (cap > 0 && (B > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
+  if (reinterpret_cast<uintptr_t>(pair_sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;
+  PeerArgs px;
+  px.world = x->world; px.rank = x->rank; px.b_local = B; px.n_parts_local = n_parts; px.pair_sums = pair_sums;
+  px.seq = ++x->seq;
+  const size_t parity = static_cast<size_t>(px.seq & 1);
+  for (int r = 0; r < x->world; ++r) {
+    px.peer_sums[r] = reinterpret_cast<double2*>(x->peer[r] + parity * x->sums_bytes);
+    px.peer_flags[r] = reinterpret_cast<unsigned long long*>(x->peer[r] + 2 * x->sums_bytes) + parity * ASSL_EXCHANGE_MAX_WORLD;
+  }
+  running_stats_kernel<<<kStatCtas, kScanThreads, 0, as_stream(stream)>>>(
+      state, reinterpret_cast<const double*>(px.peer_sums[x->rank]), static_cast<long long>(x->world) * B, 1,
+      1.0 / static_cast<double>(elems), max_update, static_cast<long long>(x->rank) * B, B, mean_std, slot0, cap, px);
+  return launch_status();
 }

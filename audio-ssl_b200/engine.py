@@ -51,6 +51,51 @@ def gather_clip_sums(local):
     return gathered
 
 
+class StatsExchange:
+    """Per-clip sums across the GPUs of one node through peer memory (``assl_running_stats_exchange``): one kernel
+    per rank instead of reduce + NCCL all-gather + scan.  ``torch.distributed`` only carries the 64-byte IPC
+    handles once.  ``StatsExchange.open`` returns None when the devices cannot map each other's memory (no P2P,
+    more than one node) or ``ASSL_STATS_EXCHANGE=nccl`` is set: the caller keeps the all-gather path."""
+
+    def __init__(self, handle, rank, world, max_clips):
+        self.handle, self.rank, self.world, self.max_clips = handle, rank, world, max_clips
+
+    @classmethod
+    def open(cls, max_clips, device):
+        import os
+        import torch.distributed as dist
+        rank, world = _dist_world()
+        if world < 2 or world > 16 or os.environ.get("ASSL_STATS_EXCHANGE", "peer") == "nccl":
+            return None
+        lib = _native.lib()
+        mine = (C.c_ubyte * 64)()
+        handle = C.c_void_p()
+        ok = lib.assl_exchange_create(C.byref(handle), rank, world, int(max_clips), mine) == 0
+        local = torch.tensor(list(mine) if ok else [0] * 64, dtype=torch.uint8, device=device)
+        everyone = torch.empty(world * 64, dtype=torch.uint8, device=device)
+        dist.all_gather_into_tensor(everyone, local)
+        raw = bytes(everyone.cpu().tolist())
+        if ok:
+            ok = lib.assl_exchange_connect(handle, raw) == 0
+        agree = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device)
+        dist.all_reduce(agree, op=dist.ReduceOp.MIN)               # all ranks take the same path
+        if int(agree.item()) == 0:
+            if handle:
+                lib.assl_exchange_destroy(handle)
+            return None
+        return cls(handle, rank, world, int(max_clips))
+
+    def run(self, state, sums, b, n_parts, elems, max_update, stats, slot0, cap):
+        _native.check(_native.lib().assl_running_stats_exchange(
+            self.handle, _ptr(state), _ptr(sums), b, n_parts, elems, int(max_update), _ptr(stats), slot0, cap,
+            _stream_ptr()), "assl_running_stats_exchange")
+
+    def close(self):
+        if self.handle:
+            _native.lib().assl_exchange_destroy(self.handle)
+            self.handle = None
+
+
 class ViewEngine:
     def __init__(self, n_memory=2048, pushes_per_clip=2, ratio=0.4, log_mixup=True,
                  virtual_crop_scale=(1.0, 1.5), interp="bicubic", normalize=True, max_update=None,
@@ -68,6 +113,7 @@ class ViewEngine:
         self.clips_done = 0
         self.ring = self.stats = self.state = None
         self.f = self.t = None
+        self._exchange = False               # False: not tried yet; None: unavailable; else a StatsExchange
 
     # ------------------------------------------------------------------ buffers
     def ensure(self, f, t, device):
@@ -99,7 +145,11 @@ class ViewEngine:
         b = sums.shape[0]
         rank, world = _dist_world()
         elems = self.f * self.t
-        if world > 1 and self.sync_stats:
+        if world > 1 and self.sync_stats and self._exchange is False:
+            self._exchange = StatsExchange.open(self.max_batch, sums.device)
+        if world > 1 and self.sync_stats and self._exchange is not None and b <= self._exchange.max_clips:
+            self._exchange.run(self.state, sums, b, n_parts, elems, self.max_update, self.stats, self.slot0, self.cap)
+        elif world > 1 and self.sync_stats:
             local = torch.empty((b, 2), dtype=torch.float64, device=sums.device)
             _native.check(lib.assl_clip_sums(_ptr(sums), b, n_parts, _ptr(local), _stream_ptr()))
             gathered = gather_clip_sums(local)

@@ -3,9 +3,13 @@ waveform -> two-views pipeline built on the same engine.
 
 The reference composes ``RunningNorm`` (once per clip) with ``Sequential(MixupBYOLA, RandomResizeCrop)``
 applied twice on ONE shared MixupBYOLA instance; here that is one statistics scan plus one fused kernel
-launch per batch.  ``Kmix`` and ``PatchDrop`` entries of the shipped configs are ignored with a warning:
-in the reference they cannot run (``centroid_path: None`` fails in ``torch.load``, augmentations.py:136;
-``PatchDrop.forward`` uses an undefined name, :72-75).
+launch per batch.  A ``Kmix`` entry with a ``centroid_path`` appends :class:`augmentations.Kmix` after the crop
+like the reference's ``nn.Sequential`` (src/augmentations/__init__.py:24-25); it then sees the views in the
+reference's order (view 1 of clip 0, view 2 of clip 0, view 1 of clip 1, ...) but draws after the batch's
+MixupBYOLA / RandomResizeCrop draws instead of interleaved with them (its draws are data dependent, see
+DESIGN.md 4.4).  ``Kmix`` with ``centroid_path: None`` (the shipped configs) and ``PatchDrop`` are ignored with a
+warning: in the reference they cannot run (``torch.load(None)``, augmentations.py:136; ``PatchDrop.forward`` uses
+an undefined name, :72-75).
 """
 from __future__ import annotations
 
@@ -34,10 +38,16 @@ class AugmentationModule:
                  max_batch=4096, seed=0, sync_stats=True):
         pre = config["pretrain"]
         aug = pre["augmentations"]
-        for name in ("Kmix", "PatchDrop"):
-            if name in aug:
-                warnings.warn(f"{name} is not part of the accelerated path and is ignored "
-                              "(it cannot run in the reference either)", stacklevel=2)
+        self.kmix = None
+        km = aug.get("Kmix")
+        if km is not None and km.get("centroid_path") is not None:
+            from .augmentations import Kmix
+            self.kmix = Kmix(ratio=km["ratio"], log_mixup_exp=km["log_mixup_exp"], top_k=km["top_k"],
+                             centroid_path=km["centroid_path"], max_batch=2 * max_batch)
+        elif km is not None:
+            warnings.warn("Kmix without a centroid_path is ignored (the reference fails in torch.load there)", stacklevel=2)
+        if "PatchDrop" in aug:
+            warnings.warn("PatchDrop is ignored (PatchDrop.forward raises NameError in the reference)", stacklevel=2)
         mix = aug.get("MixupBYOLA")
         rrc = aug.get("RandomResizeCrop")
         self.has_mix, self.has_crop = mix is not None, rrc is not None
@@ -79,7 +89,16 @@ class AugmentationModule:
                 v1s.append(a); v2s.append(b)
         v1 = v1s[0] if len(v1s) == 1 else torch.cat(v1s)
         v2 = v2s[0] if len(v2s) == 1 else torch.cat(v2s)
+        v1, v2 = self._post(v1, v2)
         return (v1[:, 0], v2[:, 0]) if single else (v1, v2)
+
+    def _post(self, v1, v2):
+        """Augmentations the reference chains after the crop (Kmix): views in the reference's order v1[0], v2[0], v1[1], ..."""
+        if self.kmix is None:
+            return v1, v2
+        both = self.kmix(torch.stack((v1, v2), 1).reshape(-1, *v1.shape[1:]))
+        both = both.reshape(v1.shape[0], 2, *v1.shape[1:])
+        return both[:, 0], both[:, 1]
 
     def _params(self, params, lo, hi):
         if params is None:
@@ -144,7 +163,7 @@ class UpstreamInputPipeline:
                 v1s.append(a); v2s.append(c)
         v1 = v1s[0] if len(v1s) == 1 else torch.cat(v1s)
         v2 = v2s[0] if len(v2s) == 1 else torch.cat(v2s)
-        return v1, v2
+        return self.tfms._post(v1, v2)
 
     def _windows_to_views(self, part, gain, draw):
         """[b, L] windows on the GPU -> log-mel into the ring -> statistics -> two views."""
@@ -192,4 +211,4 @@ class UpstreamInputPipeline:
                 v1s.append(a); v2s.append(c)
         v1 = v1s[0] if len(v1s) == 1 else torch.cat(v1s)
         v2 = v2s[0] if len(v2s) == 1 else torch.cat(v2s)
-        return v1, v2
+        return self.tfms._post(v1, v2)

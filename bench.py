@@ -169,7 +169,7 @@ def run_ours(args):
 
     import audiossl_b200 as A
     from audiossl_b200 import _native
-    from audiossl_b200.engine import gather_clip_sums
+    from audiossl_b200.engine import StatsExchange, gather_clip_sums
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -210,6 +210,8 @@ def run_ours(args):
     steps_params = [upload(tf.sampler.draw(s * B, B, N_MELS, T), s * B) for s in range(W + K)]
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(W + K)]
 
+    exchange = StatsExchange.open(B, dev) if world > 1 else None        # peer-memory path; None -> NCCL all-gather
+
     def device_step(s):
         slot0 = (s * B) % cap
         clip, mix, alpha, crop = steps_params[s]
@@ -218,7 +220,9 @@ def run_ours(args):
         _native.check(lib.assl_logmel_f32(plan.handle, P(waves[s % args.rotate]), None, B, L, L, P(eng.ring), slot0, cap,
                                           P(sums), 0, stream()))
         e[1].record()
-        if world > 1:
+        if exchange is not None:
+            exchange.run(eng.state, sums, B, tiles, N_MELS * T, max_update, eng.stats, slot0, cap)
+        elif world > 1:
             _native.check(lib.assl_clip_sums(P(sums), B, tiles, P(local_sums), stream()))
             gathered = gather_clip_sums(local_sums)
             _native.check(lib.assl_running_stats(P(eng.state), P(gathered), world * B, 1, N_MELS * T, max_update,
@@ -315,7 +319,10 @@ def run_ours(args):
     out = {
         "metric": METRIC, "value": clips_per_s, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": workload_config(args, B),
+        "dtype": "f32", "data": "synthetic",
+        "config": dict(workload_config(args, B), stats_exchange=("none (one GPU)" if world == 1 else
+                                                                 "peer memory over NVLink, fused into the statistics kernel"
+                                                                 if exchange is not None else "NCCL all-gather")),
         "roofline": {"bound": "hbm", "kernel": "logmel_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
                      "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": B * a_fe, "kernel_ms": k_ms[0]},
@@ -325,7 +332,7 @@ def run_ours(args):
         "e2e": {"value": world * B * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * L * 4 + B * 40,
                 "d2h_bytes_per_step": 2 * B * N_MELS * T * 4, "ms_per_step": 1e3 * e2e_s / K, "checksum": checksum,
                 "api": "assl_pipeline_host_f32 + assl_pipeline_host_sync (pinned host waveforms in, both views back to pinned host memory; uploads/kernels/downloads of consecutive calls overlap)"},
-        "gpu_launches": K * (3 + (1 if world > 1 else 0)), "clocks": clocks,
+        "gpu_launches": K * (3 if (world == 1 or exchange is not None) else 4), "clocks": clocks,
     }
     if world == 1 and not args.no_cpu:
         arm = CpuArm(L)

@@ -140,6 +140,36 @@ int assl_clip_normalize_f32(const float* x, float* y, int64_t B, int64_t elems, 
 int assl_clip_sums(const double* tile_sums, int64_t B, int64_t n_parts, double* clip_sums,
                    void* stream);
 
+/* -- running pre-normalisation across the GPUs of one node, over peer memory ----------------
+ * With the batch sharded by clip (rank r owns clips [r*B, (r+1)*B) of the global order), the
+ * running statistics of the reference's single stream need every rank's per-clip sums.  Instead
+ * of reduce -> NCCL all-gather -> scan (three launches and a collective's latency), ONE kernel per
+ * rank reduces its own clips, stores the per-clip sums straight into every peer's buffer over
+ * NVLink (P2P stores), raises a per-rank flag with system-scope release, waits for the peers'
+ * flags and runs the scan over the global batch.  No host synchronisation, nothing but that
+ * kernel on the stream.
+ *
+ * assl_exchange_create   allocates this rank's buffer (room for world * max_clips per-clip sums, two
+ *                        parities, flags) and writes its 64-byte CUDA IPC handle to handle_out
+ * assl_exchange_connect  all_handles = world * 64 bytes, rank-major (all-gather them with any host
+ *                        or device collective); maps the peers' buffers.  ASSL_ERR_CUDA when the
+ *                        devices cannot reach each other -- fall back to assl_clip_sums + all-gather
+ * assl_running_stats_exchange  arguments as assl_running_stats, except: pair_sums [B, n_parts, 2]
+ *                        are THIS rank's clips, every rank must call it with the same B, the scan
+ *                        runs over world * B clips and (mean, std) of the local slice is written.
+ *                        A peer that does not show up within ~2 s sets state[7] = 1 (checked by
+ *                        assl_exchange_error) instead of hanging the GPU.                        */
+typedef struct assl_exchange assl_exchange;
+#define ASSL_EXCHANGE_HANDLE_BYTES 64
+#define ASSL_EXCHANGE_MAX_WORLD 16
+int assl_exchange_create(assl_exchange** out, int32_t rank, int32_t world, int64_t max_clips,
+                         void* handle_out);
+int assl_exchange_connect(assl_exchange* x, const void* all_handles);
+int assl_exchange_destroy(assl_exchange* x);
+int assl_running_stats_exchange(assl_exchange* x, double* state, const double* pair_sums, int64_t B,
+                                int64_t n_parts, int64_t elems, int64_t max_update, float* mean_std,
+                                int64_t slot0, int64_t cap, void* stream);
+
 /* -- two views -----------------------------------------------------------------------------
  * Replaces, per clip and per view, RunningNorm.forward's (x-mean)/std (augmentations.py:282),
  * MixupBYOLA.forward's mix (:99-106, log_mixup_exp :8-12) and RandomResizeCrop.forward (:40-55:

@@ -1,0 +1,86 @@
+"""Multi-GPU check of the statistics exchange (not collected by pytest; needs >= 2 GPUs):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29531 \
+        tests/multigpu_check.py
+
+1. the peer-memory path (assl_running_stats_exchange) == the NCCL path (assl_clip_sums + all-gather +
+   assl_running_stats) == one process scanning the whole batch, bit for bit, over several steps (both parities,
+   carries, a smaller last batch);
+2. the sharded front end + views (mixup off, explicit crops) == one process on the unsharded batch.
+"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    import audiossl_b200 as A
+    from audiossl_b200 import _native
+    from audiossl_b200.engine import StatsExchange, gather_clip_sums
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
+    dist.init_process_group("nccl", device_id=dev)
+    lib = _native.lib()
+    P = lambda t: C.c_void_p(t.data_ptr())                      # noqa: E731
+    st = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)   # noqa: E731
+
+    ex = StatsExchange.open(300, dev)
+    assert ex is not None, "peer-memory exchange unavailable on this box"
+    parts, elems, cap, max_update = 7, 640, 4096, 1500
+    state = {k: torch.zeros(8, dtype=torch.float64, device=dev) for k in "abc"}
+    stats = {k: torch.zeros((cap, 2), dtype=torch.float32, device=dev) for k in "abc"}
+    g = torch.Generator(device="cpu").manual_seed(7)
+    done = 0
+    for step, b in enumerate([300, 300, 300, 129, 300, 1]):
+        allsums = torch.rand((world, b, parts, 2), generator=g, dtype=torch.float64) * 50 + 1   # same on every rank
+        mine = allsums[rank].to(dev)
+        slot0 = done % cap
+        ex.run(state["a"], mine, b, parts, elems, max_update, stats["a"], slot0, cap)
+        local = torch.empty((b, 2), dtype=torch.float64, device=dev)
+        _native.check(lib.assl_clip_sums(P(mine), b, parts, P(local), st()))
+        gathered = gather_clip_sums(local)
+        _native.check(lib.assl_running_stats(P(state["b"]), P(gathered), world * b, 1, elems, max_update, rank * b, b,
+                                             P(stats["b"]), slot0, cap, st()))
+        whole = allsums.reshape(world * b, parts, 2).to(dev)
+        _native.check(lib.assl_running_stats(P(state["c"]), P(whole), world * b, parts, elems, max_update, rank * b, b,
+                                             P(stats["c"]), slot0, cap, st()))
+        torch.cuda.synchronize()
+        for k in "bc":
+            assert torch.equal(state["a"], state[k]), (step, k, state["a"], state[k])
+            assert torch.equal(stats["a"], stats[k]), (step, k)
+        assert float(state["a"][7]) == 0.0
+        done += b
+    assert float(state["a"][0]) == min(done * world, max_update)
+
+    # ---- sharded pipeline vs one process
+    cfg = {"pretrain": {"normalization": "mean_var", "input": {"length_wave": 0.5},
+                        "augmentations": {"RandomResizeCrop": {"virtual_crop_scale": [1.0, 1.5], "freq_crop_scale": [0.6, 1.5],
+                                                               "time_crop_scale": [0.6, 1.5]}}}}
+    b = 96
+    wave = (torch.randn(world * b, 8000, generator=g) * 0.1).to(dev)
+    T = A.Plan().num_frames(8000)
+    params = A.FastSampler(mixup=False, seed=3).draw(0, world * b, 64, T)
+    take = lambda p, lo, hi: A.ViewParams(p.alpha[lo:hi], p.src_clip[lo:hi], p.bank_index[lo:hi], p.crop[lo:hi])   # noqa: E731
+    sharded = A.UpstreamInputPipeline(cfg, 10 ** 6, max_batch=b)
+    v1, v2 = sharded(wave[rank * b:(rank + 1) * b], params=take(params, rank * b, (rank + 1) * b))
+    assert sharded.tfms.engine._exchange is not None
+    single = A.UpstreamInputPipeline(cfg, 10 ** 6, max_batch=world * b, sync_stats=False)
+    w1, w2 = single(wave, params=params)
+    torch.cuda.synchronize()
+    assert torch.equal(v1, w1[rank * b:(rank + 1) * b]) and torch.equal(v2, w2[rank * b:(rank + 1) * b])
+    dist.barrier()
+    ex.close()
+    if rank == 0:
+        print(f"multigpu_check: OK on {world} GPUs (peer exchange == NCCL path == single stream, bit for bit)")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

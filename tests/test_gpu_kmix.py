@@ -62,3 +62,32 @@ def test_kmix_rejects_what_the_reference_cannot_run():
         A.Kmix(top_k=1)
     with pytest.raises(ValueError):
         A.Kmix(top_k=1, centroids=c)(torch.zeros(1, 9, 5))
+
+
+def test_augmentation_module_chains_kmix_after_the_crop(golden_dir, tmp_path):
+    """config['pretrain']['augmentations']['Kmix'] with a centroid file: applied to the views like the reference's
+    nn.Sequential(MixupBYOLA, RandomResizeCrop, Kmix), in the order view 1, view 2 of each clip."""
+    import random
+    import audiossl_b200 as A
+    g = np.load(os.path.join(golden_dir, "kmix_reference.npz"))
+    path = str(tmp_path / "centroids.pt")
+    torch.save(torch.from_numpy(g["centroids"]), path)
+    aug = {"MixupBYOLA": {"ratio": 0.4, "log_mixup_exp": True},
+           "RandomResizeCrop": {"virtual_crop_scale": [1.0, 1.5], "freq_crop_scale": [0.6, 1.5], "time_crop_scale": [0.6, 1.5]}}
+    cfg = {"pretrain": {"normalization": "mean_var", "augmentations": dict(aug)}}
+    cfg_k = {"pretrain": {"normalization": "mean_var",
+                          "augmentations": dict(aug, Kmix={"ratio": 0.3, "log_mixup_exp": True, "top_k": 1, "centroid_path": path})}}
+    x = torch.from_numpy(g["x"][:150]).cuda()                      # [150, 1, 16, 20]: crosses the 128-entry switch
+    np.random.seed(5); random.seed(5)
+    plain = A.AugmentationModule(cfg, 1000)
+    a1, a2 = plain(x)
+    km = A.Kmix(ratio=0.3, log_mixup_exp=True, top_k=1, centroid_path=path)
+    want = km(torch.stack((a1, a2), 1).reshape(-1, *a1.shape[1:])).reshape(a1.shape[0], 2, *a1.shape[1:])
+    np.random.seed(5); random.seed(5)
+    chained = A.AugmentationModule(cfg_k, 1000)
+    b1, b2 = chained(x)
+    assert torch.equal(b1, want[:, 0]) and torch.equal(b2, want[:, 1])
+    assert not torch.equal(b1, a1)
+    with pytest.warns(UserWarning):
+        A.AugmentationModule({"pretrain": {"normalization": "mean_var", "augmentations": dict(
+            aug, Kmix={"ratio": 0.3, "log_mixup_exp": True, "top_k": 1, "centroid_path": None})}}, 10)
