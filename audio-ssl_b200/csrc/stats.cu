@@ -92,11 +92,17 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
   return v;
 }
 
-// state: [0] n_put  [1] sum of m_j (j>=1)  [2] sum of v_j (j>=1)  [3] mean  [4] std  [5..7] reserved
+// state: [0] n_put  [1] sum of m_j (j>=1)  [2] sum of v_j (j>=1)  [3] mean  [4] std  [5..6] reserved  [7] exchange error
 //
-// Launched as ONE thread-block cluster of kStatCtas CTAs: all of them reduce the per-pair sums of their share of
-// the clips (that read is the bulk of the bytes and a single SM cannot keep enough of it in flight), drop the
-// per-clip (m, q) into CTA 0's shared memory through DSMEM, and CTA 0 runs the two block-wide scans.
+// Launched as ONE thread-block cluster of kStatCtas CTAs.  The clips are taken kStatCtas * 1024 at a time, one
+// chunk of 1024 per CTA:
+//   1. per-clip (m, q) = (sum x, sum x^2) / elems of every chunk land in the owning CTA's shared memory -- for
+//      per-pair sums all CTAs reduce 128 clips of each chunk and hand the result over through DSMEM (that read is
+//      the bulk of the bytes and a single SM cannot keep enough of it in flight); gathered per-clip sums
+//      (n_parts = 1) are simply loaded by the owner;
+//   2. every CTA scans its chunk, the chunk totals are exchanged through DSMEM and added in chunk order, so the
+//      result is bit-identical to a sequential walk over the chunks while a global batch of 8 GPUs x 1024 clips
+//      costs the time of one chunk.
 __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads) running_stats_kernel(
     double* state, const double* sums, long long n_clips, long long n_parts, double inv_elems,
     long long max_update, long long first, long long count, float* mean_std, long long slot0, long long cap,
@@ -106,17 +112,12 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
   const unsigned rank = cluster.block_rank();
   __shared__ double s_warp[32];
   __shared__ double s_m[kScanThreads], s_q[kScanThreads];
+  __shared__ double s_tot[2][kStatCtas];           // chunk totals of m / of v, a full copy in every CTA
   __shared__ float s_frozen[2];
-  double* lead_m = cluster.map_shared_rank(s_m, 0);
-  double* lead_q = cluster.map_shared_rank(s_q, 0);
   const int tid = threadIdx.x;
-  long long n0 = 0;
-  double carry_m = 0.0, carry_v = 0.0;
-  if (rank == 0) {
-    n0 = static_cast<long long>(state[0]);
-    carry_m = state[1]; carry_v = state[2];
-    if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); }
-  }
+  const long long n0 = static_cast<long long>(state[0]);
+  double carry_m = state[1], carry_v = state[2];
+  if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); }
 
   if (px.world > 0) {
     // ---- exchange: totals of this rank's clips -> the slice [rank * b_local, ...) of EVERY rank's buffer (stores
@@ -148,45 +149,82 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
     if (rank == 0 && tid == 0 && s_late) state[7] = 1.0;
   }
 
-  for (long long base = 0; base < n_clips; base += kScanThreads) {
-    {   // per-clip totals: 8 lanes per clip read the clip's parts side by side, 128 clips per CTA
-      const long long c = rank * (kScanThreads / 8) + (tid >> 3);
-      double sx, sxx;
-      clip_total8(sums, base + c, n_clips, n_parts, tid & 7, &sx, &sxx);
-      if ((tid & 7) == 0) { lead_m[c] = sx * inv_elems; lead_q[c] = sxx * inv_elems; }
+  for (long long sbase = 0; sbase < n_clips; sbase += static_cast<long long>(kStatCtas) * kScanThreads) {
+    const long long left = n_clips - sbase;
+    const int n_chunks = static_cast<int>(left >= static_cast<long long>(kStatCtas) * kScanThreads
+                                              ? kStatCtas : (left + kScanThreads - 1) / kScanThreads);
+    if (n_parts == 1) {                              // per-clip sums: the owner loads its chunk
+      const long long idx = sbase + rank * kScanThreads + tid;
+      if (idx < n_clips) {
+        const double2 v = reinterpret_cast<const double2*>(sums)[idx];
+        s_m[tid] = v.x * inv_elems; s_q[tid] = v.y * inv_elems;
+      }
+    } else {                                         // per-pair sums: 8 lanes per clip, 128 clips of each chunk per CTA
+      for (int c = 0; c < n_chunks; ++c) {
+        double* dm = cluster.map_shared_rank(s_m, c);
+        double* dq = cluster.map_shared_rank(s_q, c);
+        const int cc = rank * (kScanThreads / 8) + (tid >> 3);
+        double sx, sxx;
+        clip_total8(sums, sbase + static_cast<long long>(c) * kScanThreads + cc, n_clips, n_parts, tid & 7, &sx, &sxx);
+        if ((tid & 7) == 0) { dm[cc] = sx * inv_elems; dq[cc] = sxx * inv_elems; }
+      }
     }
     cluster.sync();
-    if (rank == 0) {
-      const long long idx = base + tid;
-      const bool valid = idx < n_clips;
-      const long long k = n0 + idx;                     // put index of this clip
-      const double m = valid ? s_m[tid] : 0.0, q = valid ? s_q[tid] : 0.0;
-      const bool active = valid && k < max_update;
-      const bool counted = active && k >= 1;
-      double tot;
-      const double pm = block_scan_incl(counted ? m : 0.0, s_warp, &tot) + carry_m;
-      carry_m += tot;
-      const double mu = (k == 0) ? m : pm / static_cast<double>(k);
-      double v = q - 2.0 * mu * m + mu * mu;
-      v = v > 0.0 ? v : 0.0;
-      const double pv = block_scan_incl(counted ? v : 0.0, s_warp, &tot) + carry_v;
-      carry_v += tot;
-      const double s2 = (k == 0) ? v : pv / static_cast<double>(k);
-      float my_mean = 0.f, my_std = 1.f;
-      if (active) {
-        my_mean = static_cast<float>(mu);
-        my_std = fminf(fmaxf(sqrtf(static_cast<float>(s2)), kLogEps), kF32Max);   // clamp(std, eps, max) :281
-        if (k == max_update - 1 || idx == n_clips - 1) { s_frozen[0] = my_mean; s_frozen[1] = my_std; }
-      }
-      __syncthreads();
-      if (valid && !active) { my_mean = s_frozen[0]; my_std = s_frozen[1]; }     // statistics frozen :276
-      if (valid && idx >= first && idx < first + count) {
-        const long long s = ring_slot(slot0, idx - first, cap);
-        mean_std[2 * s] = my_mean;
-        mean_std[2 * s + 1] = my_std;
+
+    const long long idx = sbase + rank * kScanThreads + tid;
+    const bool valid = idx < n_clips;
+    const long long k = n0 + idx;                     // put index of this clip
+    const double m = valid ? s_m[tid] : 0.0, q = valid ? s_q[tid] : 0.0;
+    const bool active = valid && k < max_update;
+    const bool counted = active && k >= 1;
+    double tot;
+    if (n_chunks == 1 && rank > 0) break;            // a single chunk: CTA 0 finishes alone (cluster-uniform condition)
+    double pm = block_scan_incl(counted ? m : 0.0, s_warp, &tot);
+    if (n_chunks == 1) {
+      pm += carry_m; carry_m += tot;
+    } else {
+      if (tid < kStatCtas) cluster.map_shared_rank(&s_tot[0][0], tid)[rank] = tot;
+      cluster.sync();
+      double cin = carry_m;
+      for (unsigned c = 0; c < rank; ++c) cin += s_tot[0][c];
+      for (int c = 0; c < kStatCtas; ++c) carry_m += s_tot[0][c];
+      pm += cin;
+    }
+    const double mu = (k == 0) ? m : pm / static_cast<double>(k);
+    double v = q - 2.0 * mu * m + mu * mu;
+    v = v > 0.0 ? v : 0.0;
+    double pv = block_scan_incl(counted ? v : 0.0, s_warp, &tot);
+    if (n_chunks == 1) {
+      pv += carry_v; carry_v += tot;
+    } else {
+      if (tid < kStatCtas) cluster.map_shared_rank(&s_tot[1][0], tid)[rank] = tot;
+      cluster.sync();
+      double cin = carry_v;
+      for (unsigned c = 0; c < rank; ++c) cin += s_tot[1][c];
+      for (int c = 0; c < kStatCtas; ++c) carry_v += s_tot[1][c];
+      pv += cin;
+    }
+    const double s2 = (k == 0) ? v : pv / static_cast<double>(k);
+    float my_mean = 0.f, my_std = 1.f;
+    if (active) {
+      my_mean = static_cast<float>(mu);
+      my_std = fminf(fmaxf(sqrtf(static_cast<float>(s2)), kLogEps), kF32Max);   // clamp(std, eps, max) :281
+      if (k == max_update - 1 || idx == n_clips - 1) { state[3] = my_mean; state[4] = my_std; }
+      if (k == max_update - 1) {                       // the statistics freeze here: every later clip uses these
+        for (int c = 0; c < (n_chunks == 1 ? 1 : kStatCtas); ++c) {
+          float* fz = cluster.map_shared_rank(s_frozen, c);
+          fz[0] = my_mean; fz[1] = my_std;
+        }
       }
     }
-    cluster.sync();       // CTA 0 is done with (m, q) before the next chunk lands; nobody leaves while peers still write
+    if (n_chunks == 1) __syncthreads();              // (the last pass: nothing is overwritten after it)
+    else cluster.sync();                             // frozen values are out; (m, q) and the totals may be overwritten
+    if (valid && !active) { my_mean = s_frozen[0]; my_std = s_frozen[1]; }     // statistics frozen :276
+    if (valid && idx >= first && idx < first + count) {
+      const long long s = ring_slot(slot0, idx - first, cap);
+      mean_std[2 * s] = my_mean;
+      mean_std[2 * s + 1] = my_std;
+    }
   }
   if (rank == 0 && tid == 0) {
     long long n1 = n0;
@@ -194,8 +232,6 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
     state[0] = static_cast<double>(n1);
     state[1] = carry_m;
     state[2] = carry_v;
-    state[3] = s_frozen[0];
-    state[4] = s_frozen[1];
   }
 }
 

@@ -211,3 +211,39 @@ def test_c_abi_host_pipeline_matches_device_pipeline():
         # chunked statistics scans may round the running mean/std differently in the last bit
         _close(hv[k][0], want[k][0], rtol=1e-6, atol=2e-6, what=f"call {k} view1")
         _close(hv[k][1], want[k][1], rtol=1e-6, atol=2e-6, what=f"call {k} view2")
+
+
+@pytest.mark.parametrize("n_parts", [1, 5, 51])
+def test_running_stats_many_chunks_and_freeze(n_parts):
+    """20000 clips in one call (three passes of the 8-CTA cluster, a partial last chunk), statistics freezing in the
+    middle of a chunk, then a second call that starts frozen: against the reference recurrence in float64."""
+    import ctypes as C
+    from audiossl_b200 import _native
+    lib = _native.lib()
+    n, elems, max_update = 20000, 640, 13333
+    rng = np.random.default_rng(n_parts)
+    parts = rng.random((n, n_parts, 2)) * 40 + 1
+    parts[:, :, 1] += 2000                                            # keep q - mu^2 positive
+    d_parts = torch.from_numpy(parts).cuda()
+    state = torch.zeros(8, dtype=torch.float64, device="cuda")
+    out = torch.zeros((n, 2), dtype=torch.float32, device="cuda")
+    P = lambda t: C.c_void_p(t.data_ptr())                            # noqa: E731
+    for lo, hi in ((0, 15000), (15000, n)):
+        _native.check(lib.assl_running_stats(P(state), P(d_parts[lo:hi]), hi - lo, n_parts, elems, max_update, 0, hi - lo,
+                                             P(out[lo:hi]), 0, 0, None))
+    got = out.cpu().numpy()
+    tot = parts.sum(axis=1) / elems
+    mu = sv = 0.0
+    frozen = None
+    for k in range(n):
+        m, q = tot[k]
+        if k < max_update:
+            mu = m if k == 0 else mu + (m - mu) / k                  # divisor = samples seen BEFORE (augmentations.py:226)
+            v = max(q - 2 * mu * m + mu * mu, 0.0)
+            sv = v if k == 0 else sv + (v - sv) / k
+            frozen = (mu, np.sqrt(sv))
+        want = frozen
+        assert abs(got[k, 0] - want[0]) <= 1e-6 * abs(want[0]) + 1e-7, k
+        assert abs(got[k, 1] - want[1]) <= 1e-5 * abs(want[1]) + 1e-7, k
+    st = state.cpu().numpy()
+    assert st[0] == max_update and abs(st[3] - frozen[0]) <= 1e-6 * abs(frozen[0])
