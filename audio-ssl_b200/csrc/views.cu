@@ -73,6 +73,80 @@ __host__ __device__ inline size_t views_smem_bytes(int canvas_h, int src_w, int 
          (sizeof(float) + sizeof(int)) * 4 * static_cast<size_t>(n_freq);
 }
 
+// ---- stage A: normalise + mix the crop span [0,h) x [xs_lo, xs_lo+nsx) into shared memory, G groups of 32 columns.
+//      exp(xn) = ex2(x*a + b) with a = log2e/std, b = -mean*log2e/std: one FFMA + one MUFU per operand.
+template <int G>
+__device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, long long b, int v, int h, int ci, int cj,
+                                              int xs_lo, int nsx, int lane, int warp) {
+  const int F = a.c.n_freq, T = a.c.n_time;
+  const int plane = F * T;
+  const int xslot = a.clip_slot[b];
+  const float* xp = a.lms + static_cast<long long>(xslot) * plane;
+  float mu = 0.f, inv = 1.f;
+  if (a.mean_std) { mu = a.mean_std[2 * xslot]; inv = 1.f / a.mean_std[2 * xslot + 1]; }
+  const int zslot = a.mix_slot[b * 2 + v];
+  const bool mix = zslot >= 0;
+  const float* zp = a.lms + static_cast<long long>(mix ? zslot : 0) * plane;
+  float zmu = 0.f, zinv = 1.f;
+  if (mix && a.mean_std) { zmu = a.mean_std[2 * zslot]; zinv = 1.f / a.mean_std[2 * zslot + 1]; }
+  const float al = a.alpha[b * 2 + v];
+  const float wx = 1.f - al, wz = al;
+  const bool logmix = mix && a.c.log_mixup;
+  const float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
+  const float xa = logmix ? inv * kLog2e : inv, xb = -mu * xa;
+  const float za = logmix ? zinv * kLog2e : zinv, zb = -zmu * za;
+  // columns of the span that fall inside the pasted clip: lx = cj + xs_lo + xs - x0 in [0, T)
+  const int lx0 = cj + xs_lo - a.x0;
+  const int xs_in0 = max(0, -lx0), xs_in1 = min(nsx, T - lx0);
+  // Rows are taken kRowBatch at a time per warp and ALL their global loads are issued before any
+  // arithmetic, so a warp keeps 2 * kRowBatch * ceil(nsx/32) loads in flight instead of 2.
+  constexpr int kRowBatch = 2;
+  constexpr int kColGroups = G;                               // 32 * G >= nsx (chosen per CTA)
+  for (int yb = warp * kRowBatch; yb < h; yb += (kViewThreads / 32) * kRowBatch) {
+    float xv[kRowBatch][kColGroups], zv[kRowBatch][kColGroups];
+#pragma unroll
+    for (int r = 0; r < kRowBatch; ++r) {
+      const int ly = ci + yb + r - a.y0;
+      const bool row_in = (yb + r < h) && ly >= 0 && ly < F;     // warp-uniform
+      const float* xr = xp + ly * T + lx0;
+      const float* zr = zp + ly * T + lx0;
+#pragma unroll
+      for (int c = 0; c < kColGroups; ++c) {
+        const int xs = lane + 32 * c;
+        const bool in = row_in && xs >= xs_in0 && xs < xs_in1;
+        xv[r][c] = in ? __ldg(xr + xs) : 0.f;
+        zv[r][c] = (in && mix) ? __ldg(zr + xs) : 0.f;
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < kRowBatch; ++r) {
+      const int y = yb + r;
+      const int ly = ci + y - a.y0;
+      const bool row_in = ly >= 0 && ly < F;
+      float* drow = s_src + y * a.src_w;
+      if (y < h) {
+#pragma unroll
+        for (int c = 0; c < kColGroups; ++c) {
+          const int xs = lane + 32 * c;
+          // lanes outside the pasted clip computed on zeros and then selected away: no divergent region
+          const bool in = row_in && xs >= xs_in0 && xs < xs_in1;
+          const float xn = fmaf(xv[r][c], xa, xb);
+          float val;
+          if (logmix) {                                        // CTA-uniform
+            const float zn = fmaf(zv[r][c], za, zb);
+            val = kLn2 * __log2f(fmaf(wx, ex2_approx(xn), fmaf(wz, ex2_approx(zn), kLogEps)));
+          } else if (mix) {
+            val = fmaf(wz, fmaf(zv[r][c], za, zb), wx * xn);
+          } else {
+            val = xn;
+          }
+          if (xs < nsx) drow[xs] = in ? val : 0.f;             // zero canvas outside the pasted clip
+        }
+      }
+    }
+  }
+}
+
 // TW = output frames per tile; CG = 32-column groups of the staged crop span a warp loads per row
 template <int TW, int CG>
 __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewArgs a) {
@@ -116,77 +190,13 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
                          min(max(iy + 1, 0), h - 1), min(max(iy + 2, 0), h - 1));
   }
 
-  // ---- stage A: normalise + mix the crop span [0,h) x [xs_lo, xs_lo+nsx) into shared memory.
-  //      exp(xn) = ex2(x*a + b) with a = log2e/std, b = -mean*log2e/std: one FFMA + one MUFU per operand.
-  {
-    const int plane = F * T;
-    const int xslot = a.clip_slot[b];
-    const float* xp = a.lms + static_cast<long long>(xslot) * plane;
-    float mu = 0.f, inv = 1.f;
-    if (a.mean_std) { mu = a.mean_std[2 * xslot]; inv = 1.f / a.mean_std[2 * xslot + 1]; }
-    const int zslot = a.mix_slot[b * 2 + v];
-    const bool mix = zslot >= 0;
-    const float* zp = a.lms + static_cast<long long>(mix ? zslot : 0) * plane;
-    float zmu = 0.f, zinv = 1.f;
-    if (mix && a.mean_std) { zmu = a.mean_std[2 * zslot]; zinv = 1.f / a.mean_std[2 * zslot + 1]; }
-    const float al = a.alpha[b * 2 + v];
-    const float wx = 1.f - al, wz = al;
-    const bool logmix = mix && a.c.log_mixup;
-    const float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
-    const float xa = logmix ? inv * kLog2e : inv, xb = -mu * xa;
-    const float za = logmix ? zinv * kLog2e : zinv, zb = -zmu * za;
-    // columns of the span that fall inside the pasted clip: lx = cj + xs_lo + xs - x0 in [0, T)
-    const int lx0 = cj + xs_lo - a.x0;
-    const int xs_in0 = max(0, -lx0), xs_in1 = min(nsx, T - lx0);
-    // Rows are taken kRowBatch at a time per warp and ALL their global loads are issued before any
-    // arithmetic, so a warp keeps 2 * kRowBatch * ceil(nsx/32) loads in flight instead of 2.
-    constexpr int kRowBatch = 2;
-    constexpr int kColGroups = CG;                              // 32 * CG >= src_w - 1 (checked at launch)
-    for (int yb = warp * kRowBatch; yb < h; yb += (kViewThreads / 32) * kRowBatch) {
-      float xv[kRowBatch][kColGroups], zv[kRowBatch][kColGroups];
-#pragma unroll
-      for (int r = 0; r < kRowBatch; ++r) {
-        const int ly = ci + yb + r - a.y0;
-        const bool row_in = (yb + r < h) && ly >= 0 && ly < F;     // warp-uniform
-        const float* xr = xp + ly * T + lx0;
-        const float* zr = zp + ly * T + lx0;
-#pragma unroll
-        for (int c = 0; c < kColGroups; ++c) {
-          const int xs = lane + 32 * c;
-          const bool in = row_in && xs >= xs_in0 && xs < xs_in1;
-          xv[r][c] = in ? __ldg(xr + xs) : 0.f;
-          zv[r][c] = (in && mix) ? __ldg(zr + xs) : 0.f;
-        }
-      }
-#pragma unroll
-      for (int r = 0; r < kRowBatch; ++r) {
-        const int y = yb + r;
-        const int ly = ci + y - a.y0;
-        const bool row_in = ly >= 0 && ly < F;
-        float* drow = s_src + y * a.src_w;
-        if (y < h) {
-#pragma unroll
-          for (int c = 0; c < kColGroups; ++c) {
-            const int xs = lane + 32 * c;
-            if (xs < nsx) {
-              float val = 0.f;                                   // zero canvas outside the pasted clip
-              if (row_in && xs >= xs_in0 && xs < xs_in1) {
-                const float xn = fmaf(xv[r][c], xa, xb);
-                if (logmix) {
-                  const float zn = fmaf(zv[r][c], za, zb);
-                  val = kLn2 * __log2f(fmaf(wx, ex2_approx(xn), fmaf(wz, ex2_approx(zn), kLogEps)));
-                } else if (mix) {
-                  val = fmaf(wz, fmaf(zv[r][c], za, zb), wx * xn);
-                } else {
-                  val = xn;
-                }
-              }
-              drow[xs] = val;
-            }
-          }
-        }
-      }
-    }
+  // ---- stage A, with as many 32-column groups as THIS crop span needs (the span follows the drawn crop width)
+  switch ((nsx + 31) >> 5) {
+    case 1: mix_crop_span<1>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
+    case 2: mix_crop_span<(CG >= 2 ? 2 : CG)>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
+    case 3: mix_crop_span<(CG >= 3 ? 3 : CG)>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
+    case 4: mix_crop_span<(CG >= 4 ? 4 : CG)>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
+    default: mix_crop_span<CG>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
   }
   __syncthreads();
 
