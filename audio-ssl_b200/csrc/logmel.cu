@@ -103,6 +103,11 @@ __device__ __forceinline__ void mbar_wait(void* bar, unsigned parity) {
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+__device__ __forceinline__ float ln_ftz(float x) {           // MUFU.LG2 * ln 2, like __logf minus its denormal pre-scaling
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y * 0.6931471805599453f;
+}
 __device__ __forceinline__ ulonglong2 lds128(unsigned addr) {
   ulonglong2 v;
   asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(addr) : "memory");
@@ -345,8 +350,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
       const float e = c.x * g2;
       acc0 = fmaf(acc0, e, c.y);
       acc1 = fmaf(acc1, e, c.y);
-      const float l0 = power ? acc0 : __logf(acc0 + kLogEps);
-      const float l1 = power ? acc1 : __logf(acc1 + kLogEps);
+      const float l0 = power ? acc0 : ln_ftz(acc0 + kLogEps);      // the argument is >= 1.19e-7: no denormal path needed
+      const float l1 = power ? acc1 : ln_ftz(acc1 + kLogEps);
       float* dst = out + m * band_stride;
       dst[0] = l0;
       s1 += l0; s2 = fmaf(l0, l0, s2);

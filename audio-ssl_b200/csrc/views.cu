@@ -41,6 +41,12 @@ __device__ __forceinline__ float ex2_approx(float x) {    // MUFU.EX2, flush-to-
   return y;
 }
 
+__device__ __forceinline__ float lg2_approx(float x) {    // MUFU.LG2 without the denormal pre-scaling (callers pass >= 1.19e-7)
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ float cubic1(float x) {   // |x| <= 1
   const float A = -0.75f;
   return ((A + 2.f) * x - (A + 3.f)) * x * x + 1.f;
@@ -134,7 +140,7 @@ __device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, l
           float val;
           if (logmix) {                                        // CTA-uniform
             const float zn = fmaf(zv[r][c], za, zb);
-            val = kLn2 * __log2f(fmaf(wx, ex2_approx(xn), fmaf(wz, ex2_approx(zn), kLogEps)));
+            val = kLn2 * lg2_approx(fmaf(wx, ex2_approx(xn), fmaf(wz, ex2_approx(zn), kLogEps)));
           } else if (mix) {
             val = fmaf(wz, fmaf(zv[r][c], za, zb), wx * xn);
           } else {
