@@ -28,6 +28,7 @@ struct ViewArgs {
   const int* mix_slot;
   const float* alpha;
   const int* crop;
+  const int* order;   // optional [2B]: launch position -> view id (2 * clip + view), heaviest views first
   float* view1;
   float* view2;
   int tiles_t;     // output-time tiles per view
@@ -166,6 +167,7 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   long long blk = blockIdx.x;
   const int tile = static_cast<int>(blk % a.tiles_t); blk /= a.tiles_t;
+  if (a.order) blk = a.order[blk];             // CTAs start in launch order: the host puts the big crops first
   const int v = static_cast<int>(blk & 1);
   const long long b = blk >> 1;
 
@@ -292,6 +294,13 @@ int launch_views(ViewArgs& a, cudaStream_t st) {
 extern "C" int assl_two_views_f32(const assl_view_cfg* vc, const float* lms, const float* mean_std, int64_t cap,
                                   const int32_t* clip_slot, const int32_t* mix_slot, const float* alpha,
                                   const int32_t* crop, int64_t B, float* view1, float* view2, void* stream) {
+  return assl_two_views_ordered_f32(vc, lms, mean_std, cap, clip_slot, mix_slot, alpha, crop, nullptr, B, view1, view2, stream);
+}
+
+extern "C" int assl_two_views_ordered_f32(const assl_view_cfg* vc, const float* lms, const float* mean_std, int64_t cap,
+                                          const int32_t* clip_slot, const int32_t* mix_slot, const float* alpha,
+                                          const int32_t* crop, const int32_t* order, int64_t B, float* view1,
+                                          float* view2, void* stream) {
   using namespace assl;
   if (!vc || !lms || !clip_slot || !mix_slot || !alpha || !crop || !view1 || !view2 || B < 0) return ASSL_ERR_INVALID_ARG;
   if (vc->n_freq < 1 || vc->n_time < 1 || vc->canvas_h < vc->n_freq || vc->canvas_w < vc->n_time) return ASSL_ERR_INVALID_ARG;
@@ -299,7 +308,7 @@ extern "C" int assl_two_views_f32(const assl_view_cfg* vc, const float* lms, con
   if (B == 0) return ASSL_OK;
   ViewArgs a;
   a.c = *vc; a.lms = lms; a.mean_std = mean_std; a.cap = cap; a.B = B;
-  a.clip_slot = clip_slot; a.mix_slot = mix_slot; a.alpha = alpha; a.crop = crop;
+  a.clip_slot = clip_slot; a.mix_slot = mix_slot; a.alpha = alpha; a.crop = crop; a.order = order;
   a.view1 = view1; a.view2 = view2;
   a.y0 = (vc->canvas_h - vc->n_freq) / 2;
   a.x0 = (vc->canvas_w - vc->n_time) / 2;

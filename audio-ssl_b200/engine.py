@@ -34,6 +34,14 @@ def _dist_world():
     return 0, 1
 
 
+def heavy_first(crop):
+    """Launch order of the views of a batch for ``assl_two_views_ordered_f32``: [2B] int32, view ids (2*clip + view)
+    sorted by decreasing cost.  A view stages h crop rows in ceil((w + 4) / 32) groups of 32 columns."""
+    c = np.asarray(crop, np.int64).reshape(-1, 4)
+    cost = c[:, 2] * (20 * ((c[:, 3] + 4 + 31) // 32) + 45)
+    return np.argsort(-cost, kind="stable").astype(np.int32)
+
+
 def shard_bounds(n_global: int, rank: int, world: int):
     """Contiguous block split of a global batch by clip index."""
     base, rem = divmod(n_global, world)
@@ -181,13 +189,14 @@ class ViewEngine:
         d_clip = torch.from_numpy(clip_slot).to(device, non_blocking=True)
         d_alpha = torch.from_numpy(np.ascontiguousarray(params.alpha, np.float32)).to(device, non_blocking=True)
         d_crop = torch.from_numpy(np.ascontiguousarray(params.crop, np.int32)).to(device, non_blocking=True)
+        d_order = torch.from_numpy(heavy_first(params.crop)).to(device, non_blocking=True)
         v1 = torch.empty((batch, 1, self.f, self.t), dtype=torch.float32, device=device)
         v2 = torch.empty_like(v1)
         vcfg = _native.ViewCfg(self.f, self.t, ch, cw, INTERP[self.interp], 1 if self.log_mixup else 0)
-        _native.check(_native.lib().assl_two_views_f32(
+        _native.check(_native.lib().assl_two_views_ordered_f32(
             C.byref(vcfg), _ptr(self.ring), _ptr(self.stats if self.normalize else None), self.cap,
-            _ptr(d_clip), _ptr(d_mix), _ptr(d_alpha), _ptr(d_crop), batch, _ptr(v1), _ptr(v2), _stream_ptr()),
-            "assl_two_views_f32")
+            _ptr(d_clip), _ptr(d_mix), _ptr(d_alpha), _ptr(d_crop), _ptr(d_order), batch, _ptr(v1), _ptr(v2),
+            _stream_ptr()), "assl_two_views_ordered_f32")
         self.clips_done += batch
         return v1, v2
 

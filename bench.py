@@ -169,7 +169,7 @@ def run_ours(args):
 
     import audiossl_b200 as A
     from audiossl_b200 import _native
-    from audiossl_b200.engine import StatsExchange, gather_clip_sums
+    from audiossl_b200.engine import StatsExchange, gather_clip_sums, heavy_first
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -205,7 +205,8 @@ def run_ours(args):
     def upload(p, clips_done):
         mix = np.where(p.src_clip >= 0, p.src_clip % cap, -1).astype(np.int32)
         clip = ((clips_done + np.arange(B, dtype=np.int64)) % cap).astype(np.int32)
-        return [torch.from_numpy(a).to(dev) for a in (clip, mix, np.ascontiguousarray(p.alpha), np.ascontiguousarray(p.crop))]
+        return [torch.from_numpy(a).to(dev) for a in (clip, mix, np.ascontiguousarray(p.alpha), np.ascontiguousarray(p.crop),
+                                                      heavy_first(p.crop))]
 
     steps_params = [upload(tf.sampler.draw(s * B, B, N_MELS, T), s * B) for s in range(W + K)]
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(W + K)]
@@ -214,7 +215,7 @@ def run_ours(args):
 
     def device_step(s):
         slot0 = (s * B) % cap
-        clip, mix, alpha, crop = steps_params[s]
+        clip, mix, alpha, crop, order = steps_params[s]
         e = evs[s]
         e[0].record()
         _native.check(lib.assl_logmel_f32(plan.handle, P(waves[s % args.rotate]), None, B, L, L, P(eng.ring), slot0, cap,
@@ -231,8 +232,8 @@ def run_ours(args):
             _native.check(lib.assl_running_stats(P(eng.state), P(sums), B, tiles, N_MELS * T, max_update, 0, B,
                                                  P(eng.stats), slot0, cap, stream()))
         e[2].record()
-        _native.check(lib.assl_two_views_f32(C.byref(vcfg), P(eng.ring), P(eng.stats), cap, P(clip), P(mix), P(alpha),
-                                             P(crop), B, P(v1), P(v2), stream()))
+        _native.check(lib.assl_two_views_ordered_f32(C.byref(vcfg), P(eng.ring), P(eng.stats), cap, P(clip), P(mix), P(alpha),
+                                                     P(crop), P(order), B, P(v1), P(v2), stream()))
         e[3].record()
 
     def fence():

@@ -191,6 +191,15 @@ int assl_two_views_f32(const assl_view_cfg* vcfg, const float* lms, const float*
                        const float* alpha, const int32_t* crop, int64_t B, float* view1,
                        float* view2, void* stream);
 
+/* The same, with the order in which the views are started: order [2B] int32 on the device, launch position ->
+ * view id (2 * clip + view), a permutation.  A view's cost grows with its crop (rows x 32-column groups of the
+ * staged span), CTAs start in launch order, so putting the big crops first shortens the tail of the launch
+ * (1024 clips = 3.5 waves of CTAs).  NULL = clip order.  The results do not depend on it.                 */
+int assl_two_views_ordered_f32(const assl_view_cfg* cfg, const float* lms, const float* mean_std,
+                               int64_t cap, const int32_t* clip_slot, const int32_t* mix_slot,
+                               const float* alpha, const int32_t* crop, const int32_t* order, int64_t B,
+                               float* view1, float* view2, void* stream);
+
 /* -- Kmix cluster features ------------------------------------------------------------------
  * The data-dependent half of Kmix.get_index (src/augmentations/augmentations.py:142-165): per clip, the
  * per-band mean over time is assigned to the nearest of K centroids, once L2-normalised

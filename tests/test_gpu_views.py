@@ -247,3 +247,35 @@ def test_running_stats_many_chunks_and_freeze(n_parts):
         assert abs(got[k, 1] - want[1]) <= 1e-5 * abs(want[1]) + 1e-7, k
     st = state.cpu().numpy()
     assert st[0] == max_update and abs(st[3] - frozen[0]) <= 1e-6 * abs(frozen[0])
+
+
+def test_launch_order_does_not_change_the_views():
+    """assl_two_views_ordered_f32: any permutation of the views (heaviest first in the product) gives the same bits."""
+    import ctypes as C
+    import audiossl_b200 as A
+    from audiossl_b200 import _native
+    from audiossl_b200.engine import heavy_first
+    lib = _native.lib()
+    b, f, t = 37, 64, 101
+    g = torch.Generator(device="cpu").manual_seed(3)
+    ring = torch.randn(b, f, t, generator=g).cuda()
+    stats = torch.stack((torch.randn(b, generator=g) * 0.1, torch.rand(b, generator=g) + 0.5), 1).contiguous().cuda()
+    p = A.FastSampler(seed=5).draw(b, b, f, t)                  # bank picks among the b clips before this batch
+    mix = torch.from_numpy(np.where(p.src_clip >= 0, p.src_clip % b, -1).astype(np.int32)).cuda()
+    clip = torch.arange(b, dtype=torch.int32).cuda()
+    alpha, crop = torch.from_numpy(p.alpha).cuda(), torch.from_numpy(p.crop).cuda()
+    vcfg = _native.ViewCfg(f, t, f, int(t * 1.5), 0, 1)
+    P = lambda x: C.c_void_p(x.data_ptr()) if x is not None else None   # noqa: E731
+    outs = []
+    order = heavy_first(p.crop)
+    assert sorted(order.tolist()) == list(range(2 * b))
+    cost = p.crop.reshape(-1, 4)[order]
+    assert cost[0, 2] * cost[0, 3] >= cost[-1, 2] * cost[-1, 3]
+    shuffled = torch.from_numpy(np.random.default_rng(0).permutation(2 * b).astype(np.int32)).cuda()
+    for o in (None, torch.from_numpy(order).cuda(), shuffled):
+        v1, v2 = torch.empty(b, f, t, device="cuda"), torch.empty(b, f, t, device="cuda")
+        _native.check(lib.assl_two_views_ordered_f32(C.byref(vcfg), P(ring), P(stats), b, P(clip), P(mix), P(alpha), P(crop),
+                                                     P(o), b, P(v1), P(v2), None))
+        outs.append((v1, v2))
+    for v1, v2 in outs[1:]:
+        assert torch.equal(v1, outs[0][0]) and torch.equal(v2, outs[0][1])
