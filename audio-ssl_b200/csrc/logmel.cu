@@ -175,8 +175,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   for (int i = tid; i < a.n_mels; i += n_threads) s_mconst[i] = a.mconst[i];
   for (int i = tid; i < kIvSlots * 32; i += n_threads) s_lane[i] = a.lane_iv[i];
   for (int i = tid; i <= a.n_mels; i += n_threads) s_pos[i] = a.iv_pos[i];
-  // (the row padding of s_ex is never written again; bins a part does not own are masked out, not multiplied)
-  for (int i = tid; i < n_warps * kExWarp; i += n_threads) s_ex[i] = make_float2(0.f, 0.f);
+  // (s_ex needs no clearing: every power bin a part reads is either written by this pair or selected away,
+  //  never multiplied, and every interval total is started before it is read)
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();                                   // the only CTA-wide barrier
 
