@@ -138,3 +138,21 @@ def test_mast_variant_128_mels_time_major():
     assert tuple(got_t.shape) == (6, 101, 128)
     _close(got_t.permute(0, 2, 1).cpu().numpy(), want)
     assert torch.equal(got_t.permute(0, 2, 1), m.log_mel(w.cuda()))      # same values, only the layout differs
+
+
+def test_unaligned_and_strided_waveforms(mel):
+    """Bases that are not 16-byte aligned (no bulk copy: the per-warp patch loop stages the whole span) and rows with
+    a stride (ld > L) give the same bits as the aligned, packed batch."""
+    import audiossl_b200 as A
+    w = families(9, 8000, 41)
+    ref = A.extract_log_mel_spectrogram(w.cuda(), mel)
+    flat = torch.zeros(9 * 8000 + 1, device="cuda")
+    flat[1:] = w.cuda().reshape(-1)
+    shifted = flat[1:].view(9, 8000)                          # base + 4 bytes
+    assert shifted.data_ptr() % 16 != 0
+    assert torch.equal(A.extract_log_mel_spectrogram(shifted, mel), ref)
+    wide = torch.zeros(9, 8004, device="cuda")
+    wide[:, :8000] = w.cuda()
+    out = torch.empty_like(ref)
+    mel.plan.logmel_into(wide[:, :8000], out)                  # ld = 8004
+    assert torch.equal(out, ref)

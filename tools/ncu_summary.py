@@ -20,7 +20,9 @@ RAW = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum"
        "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
        "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed", "lts__t_sector_hit_rate.pct",
-       "sm__cycles_elapsed.max", "launch__grid_size", "launch__shared_mem_per_block_dynamic"]
+       "sm__cycles_elapsed.max", "launch__grid_size", "launch__block_size", "launch__shared_mem_per_block_dynamic",
+       "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active",
+       "smsp__warps_active.avg.per_cycle_active", "smsp__warps_eligible.avg.per_cycle_active"]
 
 
 def ncu(args):
@@ -49,6 +51,11 @@ def main():
         for m in RAW:
             if m in ix:
                 print(f"   {m:72s} {r[ix[m]]} {units[ix[m]]}")
+        print("   warps stalled per issued instruction, by reason:")
+        stalls = sorted(((float(r[i].replace(",", "")), h) for h, i in ix.items()
+                         if "average_warps_issue_stalled" in h and h.endswith("_per_issue_active.ratio")), reverse=True)
+        for v, h in stalls[:10]:
+            print(f"      {v:6.3f}  {h.split('stalled_')[1].split('_per_issue')[0]}")
     for name in seen:
         kn = re.sub(r"\(.*", "", name).split("::")[-1].split("<")[0].split()[-1]
         rows = list(csv.reader(io.StringIO(ncu(["-i", a.rep, "--page", "source", "--csv", "--kernel-name",
