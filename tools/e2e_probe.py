@@ -64,6 +64,11 @@ def loop(download=True, ahead=False):
           f"H2D {B * L * 4 * K / dt / 1e9:5.1f} GB/s  host enqueue {1e3 * host_ms / K:5.3f} ms/step")
 
 
+import os
 loop(True, False)
 loop(True, True)
 loop(False, True)
+for c in (1, 2, 4, 8):
+    os.environ['ASSL_PIPE_CHUNKS'] = str(c)
+    print('chunks', c, end='  ')
+    loop(True, True)
