@@ -5,7 +5,7 @@
 //
 // Work decomposition
 //   One persistent CTA per SM; every WARP is its own pipeline over frame pairs (pair p of the flattened
-//   (clip, pair) list goes to warp p mod #warps, so neighbouring warps work on neighbouring frames and the
+//   (clip, pair) list goes to warp p mod #warps (numbered across the SMs), so at any time the resident warps work on neighbouring frames and the
 //   6.4x overlap between hop-160 frames is served by L2).  There is no CTA-wide barrier after the prologue:
 //   the warps drift apart, so while some sit in the FFTs (FP32 pipe) others are in the transposition or
 //   the filterbank (shared-memory pipe) instead of all of them queueing for the same unit.
@@ -189,7 +189,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
     mbar_expect_tx(bar, bytes);
     if (bytes) bulk_g2s(buf + s.lo, a.wave + s.clip * a.ld + s.base + s.lo, bytes, bar);
   };
-  const int first = static_cast<int>(blockIdx.x) * n_warps + warp;
+  // warp-major numbering: consecutive pairs go to different SMs, so the last, partial round (52224 pairs over 2368
+  // warps = 22.05 rounds) is one uncontended warp on each of 128 SMs instead of 16 contending warps on 8 of them
+  const int first = warp * static_cast<int>(gridDim.x) + static_cast<int>(blockIdx.x);
   if (a.bulk_ok && lane == 0 && first < a.total_pairs) issue(first);
 
   c32* ex = reinterpret_cast<c32*>(s_ex + warp * kExWarp);
