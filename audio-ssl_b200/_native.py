@@ -72,7 +72,13 @@ SIGNATURES = {
     "assl_exchange_create": (C.c_int, [C.POINTER(_P), C.c_int32, C.c_int32, _I64, _P]),
     "assl_exchange_connect": (C.c_int, [_P, _P]),
     "assl_exchange_destroy": (C.c_int, [_P]),
-    "assl_running_stats_exchange": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P, _I64, _I64, _P]),
+    "assl_running_stats_exchange": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P, _I64, _I64, C.c_int32, _P]),
+    "assl_peer_alloc": (C.c_int, [C.POINTER(_P), _I64, _P]),
+    "assl_peer_free": (C.c_int, [_P]),
+    "assl_peer_open": (C.c_int, [_P, C.POINTER(_P)]),
+    "assl_peer_close": (C.c_int, [_P]),
+    "assl_two_views_global_f32": (C.c_int, [C.POINTER(ViewCfg), _P, _P, C.c_int32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64,
+                                             _P, _P, _P]),
     "assl_two_views_f32": (C.c_int, [C.POINTER(ViewCfg), _P, _P, _I64, _P, _P, _P, _P, _I64, _P, _P, _P]),
     "assl_two_views_ordered_f32": (C.c_int, [C.POINTER(ViewCfg), _P, _P, _I64, _P, _P, _P, _P, _P, _I64, _P, _P, _P]),
     "assl_clip_clusters_f32": (C.c_int, [_P, _I64, C.c_int32, C.c_int32, _P, C.c_int32, _P, _P, _P]),

@@ -437,12 +437,13 @@ extern "C" int assl_exchange_destroy(assl_exchange* x) {
 
 extern "C" int assl_running_stats_exchange(assl_exchange* x, double* state, const double* pair_sums, int64_t B,
                                            int64_t n_parts, int64_t elems, int64_t max_update, float* mean_std,
-                                           int64_t slot0, int64_t cap, void* stream) {
+                                           int64_t slot0, int64_t cap, int32_t write_all, void* stream) {
   using namespace assl;
   if (!x || !x->connected || !state || !pair_sums || !mean_std || B < 1 || B > x->max_clips || n_parts < 1 || elems < 1 ||
       max_update < 1 || slot0 < 0 || cap < 0)
     return ASSL_ERR_INVALID_ARG;
-  if (cap > 0 && (B > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
+  const long long n_all = static_cast<long long>(x->world) * B;
+  if (cap > 0 && ((write_all ? n_all : B) > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
   if (reinterpret_cast<uintptr_t>(pair_sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;
   PeerArgs px;
   px.world = x->world; px.rank = x->rank; px.b_local = B; px.n_parts_local = n_parts; px.pair_sums = pair_sums;
@@ -453,7 +454,31 @@ extern "C" int assl_running_stats_exchange(assl_exchange* x, double* state, cons
     px.peer_flags[r] = reinterpret_cast<unsigned long long*>(x->peer[r] + 2 * x->sums_bytes) + parity * ASSL_EXCHANGE_MAX_WORLD;
   }
   running_stats_kernel<<<kStatCtas, kScanThreads, 0, as_stream(stream)>>>(
-      state, reinterpret_cast<const double*>(px.peer_sums[x->rank]), static_cast<long long>(x->world) * B, 1,
-      1.0 / static_cast<double>(elems), max_update, static_cast<long long>(x->rank) * B, B, mean_std, slot0, cap, px);
+      state, reinterpret_cast<const double*>(px.peer_sums[x->rank]), n_all, 1, 1.0 / static_cast<double>(elems), max_update,
+      write_all ? 0 : static_cast<long long>(x->rank) * B, write_all ? n_all : B, mean_std, slot0, cap, px);
   return launch_status();
 }
+
+// ---- IPC-exportable buffers (the log-mel ring of the global-bank mode)
+extern "C" int assl_peer_alloc(void** ptr, int64_t bytes, void* handle_out) {
+  if (!ptr || !handle_out || bytes < 1) return ASSL_ERR_INVALID_ARG;
+  *ptr = nullptr;
+  void* p = nullptr;
+  cudaIpcMemHandle_t h;
+  if (cudaMalloc(&p, static_cast<size_t>(bytes)) != cudaSuccess || cudaIpcGetMemHandle(&h, p) != cudaSuccess) {
+    cudaFree(p); cudaGetLastError();
+    return ASSL_ERR_CUDA;
+  }
+  std::memcpy(handle_out, &h, sizeof(h));
+  *ptr = p;
+  return ASSL_OK;
+}
+extern "C" int assl_peer_free(void* ptr) { return cudaFree(ptr) == cudaSuccess ? ASSL_OK : ASSL_ERR_CUDA; }
+extern "C" int assl_peer_open(const void* handle, void** ptr) {
+  if (!handle || !ptr) return ASSL_ERR_INVALID_ARG;
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, sizeof(h));
+  if (cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); return ASSL_ERR_CUDA; }
+  return ASSL_OK;
+}
+extern "C" int assl_peer_close(void* ptr) { return cudaIpcCloseMemHandle(ptr) == cudaSuccess ? ASSL_OK : ASSL_ERR_CUDA; }

@@ -29,6 +29,12 @@ struct ViewArgs {
   const float* alpha;
   const int* crop;
   const int* order;   // optional [2B]: launch position -> view id (2 * clip + view), heaviest views first
+  // global-bank mode (assl_two_views_global_f32): bank entries may sit in a peer GPU's ring, statistics in a ring
+  // indexed by global clip; all null / unused otherwise
+  const int* mix_rank;    // [B,2] whose ring holds the bank entry
+  const int* clip_stat;   // [B]   slot of the clip's (mean, std)
+  const int* mix_stat;    // [B,2] slot of the bank entry's (mean, std)
+  const float* peer_lms[ASSL_EXCHANGE_MAX_WORLD];   // every rank's ring as mapped into this process
   float* view1;
   float* view2;
   int tiles_t;     // output-time tiles per view
@@ -88,14 +94,17 @@ __device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, l
   const int F = a.c.n_freq, T = a.c.n_time;
   const int plane = F * T;
   const int xslot = a.clip_slot[b];
+  const int xstat = a.clip_stat ? a.clip_stat[b] : xslot;
   const float* xp = a.lms + static_cast<long long>(xslot) * plane;
   float mu = 0.f, inv = 1.f;
-  if (a.mean_std) { mu = a.mean_std[2 * xslot]; inv = 1.f / a.mean_std[2 * xslot + 1]; }
+  if (a.mean_std) { mu = a.mean_std[2 * xstat]; inv = 1.f / a.mean_std[2 * xstat + 1]; }
   const int zslot = a.mix_slot[b * 2 + v];
   const bool mix = zslot >= 0;
-  const float* zp = a.lms + static_cast<long long>(mix ? zslot : 0) * plane;
+  const int zstat = a.mix_stat ? a.mix_stat[b * 2 + v] : zslot;
+  const float* zbase = (a.mix_rank && mix) ? a.peer_lms[a.mix_rank[b * 2 + v]] : a.lms;   // a peer's ring: loads over NVLink
+  const float* zp = zbase + static_cast<long long>(mix ? zslot : 0) * plane;
   float zmu = 0.f, zinv = 1.f;
-  if (mix && a.mean_std) { zmu = a.mean_std[2 * zslot]; zinv = 1.f / a.mean_std[2 * zslot + 1]; }
+  if (mix && a.mean_std) { zmu = a.mean_std[2 * zstat]; zinv = 1.f / a.mean_std[2 * zstat + 1]; }
   const float al = a.alpha[b * 2 + v];
   const float wx = 1.f - al, wz = al;
   const bool logmix = mix && a.c.log_mixup;
@@ -301,14 +310,28 @@ extern "C" int assl_two_views_ordered_f32(const assl_view_cfg* vc, const float* 
                                           const int32_t* clip_slot, const int32_t* mix_slot, const float* alpha,
                                           const int32_t* crop, const int32_t* order, int64_t B, float* view1,
                                           float* view2, void* stream) {
+  return assl_two_views_global_f32(vc, lms, nullptr, 0, mean_std, clip_slot, nullptr, mix_slot, nullptr, nullptr, alpha, crop,
+                                   order, B, view1, view2, stream);
+}
+
+extern "C" int assl_two_views_global_f32(const assl_view_cfg* vc, const float* lms, const float* const* peer_lms,
+                                         int32_t world, const float* mean_std, const int32_t* clip_slot,
+                                         const int32_t* clip_stat, const int32_t* mix_slot, const int32_t* mix_rank,
+                                         const int32_t* mix_stat, const float* alpha, const int32_t* crop,
+                                         const int32_t* order, int64_t B, float* view1, float* view2, void* stream) {
   using namespace assl;
+  const int64_t cap = 0;
   if (!vc || !lms || !clip_slot || !mix_slot || !alpha || !crop || !view1 || !view2 || B < 0) return ASSL_ERR_INVALID_ARG;
+  if (world < 0 || world > ASSL_EXCHANGE_MAX_WORLD || (world > 0 && (!peer_lms || !mix_rank))) return ASSL_ERR_INVALID_ARG;
+  if ((clip_stat == nullptr) != (mix_stat == nullptr)) return ASSL_ERR_INVALID_ARG;
   if (vc->n_freq < 1 || vc->n_time < 1 || vc->canvas_h < vc->n_freq || vc->canvas_w < vc->n_time) return ASSL_ERR_INVALID_ARG;
   if (vc->interp != 0 && vc->interp != 1) return ASSL_ERR_INVALID_ARG;
   if (B == 0) return ASSL_OK;
   ViewArgs a;
   a.c = *vc; a.lms = lms; a.mean_std = mean_std; a.cap = cap; a.B = B;
   a.clip_slot = clip_slot; a.mix_slot = mix_slot; a.alpha = alpha; a.crop = crop; a.order = order;
+  a.mix_rank = world > 0 ? mix_rank : nullptr; a.clip_stat = clip_stat; a.mix_stat = mix_stat;
+  for (int r = 0; r < ASSL_EXCHANGE_MAX_WORLD; ++r) a.peer_lms[r] = r < world ? peer_lms[r] : nullptr;
   a.view1 = view1; a.view2 = view2;
   a.y0 = (vc->canvas_h - vc->n_freq) / 2;
   a.x0 = (vc->canvas_w - vc->n_time) / 2;

@@ -93,10 +93,10 @@ class StatsExchange:
             return None
         return cls(handle, rank, world, int(max_clips))
 
-    def run(self, state, sums, b, n_parts, elems, max_update, stats, slot0, cap):
+    def run(self, state, sums, b, n_parts, elems, max_update, stats, slot0, cap, write_all=False):
         _native.check(_native.lib().assl_running_stats_exchange(
             self.handle, _ptr(state), _ptr(sums), b, n_parts, elems, int(max_update), _ptr(stats), slot0, cap,
-            _stream_ptr()), "assl_running_stats_exchange")
+            1 if write_all else 0, _stream_ptr()), "assl_running_stats_exchange")
 
     def close(self):
         if self.handle:
@@ -104,10 +104,46 @@ class StatsExchange:
             self.handle = None
 
 
+class _RawCudaArray:
+    """A cudaMalloc'd buffer of the C library seen through ``__cuda_array_interface__`` (torch.as_tensor wraps it)."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False),
+                                         "version": 3, "strides": None}
+
+
+class PeerRing:
+    """The log-mel ring of the global-bank mode: allocated by the C library so that its CUDA IPC handle can be opened
+    by the other ranks of the node; ``ptrs`` = every rank's ring as mapped into this process."""
+
+    def __init__(self, shape, device):
+        import torch.distributed as dist
+        lib = _native.lib()
+        rank, world = _dist_world()
+        self.local = C.c_void_p()
+        mine = (C.c_ubyte * 64)()
+        nbytes = 4 * int(np.prod(shape))
+        with torch.cuda.device(device):
+            _native.check(lib.assl_peer_alloc(C.byref(self.local), nbytes, mine), "assl_peer_alloc")
+            everyone = torch.empty(world * 64, dtype=torch.uint8, device=device)
+            dist.all_gather_into_tensor(everyone, torch.tensor(list(mine), dtype=torch.uint8, device=device))
+            raw = bytes(everyone.cpu().tolist())
+            self.ptrs = (C.c_void_p * world)()
+            for r in range(world):
+                if r == rank:
+                    self.ptrs[r] = self.local.value
+                else:
+                    p = C.c_void_p()
+                    _native.check(lib.assl_peer_open(raw[64 * r:64 * (r + 1)], C.byref(p)), "assl_peer_open")
+                    self.ptrs[r] = p.value
+        self.rank, self.world = rank, world
+        self.tensor = torch.as_tensor(_RawCudaArray(self.local.value, shape), device=device)
+
+
 class ViewEngine:
     def __init__(self, n_memory=2048, pushes_per_clip=2, ratio=0.4, log_mixup=True,
                  virtual_crop_scale=(1.0, 1.5), interp="bicubic", normalize=True, max_update=None,
-                 max_batch=4096, sync_stats=True):
+                 max_batch=4096, sync_stats=True, global_bank=False):
         if interp not in INTERP:
             raise ValueError(f"interp must be one of {sorted(INTERP)}")
         self.n_memory, self.nv = int(n_memory), int(pushes_per_clip)
@@ -118,6 +154,20 @@ class ViewEngine:
         self.max_batch, self.sync_stats = int(max_batch), sync_stats
         self.history = -(-self.n_memory // self.nv)          # distinct clips the FIFO can still hold
         self.cap = self.history + self.max_batch
+        # global bank (optional): the FIFO runs over the GLOBAL clip order; bank entries are read from the
+        # peers' rings over NVLink.  Every step must bring exactly max_batch clips per rank.  The ring is
+        # steps_back + 2 steps deep: a step's clips can be picked for steps_back more steps, and a rank is never
+        # more than one statistics exchange ahead of the slowest reader.
+        self.global_bank = bool(global_bank) and _dist_world()[1] > 1
+        if self.global_bank:
+            if not (normalize and sync_stats):
+                raise ValueError("global_bank needs the synchronised running statistics (normalize and sync_stats)")
+            self.rank, self.world = _dist_world()
+            gb = self.world * self.max_batch
+            self.steps_back = -(-self.history // gb) if self.history else 0
+            self.cap = (self.steps_back + 2) * self.max_batch
+            self.gcap = (self.steps_back + 2) * gb
+            self.peer_ring = None
         self.clips_done = 0
         self.ring = self.stats = self.state = None
         self.f = self.t = None
@@ -127,8 +177,13 @@ class ViewEngine:
     def ensure(self, f, t, device):
         if self.ring is None:
             self.f, self.t = int(f), int(t)
-            self.ring = torch.empty((self.cap, self.f, self.t), dtype=torch.float32, device=device)
-            self.stats = torch.zeros((self.cap, 2), dtype=torch.float32, device=device)
+            if self.global_bank:
+                self.peer_ring = PeerRing((self.cap, self.f, self.t), device)
+                self.ring = self.peer_ring.tensor
+                self.stats = torch.zeros((self.gcap, 2), dtype=torch.float32, device=device)   # over GLOBAL clips
+            else:
+                self.ring = torch.empty((self.cap, self.f, self.t), dtype=torch.float32, device=device)
+                self.stats = torch.zeros((self.cap, 2), dtype=torch.float32, device=device)
             self.stats[:, 1] = 1.0
             self.state = torch.zeros(8, dtype=torch.float64, device=device)
         elif (self.f, self.t) != (int(f), int(t)):
@@ -155,6 +210,12 @@ class ViewEngine:
         elems = self.f * self.t
         if world > 1 and self.sync_stats and self._exchange is False:
             self._exchange = StatsExchange.open(self.max_batch, sums.device)
+        if self.global_bank:
+            if self._exchange is None or b != self.max_batch:
+                raise RuntimeError("global_bank needs the peer-memory exchange and exactly max_batch clips per rank and step")
+            self._exchange.run(self.state, sums, b, n_parts, elems, self.max_update, self.stats,
+                               (self.clips_done * world) % self.gcap, self.gcap, write_all=True)
+            return
         if world > 1 and self.sync_stats and self._exchange is not None and b <= self._exchange.max_clips:
             self._exchange.run(self.state, sums, b, n_parts, elems, self.max_update, self.stats, self.slot0, self.cap)
         elif world > 1 and self.sync_stats:
@@ -179,6 +240,8 @@ class ViewEngine:
         """Two views of the ``batch`` clips at the ring head, then advance the head."""
         ch, cw = canvas_size(self.f, self.t, self.vscale)
         validate_crops(params.crop, ch, cw)
+        if self.global_bank:
+            return self._launch_views_global(params, batch, device, ch, cw)
         g0 = self.clips_done
         src = params.src_clip
         if np.any(src >= g0 + batch) or np.any((src >= 0) & (src < g0 + batch - self.cap)):
@@ -197,6 +260,41 @@ class ViewEngine:
             C.byref(vcfg), _ptr(self.ring), _ptr(self.stats if self.normalize else None), self.cap,
             _ptr(d_clip), _ptr(d_mix), _ptr(d_alpha), _ptr(d_crop), _ptr(d_order), batch, _ptr(v1), _ptr(v2),
             _stream_ptr()), "assl_two_views_ordered_f32")
+        self.clips_done += batch
+        return v1, v2
+
+    def _launch_views_global(self, params, batch, device, ch, cw):
+        """``params.src_clip`` holds GLOBAL clip ids (the sampler drew over the global batch); this rank's slice."""
+        if batch != self.max_batch:
+            raise RuntimeError("global_bank needs exactly max_batch clips per rank and step")
+        w, bsz = self.world, self.max_batch
+        gb = w * bsz
+        step = self.clips_done // bsz
+        mine = step * gb + self.rank * bsz + np.arange(batch, dtype=np.int64)          # global ids of this rank's clips
+        src = np.asarray(params.src_clip, np.int64)
+        # (view 2 may pick the clip itself: the FIFO already holds view 1's push of it)
+        if np.any(src > mine[:, None]) or np.any((src >= 0) & (src < mine[:, None] - self.history)):
+            raise ValueError("mixup source outside the global bank")
+        has = src >= 0
+        s_step, s_in = np.divmod(np.where(has, src, 0), gb)
+        s_rank, s_b = np.divmod(s_in, bsz)
+        if np.any(has & (s_step < step - self.steps_back)):
+            raise ValueError("mixup source older than the ring keeps")
+        to_dev = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a, dt)).to(device, non_blocking=True)   # noqa: E731
+        d_mix = to_dev(np.where(has, (s_step * bsz + s_b) % self.cap, -1), np.int32)
+        d_rank = to_dev(np.where(has, s_rank, 0), np.int32)
+        d_mstat = to_dev(np.where(has, src % self.gcap, 0), np.int32)
+        d_clip = to_dev((self.clips_done + np.arange(batch, dtype=np.int64)) % self.cap, np.int32)
+        d_cstat = to_dev(mine % self.gcap, np.int32)
+        d_alpha, d_crop = to_dev(params.alpha, np.float32), to_dev(params.crop, np.int32)
+        d_order = torch.from_numpy(heavy_first(params.crop)).to(device, non_blocking=True)
+        v1 = torch.empty((batch, 1, self.f, self.t), dtype=torch.float32, device=device)
+        v2 = torch.empty_like(v1)
+        vcfg = _native.ViewCfg(self.f, self.t, ch, cw, INTERP[self.interp], 1 if self.log_mixup else 0)
+        _native.check(_native.lib().assl_two_views_global_f32(
+            C.byref(vcfg), _ptr(self.ring), self.peer_ring.ptrs, w, _ptr(self.stats), _ptr(d_clip), _ptr(d_cstat),
+            _ptr(d_mix), _ptr(d_rank), _ptr(d_mstat), _ptr(d_alpha), _ptr(d_crop), _ptr(d_order), batch, _ptr(v1), _ptr(v2),
+            _stream_ptr()), "assl_two_views_global_f32")
         self.clips_done += batch
         return v1, v2
 

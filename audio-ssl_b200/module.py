@@ -35,7 +35,7 @@ class AugmentationModule:
     """
 
     def __init__(self, config, len_of_files, *, interpolation="bicubic", sampler="reference",
-                 max_batch=4096, seed=0, sync_stats=True):
+                 max_batch=4096, seed=0, sync_stats=True, global_bank=False):
         pre = config["pretrain"]
         aug = pre["augmentations"]
         self.kmix = None
@@ -61,7 +61,8 @@ class AugmentationModule:
         max_update = 2 * len_of_files * 10 if self.pre_norm else None
         self.engine = ViewEngine(n_memory=2048 if mix else 0, pushes_per_clip=2, ratio=ratio, log_mixup=log_mixup,
                                  virtual_crop_scale=vscale, interp=interpolation, normalize=self.pre_norm,
-                                 max_update=max_update, max_batch=max_batch, sync_stats=sync_stats)
+                                 max_update=max_update, max_batch=max_batch, sync_stats=sync_stats,
+                                 global_bank=global_bank and mix is not None)
         kw = dict(ratio=ratio, n_memory=2048, freq_scale=fscale, time_scale=tscale, virtual_crop_scale=vscale,
                   pushes_per_clip=2, mixup=self.has_mix, crop=self.has_crop)
         if sampler == "reference":
@@ -101,7 +102,15 @@ class AugmentationModule:
         return both[:, 0], both[:, 1]
 
     def _params(self, params, lo, hi):
-        if params is None:
+        eng = self.engine
+        if params is None and eng.global_bank:
+            # the FIFO runs over the global clip order: every rank draws the parameters of the WHOLE global batch
+            # from the same generator state (same seed on every rank) and keeps its slice; src_clip = global ids
+            n = hi - lo
+            everyone = self.sampler.draw(eng.clips_done * eng.world, n * eng.world, eng.f, eng.t)
+            a, b = eng.rank * n, (eng.rank + 1) * n
+            p = ViewParams(everyone.alpha[a:b], everyone.src_clip[a:b], everyone.bank_index[a:b], everyone.crop[a:b])
+        elif params is None:
             p = self.sampler.draw(self.engine.clips_done, hi - lo, self.engine.f, self.engine.t)
         else:
             p = ViewParams(params.alpha[lo:hi], params.src_clip[lo:hi], params.bank_index[lo:hi], params.crop[lo:hi])
@@ -179,6 +188,9 @@ class UpstreamInputPipeline:
     def _ragged(self, clips, params):
         """Raw clips of any length: extract_window (+ L2 gain in the same pass) feeds the front end."""
         from .frontend import extract_windows, extract_windows_packed
+        if self.tfms.engine.global_bank:
+            raise ValueError("global_bank takes equal-length windows [B, L] (the window offsets of the other ranks' clips "
+                             "would have to be drawn here too)")
         if self.unit_length is None:
             raise ValueError("raw clips need a window length: config['pretrain']['input']['length_wave'] or unit_length=")
         eng, tf = self.tfms.engine, self.tfms

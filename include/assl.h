@@ -140,6 +140,34 @@ int assl_clip_normalize_f32(const float* x, float* y, int64_t B, int64_t elems, 
 int assl_clip_sums(const double* tile_sums, int64_t B, int64_t n_parts, double* clip_sums,
                    void* stream);
 
+/* -- global mixup bank across the GPUs of one node (optional) --------------------------------
+ * The reference's bank is per worker; with the batch sharded by clip that makes a multi-GPU run differ from
+ * one process on the unsharded batch.  In global-bank mode the FIFO runs over the GLOBAL clip order: a view may
+ * mix with a clip that lives in another rank's ring, and the kernel reads it there directly (P2P loads over
+ * NVLink) -- no copy, no collective.  Together with the statistics exchange this makes the sharded run equal
+ * to the single-stream run on the unsharded batch.
+ *
+ * assl_peer_alloc / assl_peer_open   a cudaMalloc'd buffer with its 64-byte CUDA IPC handle; the handle opened in
+ *                        another process of the same node (assl_peer_close / assl_peer_free undo them)
+ * assl_two_views_global_f32          as assl_two_views_ordered_f32, plus
+ *     peer_lms  HOST array of ``world`` pointers: every rank's log-mel ring as mapped here (own entry = lms)
+ *     mix_rank  [B,2] int32  whose ring holds the bank entry of view v (ignored where mix_slot < 0)
+ *     clip_stat [B], mix_stat [B,2] int32  slots of the (mean, std) pairs in ``mean_std``, which in this mode is
+ *               a ring over GLOBAL clips that every rank fills itself (assl_running_stats_exchange, write_all);
+ *               both NULL = the log-mel slots are used, as in the other entry points
+ * Ordering between ranks is the caller's: a peer's ring slot may be read once the statistics exchange of the
+ * step that wrote it has returned on this rank's stream (engine.ViewEngine keeps the ring three steps deep so
+ * that no rank overwrites a slot another rank may still read).                                            */
+int assl_peer_alloc(void** ptr, int64_t bytes, void* handle_out);
+int assl_peer_free(void* ptr);
+int assl_peer_open(const void* handle, void** ptr);
+int assl_peer_close(void* ptr);
+int assl_two_views_global_f32(const assl_view_cfg* cfg, const float* lms, const float* const* peer_lms,
+                              int32_t world, const float* mean_std, const int32_t* clip_slot,
+                              const int32_t* clip_stat, const int32_t* mix_slot, const int32_t* mix_rank,
+                              const int32_t* mix_stat, const float* alpha, const int32_t* crop,
+                              const int32_t* order, int64_t B, float* view1, float* view2, void* stream);
+
 /* -- running pre-normalisation across the GPUs of one node, over peer memory ----------------
  * With the batch sharded by clip (rank r owns clips [r*B, (r+1)*B) of the global order), the
  * running statistics of the reference's single stream need every rank's per-clip sums.  Instead
@@ -156,7 +184,9 @@ int assl_clip_sums(const double* tile_sums, int64_t B, int64_t n_parts, double* 
  *                        devices cannot reach each other -- fall back to assl_clip_sums + all-gather
  * assl_running_stats_exchange  arguments as assl_running_stats, except: pair_sums [B, n_parts, 2]
  *                        are THIS rank's clips, every rank must call it with the same B, the scan
- *                        runs over world * B clips and (mean, std) of the local slice is written.
+ *                        runs over world * B clips and (mean, std) of the local slice is written
+ *                        (write_all != 0: of ALL world * B clips, clip g -> slot (slot0 + g) % cap -- the
+ *                        global statistics ring of the global-bank mode).
  *                        A peer that does not show up within ~2 s sets state[7] = 1 (checked by
  *                        assl_exchange_error) instead of hanging the GPU.                        */
 typedef struct assl_exchange assl_exchange;
@@ -168,7 +198,7 @@ int assl_exchange_connect(assl_exchange* x, const void* all_handles);
 int assl_exchange_destroy(assl_exchange* x);
 int assl_running_stats_exchange(assl_exchange* x, double* state, const double* pair_sums, int64_t B,
                                 int64_t n_parts, int64_t elems, int64_t max_update, float* mean_std,
-                                int64_t slot0, int64_t cap, void* stream);
+                                int64_t slot0, int64_t cap, int32_t write_all, void* stream);
 
 /* -- two views -----------------------------------------------------------------------------
  * Replaces, per clip and per view, RunningNorm.forward's (x-mean)/std (augmentations.py:282),

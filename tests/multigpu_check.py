@@ -6,7 +6,9 @@
 1. the peer-memory path (assl_running_stats_exchange) == the NCCL path (assl_clip_sums + all-gather +
    assl_running_stats) == one process scanning the whole batch, bit for bit, over several steps (both parities,
    carries, a smaller last batch);
-2. the sharded front end + views (mixup off, explicit crops) == one process on the unsharded batch.
+2. the sharded front end + views (mixup off, explicit crops) == one process on the unsharded batch;
+3. global-bank mode (mixup ON, bank entries read from the peers' rings over NVLink) == one process on the
+   unsharded batch, bit for bit, over 9 steps.
 """
 import ctypes as C
 import os
@@ -75,10 +77,30 @@ def main():
     w1, w2 = single(wave, params=params)
     torch.cuda.synchronize()
     assert torch.equal(v1, w1[rank * b:(rank + 1) * b]) and torch.equal(v2, w2[rank * b:(rank + 1) * b])
+    # ---- global bank: mixup picks over the GLOBAL clip order, bank entries read from the peers' rings over NVLink.
+    #      9 steps: the ring (steps_back + 2 steps deep) wraps, picks reach back several steps and across ranks.
+    cfg_mix = {"pretrain": {"normalization": "mean_var", "input": {"length_wave": 0.5},
+                            "augmentations": {"MixupBYOLA": {"ratio": 0.4, "log_mixup_exp": True},
+                                              "RandomResizeCrop": {"virtual_crop_scale": [1.0, 1.5], "freq_crop_scale": [0.6, 1.5],
+                                                                   "time_crop_scale": [0.6, 1.5]}}}}
+    sharded = A.UpstreamInputPipeline(cfg_mix, 10 ** 6, max_batch=b, sampler="fast", seed=11, global_bank=True)
+    single = A.UpstreamInputPipeline(cfg_mix, 10 ** 6, max_batch=world * b, sampler="fast", seed=11, sync_stats=False)
+    remote = 0
+    for step in range(9):
+        wave = (torch.randn(world * b, 8000, generator=g) * 0.1).to(dev)
+        v1, v2 = sharded(wave[rank * b:(rank + 1) * b])
+        w1, w2 = single(wave)
+        torch.cuda.synchronize()
+        assert torch.equal(v1, w1[rank * b:(rank + 1) * b]) and torch.equal(v2, w2[rank * b:(rank + 1) * b]), step
+        src = sharded.tfms.last_params.src_clip
+        remote += int(np.sum((src >= 0) & ((src % (world * b)) // b != rank)))
+    assert remote > 0                                             # bank entries really came from other GPUs
+    assert float(sharded.tfms.engine.state[7]) == 0.0
     dist.barrier()
     ex.close()
     if rank == 0:
-        print(f"multigpu_check: OK on {world} GPUs (peer exchange == NCCL path == single stream, bit for bit)")
+        print(f"multigpu_check: OK on {world} GPUs (peer exchange == NCCL path == single stream, bit for bit; "
+              f"global bank == unsharded run, {remote} remote bank entries on rank 0)")
     dist.destroy_process_group()
 
 
