@@ -263,15 +263,13 @@ class ViewEngine:
         self.clips_done += batch
         return v1, v2
 
-    def _launch_views_global(self, params, batch, device, ch, cw):
-        """``params.src_clip`` holds GLOBAL clip ids (the sampler drew over the global batch); this rank's slice."""
-        if batch != self.max_batch:
-            raise RuntimeError("global_bank needs exactly max_batch clips per rank and step")
-        w, bsz = self.world, self.max_batch
-        gb = w * bsz
-        step = self.clips_done // bsz
-        mine = step * gb + self.rank * bsz + np.arange(batch, dtype=np.int64)          # global ids of this rank's clips
-        src = np.asarray(params.src_clip, np.int64)
+    def global_indices(self, src, step):
+        """Global-bank bookkeeping of one step: ``src`` [B,2] GLOBAL clip ids of the bank picks (-1 = none) of this
+        rank's clips -> int32 arrays (clip_slot [B], clip_stat [B], mix_slot [B,2], mix_rank [B,2], mix_stat [B,2]).
+        Global clip G of step s = G // (world*B) sits on rank (G % (world*B)) // B, local clip s*B + G % B."""
+        bsz, gb = self.max_batch, self.world * self.max_batch
+        local0 = step * bsz
+        mine = step * gb + self.rank * bsz + np.arange(bsz, dtype=np.int64)          # global ids of this rank's clips
         # (view 2 may pick the clip itself: the FIFO already holds view 1's push of it)
         if np.any(src > mine[:, None]) or np.any((src >= 0) & (src < mine[:, None] - self.history)):
             raise ValueError("mixup source outside the global bank")
@@ -280,14 +278,22 @@ class ViewEngine:
         s_rank, s_b = np.divmod(s_in, bsz)
         if np.any(has & (s_step < step - self.steps_back)):
             raise ValueError("mixup source older than the ring keeps")
-        to_dev = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a, dt)).to(device, non_blocking=True)   # noqa: E731
-        d_mix = to_dev(np.where(has, (s_step * bsz + s_b) % self.cap, -1), np.int32)
-        d_rank = to_dev(np.where(has, s_rank, 0), np.int32)
-        d_mstat = to_dev(np.where(has, src % self.gcap, 0), np.int32)
-        d_clip = to_dev((self.clips_done + np.arange(batch, dtype=np.int64)) % self.cap, np.int32)
-        d_cstat = to_dev(mine % self.gcap, np.int32)
-        d_alpha, d_crop = to_dev(params.alpha, np.float32), to_dev(params.crop, np.int32)
-        d_order = torch.from_numpy(heavy_first(params.crop)).to(device, non_blocking=True)
+        i32 = lambda a: np.ascontiguousarray(a, np.int32)   # noqa: E731
+        return (i32((local0 + np.arange(bsz, dtype=np.int64)) % self.cap), i32(mine % self.gcap),
+                i32(np.where(has, (s_step * bsz + s_b) % self.cap, -1)), i32(np.where(has, s_rank, 0)),
+                i32(np.where(has, src % self.gcap, 0)))
+
+    def _launch_views_global(self, params, batch, device, ch, cw):
+        """``params.src_clip`` holds GLOBAL clip ids (the sampler drew over the global batch); this rank's slice."""
+        if batch != self.max_batch:
+            raise RuntimeError("global_bank needs exactly max_batch clips per rank and step")
+        idx = self.global_indices(np.asarray(params.src_clip, np.int64), self.clips_done // self.max_batch)
+        to_dev = lambda a: torch.from_numpy(a).to(device, non_blocking=True)   # noqa: E731
+        d_clip, d_cstat, d_mix, d_rank, d_mstat = (to_dev(a) for a in idx)
+        w = self.world
+        d_alpha = to_dev(np.ascontiguousarray(params.alpha, np.float32))
+        d_crop = to_dev(np.ascontiguousarray(params.crop, np.int32))
+        d_order = to_dev(heavy_first(params.crop))
         v1 = torch.empty((batch, 1, self.f, self.t), dtype=torch.float32, device=device)
         v2 = torch.empty_like(v1)
         vcfg = _native.ViewCfg(self.f, self.t, ch, cw, INTERP[self.interp], 1 if self.log_mixup else 0)

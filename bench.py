@@ -187,7 +187,9 @@ def run_ours(args):
     B, L, W, K = args.batch, int(args.seconds * 16000), args.warmup, args.steps
     plan = A.Plan()
     T, tiles = plan.num_frames(L), plan.num_tiles(L)
-    tf = A.AugmentationModule(CFG, len_of_files=10 ** 7, sampler="fast", max_batch=B, seed=1234 + rank)
+    gbank = bool(args.global_bank) and world > 1
+    tf = A.AugmentationModule(CFG, len_of_files=10 ** 7, sampler="fast", max_batch=B, seed=1234 + (0 if gbank else rank),
+                              global_bank=gbank)
     eng = tf.engine
     eng.ensure(N_MELS, T, dev)
     cap = eng.cap
@@ -208,20 +210,32 @@ def run_ours(args):
         return [torch.from_numpy(a).to(dev) for a in (clip, mix, np.ascontiguousarray(p.alpha), np.ascontiguousarray(p.crop),
                                                       heavy_first(p.crop))]
 
-    steps_params = [upload(tf.sampler.draw(s * B, B, N_MELS, T), s * B) for s in range(W + K)]
+    def upload_global(step):
+        """Global bank: every rank draws the global batch from the same generator and keeps its slice (global clip ids)."""
+        p = tf.sampler.draw(step * B * world, B * world, N_MELS, T)
+        lo, hi = rank * B, (rank + 1) * B
+        idx = eng.global_indices(np.asarray(p.src_clip[lo:hi], np.int64), step)
+        arrs = list(idx) + [np.ascontiguousarray(p.alpha[lo:hi]), np.ascontiguousarray(p.crop[lo:hi]), heavy_first(p.crop[lo:hi])]
+        return [torch.from_numpy(a).to(dev) for a in arrs]
+
+    steps_params = [upload_global(s) if gbank else upload(tf.sampler.draw(s * B, B, N_MELS, T), s * B) for s in range(W + K)]
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(W + K)]
 
     exchange = StatsExchange.open(B, dev) if world > 1 else None        # peer-memory path; None -> NCCL all-gather
+    if gbank and exchange is None:
+        raise RuntimeError("--global-bank needs the peer-memory exchange")
 
     def device_step(s):
         slot0 = (s * B) % cap
-        clip, mix, alpha, crop, order = steps_params[s]
         e = evs[s]
         e[0].record()
         _native.check(lib.assl_logmel_f32(plan.handle, P(waves[s % args.rotate]), None, B, L, L, P(eng.ring), slot0, cap,
                                           P(sums), 0, stream()))
         e[1].record()
-        if exchange is not None:
+        if gbank:
+            exchange.run(eng.state, sums, B, tiles, N_MELS * T, max_update, eng.stats, (s * B * world) % eng.gcap, eng.gcap,
+                         write_all=True)
+        elif exchange is not None:
             exchange.run(eng.state, sums, B, tiles, N_MELS * T, max_update, eng.stats, slot0, cap)
         elif world > 1:
             _native.check(lib.assl_clip_sums(P(sums), B, tiles, P(local_sums), stream()))
@@ -232,8 +246,15 @@ def run_ours(args):
             _native.check(lib.assl_running_stats(P(eng.state), P(sums), B, tiles, N_MELS * T, max_update, 0, B,
                                                  P(eng.stats), slot0, cap, stream()))
         e[2].record()
-        _native.check(lib.assl_two_views_ordered_f32(C.byref(vcfg), P(eng.ring), P(eng.stats), cap, P(clip), P(mix), P(alpha),
-                                                     P(crop), P(order), B, P(v1), P(v2), stream()))
+        if gbank:
+            clip, cstat, mix, mrank, mstat, alpha, crop, order = steps_params[s]
+            _native.check(lib.assl_two_views_global_f32(C.byref(vcfg), P(eng.ring), eng.peer_ring.ptrs, world, P(eng.stats),
+                                                        P(clip), P(cstat), P(mix), P(mrank), P(mstat), P(alpha), P(crop),
+                                                        P(order), B, P(v1), P(v2), stream()))
+        else:
+            clip, mix, alpha, crop, order = steps_params[s]
+            _native.check(lib.assl_two_views_ordered_f32(C.byref(vcfg), P(eng.ring), P(eng.stats), cap, P(clip), P(mix), P(alpha),
+                                                         P(crop), P(order), B, P(v1), P(v2), stream()))
         e[3].record()
 
     def fence():
@@ -323,7 +344,9 @@ def run_ours(args):
         "dtype": "f32", "data": "synthetic",
         "config": dict(workload_config(args, B), stats_exchange=("none (one GPU)" if world == 1 else
                                                                  "peer memory over NVLink, fused into the statistics kernel"
-                                                                 if exchange is not None else "NCCL all-gather")),
+                                                                 if exchange is not None else "NCCL all-gather"),
+                    mixup_bank=("global FIFO, bank entries read from the peers' rings over NVLink (optional mode)" if gbank
+                                else "rank-local FIFO (as each reference worker's)")),
         "roofline": {"bound": "hbm", "kernel": "logmel_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
                      "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": B * a_fe, "kernel_ms": k_ms[0]},
@@ -359,6 +382,9 @@ def main():
     ap.add_argument("--rotate", type=int, default=4, help="distinct input batches cycled through (L2 hygiene)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="wall seconds of one CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--global-bank", action="store_true",
+                    help="N > 1 only, not the headline configuration: mixup FIFO over the global clip order, bank entries read "
+                         "from the peers' rings over NVLink (SURVEY 8e, optional mode)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
