@@ -86,3 +86,61 @@ def test_closed_form_continues_across_calls():
     mu2, sd2 = closed_form_stats(sums[11:], 24, n0=11, sum_m=m[1:].sum(), sum_v=v[1:].sum())
     np.testing.assert_allclose(np.concatenate([mu1, mu2]), want[:, 0], rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(np.concatenate([sd1, sd2]), want[:, 1], rtol=1e-4, atol=1e-5)
+
+
+def _worker_global(rank, world, port, out_q):
+    """Global-bank bookkeeping on the host (no GPU): every rank draws the global batch from the same generator,
+    keeps its slice and maps global clip ids to (rank, ring slot, statistics slot)."""
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import audiossl_b200 as A
+    from audiossl_b200.engine import ViewEngine
+    b = 96
+    eng = ViewEngine(max_batch=b, max_update=10 ** 6, global_bank=True)
+    smp = A.FastSampler(seed=4)
+    rows = []
+    for step in range(14):
+        p = smp.draw(step * b * world, b * world, 64, 51)
+        src = p.src_clip[rank * b:(rank + 1) * b].astype(np.int64)
+        rows.append((src,) + eng.global_indices(src, step))
+    out_q.put((rank, eng.cap, eng.gcap, eng.steps_back, rows))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_global_bank_index_mapping():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    world, b = 2, 96
+    procs = [ctx.Process(target=_worker_global, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, cap, gcap, steps_back, rows in res:
+        assert steps_back == -(-1024 // (world * b)) and cap == (steps_back + 2) * b and gcap == cap * world
+        # replay: where every global clip was written (rank, slot) and which statistics slot it got
+        where = {}
+        for step, (src, clip_slot, clip_stat, mix_slot, mix_rank, mix_stat) in enumerate(rows):
+            for r in range(world):
+                for i in range(b):
+                    where[step * world * b + r * b + i] = (r, (step * b + i) % cap)
+            mine = step * world * b + rank * b + np.arange(b)
+            assert np.array_equal(clip_slot, [where[g][1] for g in mine]) and np.array_equal(clip_stat, mine % gcap)
+            for i in range(b):
+                for v in range(2):
+                    g = src[i, v]
+                    if g < 0:
+                        assert mix_slot[i, v] == -1
+                        continue
+                    assert mine[i] - 1024 <= g <= mine[i]
+                    assert (mix_rank[i, v], mix_slot[i, v]) == where[g] and mix_stat[i, v] == g % gcap
+                    # nothing has overwritten that slot since: the next clip to land there is cap local clips later
+                    assert (g // (world * b)) * b + g % b + cap > step * b + b - 1
+    from audiossl_b200.engine import heavy_first
+    crop = np.array([[[0, 0, 40, 60], [0, 0, 64, 151]], [[0, 0, 64, 100], [0, 0, 38, 61]]], np.int32)
+    assert heavy_first(crop).tolist() == [1, 2, 3, 0]      # rows x 32-column groups: 64x5, 64x4, 38x3, 40x2
