@@ -70,25 +70,27 @@ __device__ inline void clip_total8(const double* sums, long long idx, long long 
   *sx = a; *sxx = b;
 }
 
-// Peer-memory exchange of the per-clip sums (assl_running_stats_exchange): where every rank's buffers of the
-// current parity are, as mapped into this process.
+// Peer-memory exchange of the per-clip sums (assl_running_stats_exchange): where every rank's buffer of the
+// current parity is, as mapped into this process.  A record is 32 bytes per clip, written and read as 8-byte
+// words {32 bits of data, 32-bit call number} -- each word carries its own flag, so the receiver needs no fence
+// and no separate flag round trip: it polls the record until all four words show this call's number (the way
+// NCCL's LL protocol moves small messages).
 struct PeerArgs {
   int world = 0;                 // 0 = single process, no exchange
   int rank = 0;
   long long b_local = 0;         // clips of this rank (the same on every rank)
   long long n_parts_local = 0;
   const double* pair_sums = nullptr;                          // this rank's [b_local, n_parts_local, 2]
-  unsigned long long seq = 0;                                 // this call's number, what the flags are raised to
-  double2* peer_sums[ASSL_EXCHANGE_MAX_WORLD] = {};           // rank j's gathered [world * b_local] buffer
-  unsigned long long* peer_flags[ASSL_EXCHANGE_MAX_WORLD] = {};   // rank j's flags [world]: slice of rank i has landed
+  unsigned seq = 0;                                           // this call's number (never 0)
+  uint4* peer_rec[ASSL_EXCHANGE_MAX_WORLD] = {};              // rank j's records [world * b_local][2]
 };
 
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+__device__ __forceinline__ void st_volatile_v4(uint4* p, uint4 v) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+__device__ __forceinline__ uint4 ld_volatile_v4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
 
@@ -119,34 +121,25 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
   double carry_m = state[1], carry_v = state[2];
   if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); }
 
+  __shared__ int s_late;
+  if (tid == 0) s_late = 0;
   if (px.world > 0) {
-    // ---- exchange: totals of this rank's clips -> the slice [rank * b_local, ...) of EVERY rank's buffer (stores
-    //      over NVLink for the peers), then one flag per peer with system-scope release; then wait until every
-    //      rank's slice has landed here.  The scan below then reads the local buffer (sums, n_parts = 1).
-    __shared__ int s_late;
-    if (tid == 0) s_late = 0;
+    // ---- exchange, sending side: totals of this rank's clips -> the records [rank * b_local, ...) of EVERY rank's
+    //      buffer (stores over NVLink for the peers; the local copy goes the same way)
     for (long long base = 0; base < px.b_local; base += kScanThreads) {
       const long long idx = base + rank * (kScanThreads / 8) + (tid >> 3);
       double sx, sxx;
       clip_total8(px.pair_sums, idx, px.b_local, px.n_parts_local, tid & 7, &sx, &sxx);
       if ((tid & 7) == 0 && idx < px.b_local) {
-        const double2 v = make_double2(sx, sxx);
-        for (int j = 0; j < px.world; ++j) px.peer_sums[j][px.rank * px.b_local + idx] = v;
+        const uint4 ra = make_uint4(__double2loint(sx), px.seq, __double2hiint(sx), px.seq);
+        const uint4 rb = make_uint4(__double2loint(sxx), px.seq, __double2hiint(sxx), px.seq);
+        for (int j = 0; j < px.world; ++j) {
+          uint4* rec = px.peer_rec[j] + 2 * (px.rank * px.b_local + idx);
+          st_volatile_v4(rec, ra);
+          st_volatile_v4(rec + 1, rb);
+        }
       }
     }
-    __threadfence_system();
-    cluster.sync();                                  // every CTA's stores are fenced before the flags go up
-    if (rank == 0 && tid < px.world) st_release_sys(px.peer_flags[tid] + px.rank, px.seq);
-    if (tid < px.world) {
-      const unsigned long long* f = px.peer_flags[px.rank] + tid;
-      const long long t0 = clock64();
-      while (ld_acquire_sys(f) < px.seq) {
-        if (clock64() - t0 > 4000000000ll) { s_late = 1; break; }   // ~2 s: a peer is gone; do not hang the GPU
-        __nanosleep(100);
-      }
-    }
-    __syncthreads();
-    if (rank == 0 && tid == 0 && s_late) state[7] = 1.0;
   }
 
   for (long long sbase = 0; sbase < n_clips; sbase += static_cast<long long>(kStatCtas) * kScanThreads) {
@@ -155,7 +148,18 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
                                               ? kStatCtas : (left + kScanThreads - 1) / kScanThreads);
     if (n_parts == 1) {                              // per-clip sums: the owner loads its chunk
       const long long idx = sbase + rank * kScanThreads + tid;
-      if (idx < n_clips) {
+      if (idx < n_clips && px.world > 0) {           // receiving side: poll this clip's record until it is this call's
+        const uint4* rec = px.peer_rec[px.rank] + 2 * idx;
+        const long long t0 = clock64();
+        uint4 ra, rb;
+        while (true) {
+          ra = ld_volatile_v4(rec); rb = ld_volatile_v4(rec + 1);
+          if (ra.y == px.seq && ra.w == px.seq && rb.y == px.seq && rb.w == px.seq) break;
+          if (clock64() - t0 > 4000000000ll) { s_late = 1; break; }   // ~2 s: a peer is gone; do not hang the GPU
+          __nanosleep(64);
+        }
+        s_m[tid] = __hiloint2double(ra.z, ra.x) * inv_elems; s_q[tid] = __hiloint2double(rb.z, rb.x) * inv_elems;
+      } else if (idx < n_clips) {
         const double2 v = reinterpret_cast<const double2*>(sums)[idx];
         s_m[tid] = v.x * inv_elems; s_q[tid] = v.y * inv_elems;
       }
@@ -226,6 +230,7 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
       mean_std[2 * s + 1] = my_std;
     }
   }
+  if (tid == 0 && s_late) state[7] = 1.0;           // (CTAs that left early saw their records arrive)
   if (rank == 0 && tid == 0) {
     long long n1 = n0;
     if (n0 < max_update) n1 = (n0 + n_clips < max_update) ? n0 + n_clips : max_update;
@@ -384,7 +389,7 @@ struct assl_exchange {
   long long max_clips = 0;
   unsigned char* local = nullptr;                         // this rank's buffer (cudaMalloc: IPC-exportable)
   unsigned char* peer[ASSL_EXCHANGE_MAX_WORLD] = {};       // every rank's buffer as mapped here (peer[rank] = local)
-  size_t sums_bytes = 0, bytes = 0;                       // per parity: [world * max_clips] double2; then 2 x flags
+  size_t rec_bytes = 0, bytes = 0;                        // per parity: [world * max_clips] records of 32 bytes
   unsigned long long seq = 0;
   bool connected = false;
 };
@@ -397,8 +402,8 @@ extern "C" int assl_exchange_create(assl_exchange** out, int32_t rank, int32_t w
   assl_exchange* x = new (std::nothrow) assl_exchange();
   if (!x) return ASSL_ERR_CUDA;
   x->rank = rank; x->world = world; x->max_clips = max_clips;
-  x->sums_bytes = (sizeof(double2) * static_cast<size_t>(world) * max_clips + 255) & ~static_cast<size_t>(255);
-  x->bytes = 2 * x->sums_bytes + 2 * sizeof(unsigned long long) * ASSL_EXCHANGE_MAX_WORLD;
+  x->rec_bytes = (32 * static_cast<size_t>(world) * max_clips + 255) & ~static_cast<size_t>(255);
+  x->bytes = 2 * x->rec_bytes;
   cudaIpcMemHandle_t h;
   if (cudaMalloc(reinterpret_cast<void**>(&x->local), x->bytes) != cudaSuccess || cudaMemset(x->local, 0, x->bytes) != cudaSuccess ||
       cudaIpcGetMemHandle(&h, x->local) != cudaSuccess) {
@@ -447,14 +452,12 @@ extern "C" int assl_running_stats_exchange(assl_exchange* x, double* state, cons
   if (reinterpret_cast<uintptr_t>(pair_sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;
   PeerArgs px;
   px.world = x->world; px.rank = x->rank; px.b_local = B; px.n_parts_local = n_parts; px.pair_sums = pair_sums;
-  px.seq = ++x->seq;
-  const size_t parity = static_cast<size_t>(px.seq & 1);
-  for (int r = 0; r < x->world; ++r) {
-    px.peer_sums[r] = reinterpret_cast<double2*>(x->peer[r] + parity * x->sums_bytes);
-    px.peer_flags[r] = reinterpret_cast<unsigned long long*>(x->peer[r] + 2 * x->sums_bytes) + parity * ASSL_EXCHANGE_MAX_WORLD;
-  }
+  ++x->seq;
+  px.seq = static_cast<unsigned>(x->seq & 0x7fffffffu) | 0x80000000u;       // never 0 (the buffer starts zeroed)
+  const size_t parity = static_cast<size_t>(x->seq & 1);
+  for (int r = 0; r < x->world; ++r) px.peer_rec[r] = reinterpret_cast<uint4*>(x->peer[r] + parity * x->rec_bytes);
   running_stats_kernel<<<kStatCtas, kScanThreads, 0, as_stream(stream)>>>(
-      state, reinterpret_cast<const double*>(px.peer_sums[x->rank]), n_all, 1, 1.0 / static_cast<double>(elems), max_update,
+      state, pair_sums, n_all, 1, 1.0 / static_cast<double>(elems), max_update,
       write_all ? 0 : static_cast<long long>(x->rank) * B, write_all ? n_all : B, mean_std, slot0, cap, px);
   return launch_status();
 }

@@ -173,12 +173,13 @@ int assl_two_views_global_f32(const assl_view_cfg* cfg, const float* lms, const 
  * running statistics of the reference's single stream need every rank's per-clip sums.  Instead
  * of reduce -> NCCL all-gather -> scan (three launches and a collective's latency), ONE kernel per
  * rank reduces its own clips, stores the per-clip sums straight into every peer's buffer over
- * NVLink (P2P stores), raises a per-rank flag with system-scope release, waits for the peers'
- * flags and runs the scan over the global batch.  No host synchronisation, nothing but that
+ * NVLink (P2P stores of 8-byte words that each carry the call number as their own flag, like NCCL's
+ * LL protocol), polls its own buffer until every rank's records show this call's number and runs
+ * the scan over the global batch.  No host synchronisation, nothing but that
  * kernel on the stream.
  *
  * assl_exchange_create   allocates this rank's buffer (room for world * max_clips per-clip sums, two
- *                        parities, flags) and writes its 64-byte CUDA IPC handle to handle_out
+ *                        parities, 32-byte flagged records) and writes its 64-byte CUDA IPC handle to handle_out
  * assl_exchange_connect  all_handles = world * 64 bytes, rank-major (all-gather them with any host
  *                        or device collective); maps the peers' buffers.  ASSL_ERR_CUDA when the
  *                        devices cannot reach each other -- fall back to assl_clip_sums + all-gather
