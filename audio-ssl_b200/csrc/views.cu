@@ -88,20 +88,23 @@ __host__ __device__ inline size_t views_smem_bytes(int canvas_h, int src_w, int 
 
 // ---- stage A: normalise + mix the crop span [0,h) x [xs_lo, xs_lo+nsx) into shared memory, G groups of 32 columns.
 //      exp(xn) = ex2(x*a + b) with a = log2e/std, b = -mean*log2e/std: one FFMA + one MUFU per operand.
-template <int G>
+template <int G, bool GB>
 __device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, long long b, int v, int h, int ci, int cj,
                                               int xs_lo, int nsx, int lane, int warp) {
   const int F = a.c.n_freq, T = a.c.n_time;
   const int plane = F * T;
+  // GB (global bank, a separate instantiation so the default kernel keeps its register budget): the bank entry may
+  // sit in a peer's ring (loads over NVLink) and the (mean, std) pairs live in a ring over global clips
   const int xslot = a.clip_slot[b];
-  const int xstat = a.clip_stat ? a.clip_stat[b] : xslot;
+  const int xstat = (GB && a.clip_stat) ? a.clip_stat[b] : xslot;
   const float* xp = a.lms + static_cast<long long>(xslot) * plane;
   float mu = 0.f, inv = 1.f;
   if (a.mean_std) { mu = a.mean_std[2 * xstat]; inv = 1.f / a.mean_std[2 * xstat + 1]; }
   const int zslot = a.mix_slot[b * 2 + v];
   const bool mix = zslot >= 0;
-  const int zstat = a.mix_stat ? a.mix_stat[b * 2 + v] : zslot;
-  const float* zbase = (a.mix_rank && mix) ? a.peer_lms[a.mix_rank[b * 2 + v]] : a.lms;   // a peer's ring: loads over NVLink
+  const int zstat = (GB && a.mix_stat) ? a.mix_stat[b * 2 + v] : zslot;
+  const float* zbase = a.lms;
+  if (GB) { if (a.mix_rank && mix) zbase = a.peer_lms[a.mix_rank[b * 2 + v]]; }
   const float* zp = zbase + static_cast<long long>(mix ? zslot : 0) * plane;
   float zmu = 0.f, zinv = 1.f;
   if (mix && a.mean_std) { zmu = a.mean_std[2 * zstat]; zinv = 1.f / a.mean_std[2 * zstat + 1]; }
@@ -164,7 +167,7 @@ __device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, l
 }
 
 // TW = output frames per tile; CG = 32-column groups of the staged crop span a warp loads per row
-template <int TW, int CG>
+template <int TW, int CG, bool GB>
 __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int F = a.c.n_freq, T = a.c.n_time;
@@ -209,11 +212,11 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
 
   // ---- stage A, with as many 32-column groups as THIS crop span needs (the span follows the drawn crop width)
   switch ((nsx + 31) >> 5) {
-    case 1: mix_crop_span<1>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
-    case 2: mix_crop_span<(CG >= 2 ? 2 : CG)>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
-    case 3: mix_crop_span<(CG >= 3 ? 3 : CG)>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
-    case 4: mix_crop_span<(CG >= 4 ? 4 : CG)>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
-    default: mix_crop_span<CG>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
+    case 1: mix_crop_span<1, GB>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
+    case 2: mix_crop_span<(CG >= 2 ? 2 : CG), GB>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
+    case 3: mix_crop_span<(CG >= 3 ? 3 : CG), GB>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
+    case 4: mix_crop_span<(CG >= 4 ? 4 : CG), GB>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
+    default: mix_crop_span<CG, GB>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
   }
   __syncthreads();
 
@@ -274,16 +277,23 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
   }
 }
 
+template <int TW, int CG, bool GB>
+int launch_views_kernel(ViewArgs& a, size_t smem, unsigned grid, cudaStream_t st) {
+  if (cudaFuncSetAttribute(two_views_kernel<TW, CG, GB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
+    return ASSL_ERR_CUDA;
+  two_views_kernel<TW, CG, GB><<<grid, kViewThreads, smem, st>>>(a);
+  return launch_status();
+}
+
 template <int TW, int CG>
 int launch_views_cg(ViewArgs& a, cudaStream_t st) {
   const size_t smem = views_smem_bytes(a.c.canvas_h, a.src_w, a.c.n_freq);
   if (smem > 227 * 1024) return ASSL_ERR_UNSUPPORTED;
-  if (cudaFuncSetAttribute(two_views_kernel<TW, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
-    return ASSL_ERR_CUDA;
   const long long grid = a.B * 2 * a.tiles_t;
   if (grid > 0x7fffffffll) return ASSL_ERR_UNSUPPORTED;
-  two_views_kernel<TW, CG><<<static_cast<unsigned>(grid), kViewThreads, smem, st>>>(a);
-  return launch_status();
+  const bool global_bank = a.mix_rank || a.clip_stat;
+  return global_bank ? launch_views_kernel<TW, CG, true>(a, smem, static_cast<unsigned>(grid), st)
+                     : launch_views_kernel<TW, CG, false>(a, smem, static_cast<unsigned>(grid), st);
 }
 
 template <int TW>
