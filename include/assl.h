@@ -72,7 +72,7 @@ int assl_plan_create(assl_plan** out, const assl_cfg* cfg);
 int assl_plan_destroy(assl_plan* plan);
 /* Frames per clip of L samples: 1 + L / hop (librosa.stft, center=True).  <0 on error. */
 int64_t assl_plan_num_frames(const assl_plan* plan, int64_t n_samples);
-/* Parts per clip of ``tile_sums`` (tiles of 8 frame pairs that can touch one clip; second dim). */
+/* Parts per clip of ``tile_sums`` (second dim): one per frame pair, ceil(T / 2). */
 int64_t assl_plan_num_tiles(const assl_plan* plan, int64_t n_samples);
 /* Copy the dense filterbank [n_mels, 1 + n_fft/2] (fp32) to HOST memory -- for parity tests. */
 int assl_plan_filterbank(const assl_plan* plan, float* host_out);
@@ -85,7 +85,7 @@ int assl_plan_filterbank(const assl_plan* plan, float* host_out);
  * wave_gain optional [B] fp32 per-clip scale applied on load (the reference's F.normalize(p=2),
  *           src/dataset/upstream_dataset.py:62-63, fused); NULL = 1
  * lms       ring/array of [n_mels, T] fp32 slots, see "Ring" above
- * tile_sums optional [B, num_tiles, 2] fp64: per tile (sum x, sum x^2) of the values written,
+ * tile_sums optional [B, num_tiles, 2] fp64, 16-byte aligned: per frame pair (sum x, sum x^2) of the values written,
  *           input of assl_running_stats; NULL to skip
  * out_kind  0 = log-mel (extract_log_mel_spectrogram), 1 = mel power (MelSpectrogramLibrosa.__call__
  *           alone, i.e. without the final log(. + eps)); add 2 for time-major slots [T, n_mels], the
