@@ -158,6 +158,24 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   float* buf = s_wave + warp * a.wave_floats;
 
   if (lane == 0) mbar_init(bar, 1);
+  const int span = kNfft + a.hop;                    // samples the two frames of a pair touch
+  const int stride = static_cast<int>(gridDim.x) * n_warps;
+  // producer side of the warp's pipeline (lane 0): bulk-copy the in-range part of a pair's span
+  auto issue = [&](int p) {
+    const PairSpan s = pair_span(a, p, span);
+    const unsigned bytes = static_cast<unsigned>(s.hi - s.lo) * 4u;
+    mbar_expect_tx(bar, bytes);
+    if (bytes) bulk_g2s(buf + s.lo, a.wave + s.clip * a.ld + s.base + s.lo, bytes, bar);
+  };
+  // warp-major numbering: consecutive pairs go to different SMs, so the last, partial round (52224 pairs over 2368
+  // warps = 22.05 rounds) is one uncontended warp on each of 128 SMs instead of 16 contending warps on 8 of them
+  const int first = warp * static_cast<int>(gridDim.x) + static_cast<int>(blockIdx.x);
+  // the first copy flies while the tables below are loaded (only this warp's lane 0 touches its barrier and buffer)
+  if (a.bulk_ok && lane == 0 && first < a.total_pairs) {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    issue(first);
+  }
+
   // Inter-stage twiddles w^k2 (w = W_1024^lane): only w^8, w^16, w^24 and w^1..w^7 are kept per lane; the
   // other 21 are applied as two rotations, (z * w^b) * w^(8a), trading 42 FFMA2/FMUL2 per transform for two
   // thirds of the table's shared-memory traffic
@@ -177,22 +195,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   for (int i = tid; i <= a.n_mels; i += n_threads) s_pos[i] = a.iv_pos[i];
   // (s_ex needs no clearing: every power bin a part reads is either written by this pair or selected away,
   //  never multiplied, and every interval total is started before it is read)
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();                                   // the only CTA-wide barrier
-
-  const int span = kNfft + a.hop;                    // samples the two frames of a pair touch
-  const int stride = static_cast<int>(gridDim.x) * n_warps;
-  // producer side of the warp's pipeline (lane 0): bulk-copy the in-range part of a pair's span
-  auto issue = [&](int p) {
-    const PairSpan s = pair_span(a, p, span);
-    const unsigned bytes = static_cast<unsigned>(s.hi - s.lo) * 4u;
-    mbar_expect_tx(bar, bytes);
-    if (bytes) bulk_g2s(buf + s.lo, a.wave + s.clip * a.ld + s.base + s.lo, bytes, bar);
-  };
-  // warp-major numbering: consecutive pairs go to different SMs, so the last, partial round (52224 pairs over 2368
-  // warps = 22.05 rounds) is one uncontended warp on each of 128 SMs instead of 16 contending warps on 8 of them
-  const int first = warp * static_cast<int>(gridDim.x) + static_cast<int>(blockIdx.x);
-  if (a.bulk_ok && lane == 0 && first < a.total_pairs) issue(first);
 
   c32* ex = reinterpret_cast<c32*>(s_ex + warp * kExWarp);
   unsigned it = 0;
