@@ -3,6 +3,7 @@
 
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include <vector>
 
@@ -25,6 +26,31 @@ inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s
 
 inline int launch_status() {
   return cudaPeekAtLastError() == cudaSuccess ? ASSL_OK : ASSL_ERR_CUDA;
+}
+
+// ---- programmatic dependent launch (PDL).  Every kernel of the path is launched with the programmatic-stream-
+// serialization attribute, calls pdl_wait() before its first access to memory an earlier kernel may have written
+// and pdl_launch_dependents() early, so the next kernel's CTAs are scheduled onto SMs as they drain and have their
+// prologue behind them when the previous grid completes (pdl_wait returns only after the whole previous grid has
+// finished and its writes are visible: the data dependencies are exactly those of plain stream order).  Launched
+// without the attribute, both calls are no-ops.  ASSL_PDL=0 turns the attribute off (A/B measurements).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("ASSL_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 __host__ __device__ inline long long ring_slot(long long slot0, long long b, long long cap) {

@@ -170,11 +170,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   // warp-major numbering: consecutive pairs go to different SMs, so the last, partial round (52224 pairs over 2368
   // warps = 22.05 rounds) is one uncontended warp on each of 128 SMs instead of 16 contending warps on 8 of them
   const int first = warp * static_cast<int>(gridDim.x) + static_cast<int>(blockIdx.x);
-  // the first copy flies while the tables below are loaded (only this warp's lane 0 touches its barrier and buffer)
-  if (a.bulk_ok && lane == 0 && first < a.total_pairs) {
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    issue(first);
-  }
+  // Launched behind another kernel of the path (PDL) this CTA gets its SM while that grid's last wave drains and
+  // loads the plan's tables (immutable, never written by a kernel) meanwhile; the waveform, the ring and the sums
+  // are touched only after pdl_wait() below.
+  pdl_launch_dependents();
 
   // Inter-stage twiddles w^k2 (w = W_1024^lane): only w^8, w^16, w^24 and w^1..w^7 are kept per lane; the
   // other 21 are applied as two rotations, (z * w^b) * w^(8a), trading 42 FFMA2/FMUL2 per transform for two
@@ -195,6 +194,12 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   for (int i = tid; i <= a.n_mels; i += n_threads) s_pos[i] = a.iv_pos[i];
   // (s_ex needs no clearing: every power bin a part reads is either written by this pair or selected away,
   //  never multiplied, and every interval total is started before it is read)
+  pdl_wait();
+  // the first copy flies while the other warps finish the tables (only this warp's lane 0 touches its barrier and buffer)
+  if (a.bulk_ok && lane == 0 && first < a.total_pairs) {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    issue(first);
+  }
   __syncthreads();                                   // the only CTA-wide barrier
 
   c32* ex = reinterpret_cast<c32*>(s_ex + warp * kExWarp);
@@ -394,7 +399,7 @@ template <int H32>
 int launch_logmel(const LogmelArgs& a, size_t smem, unsigned grid, int warps, cudaStream_t st) {
   if (cudaFuncSetAttribute(logmel_kernel<H32>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
     return ASSL_ERR_CUDA;
-  logmel_kernel<H32><<<grid, warps * 32, smem, st>>>(a);
+  if (launch_pdl(logmel_kernel<H32>, dim3(grid), dim3(warps * 32), smem, st, a) != cudaSuccess) return ASSL_ERR_CUDA;
   return launch_status();
 }
 

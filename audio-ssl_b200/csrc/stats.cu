@@ -117,6 +117,8 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
   __shared__ double s_tot[2][kStatCtas];           // chunk totals of m / of v, a full copy in every CTA
   __shared__ float s_frozen[2];
   const int tid = threadIdx.x;
+  pdl_launch_dependents();                           // (the two-view kernel's CTAs wait for this grid to complete)
+  pdl_wait();                                        // the log-mel kernel's per-pair sums are complete and visible
   const long long n0 = static_cast<long long>(state[0]);
   double carry_m = state[1], carry_v = state[2];
   if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); }
@@ -331,8 +333,11 @@ extern "C" int assl_running_stats(double* state, const double* sums, int64_t n_c
   if (cap > 0 && (count > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
   if (reinterpret_cast<uintptr_t>(sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;   // (sum, sum^2) pairs are read as one 16-byte word
   if (n_clips == 0) return ASSL_OK;
-  running_stats_kernel<<<kStatCtas, kScanThreads, 0, as_stream(stream)>>>(state, sums, n_clips, n_parts, 1.0 / static_cast<double>(elems),
-                                                                  max_update, first, count, mean_std, slot0, cap, PeerArgs());
+  if (launch_pdl(running_stats_kernel, dim3(kStatCtas), dim3(kScanThreads), 0, as_stream(stream), state, sums,
+                 static_cast<long long>(n_clips), static_cast<long long>(n_parts), 1.0 / static_cast<double>(elems),
+                 static_cast<long long>(max_update), static_cast<long long>(first), static_cast<long long>(count), mean_std,
+                 static_cast<long long>(slot0), static_cast<long long>(cap), PeerArgs()) != cudaSuccess)
+    return ASSL_ERR_CUDA;
   return launch_status();
 }
 
@@ -456,9 +461,11 @@ extern "C" int assl_running_stats_exchange(assl_exchange* x, double* state, cons
   px.seq = static_cast<unsigned>(x->seq & 0x7fffffffu) | 0x80000000u;       // never 0 (the buffer starts zeroed)
   const size_t parity = static_cast<size_t>(x->seq & 1);
   for (int r = 0; r < x->world; ++r) px.peer_rec[r] = reinterpret_cast<uint4*>(x->peer[r] + parity * x->rec_bytes);
-  running_stats_kernel<<<kStatCtas, kScanThreads, 0, as_stream(stream)>>>(
-      state, pair_sums, n_all, 1, 1.0 / static_cast<double>(elems), max_update,
-      write_all ? 0 : static_cast<long long>(x->rank) * B, write_all ? n_all : B, mean_std, slot0, cap, px);
+  if (launch_pdl(running_stats_kernel, dim3(kStatCtas), dim3(kScanThreads), 0, as_stream(stream), state, pair_sums, n_all,
+                 1ll, 1.0 / static_cast<double>(elems), static_cast<long long>(max_update),
+                 write_all ? 0ll : static_cast<long long>(x->rank) * B, write_all ? n_all : static_cast<long long>(B), mean_std,
+                 static_cast<long long>(slot0), static_cast<long long>(cap), px) != cudaSuccess)
+    return ASSL_ERR_CUDA;
   return launch_status();
 }
 

@@ -86,11 +86,17 @@ __host__ __device__ inline size_t views_smem_bytes(int canvas_h, int src_w, int 
          (sizeof(float) + sizeof(int)) * 4 * static_cast<size_t>(n_freq);
 }
 
-// ---- stage A: normalise + mix the crop span [0,h) x [xs_lo, xs_lo+nsx) into shared memory, G groups of 32 columns.
-//      exp(xn) = ex2(x*a + b) with a = log2e/std, b = -mean*log2e/std: one FFMA + one MUFU per operand.
-template <int G, bool GB>
-__device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, long long b, int v, int h, int ci, int cj,
-                                              int xs_lo, int nsx, int lane, int warp) {
+// ---- stage A: normalise + mix the crop span [0,h) x [xs_lo, xs_lo+nsx) into shared memory.
+//      Only the part of the span that lies inside the pasted clip is computed: lanes <-> its columns
+//      xs = xs_in0 + lane + 32 c, c < G = ceil(n_in / 32) (G chosen per CTA), i.e. clip columns lx_in0 + lane + 32 c --
+//      one 64-bit row pointer per lane and row, every load at an immediate offset, no per-element predicate or
+//      select (only the last group is clamped / guarded).  The zero canvas around the clip (augmentations.py:45-47)
+//      is two guarded stores per row.  exp(xn) = ex2(x*a + b) with a = log2e/std, b = -mean*log2e/std: one FFMA +
+//      one MUFU per operand.  LOGMIX (log-mixup-exp against a bank entry, the path's normal case) is a separate
+//      instantiation; the other modes (no bank entry yet, plain mixup) share the generic one.
+template <int G, bool GB, bool LOGMIX>
+__device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, long long b, int v, int h, int ci,
+                                              int lx_in0, int xs_in0, int n_in, int nsx, int lane, int warp) {
   const int F = a.c.n_freq, T = a.c.n_time;
   const int plane = F * T;
   // GB (global bank, a separate instantiation so the default kernel keeps its register budget): the bank entry may
@@ -101,7 +107,7 @@ __device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, l
   float mu = 0.f, inv = 1.f;
   if (a.mean_std) { mu = a.mean_std[2 * xstat]; inv = 1.f / a.mean_std[2 * xstat + 1]; }
   const int zslot = a.mix_slot[b * 2 + v];
-  const bool mix = zslot >= 0;
+  const bool mix = LOGMIX || zslot >= 0;
   const int zstat = (GB && a.mix_stat) ? a.mix_stat[b * 2 + v] : zslot;
   const float* zbase = a.lms;
   if (GB) { if (a.mix_rank && mix) zbase = a.peer_lms[a.mix_rank[b * 2 + v]]; }
@@ -110,60 +116,82 @@ __device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, l
   if (mix && a.mean_std) { zmu = a.mean_std[2 * zstat]; zinv = 1.f / a.mean_std[2 * zstat + 1]; }
   const float al = a.alpha[b * 2 + v];
   const float wx = 1.f - al, wz = al;
-  const bool logmix = mix && a.c.log_mixup;
   const float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
-  const float xa = logmix ? inv * kLog2e : inv, xb = -mu * xa;
-  const float za = logmix ? zinv * kLog2e : zinv, zb = -zmu * za;
-  // columns of the span that fall inside the pasted clip: lx = cj + xs_lo + xs - x0 in [0, T)
-  const int lx0 = cj + xs_lo - a.x0;
-  const int xs_in0 = max(0, -lx0), xs_in1 = min(nsx, T - lx0);
+  const float xa = LOGMIX ? inv * kLog2e : inv, xb = -mu * xa;
+  const float za = LOGMIX ? zinv * kLog2e : zinv, zb = -zmu * za;
+  constexpr int kColGroups = G;                               // 32 * G >= n_in, 32 * (G - 1) < n_in
+  const int col0 = lx_in0 + lane;                             // this lane's clip column of group 0
+  const int col_last = lx_in0 + min(lane + 32 * (kColGroups - 1), n_in - 1);   // last group: clamped into the clip
+  const bool last_ok = lane + 32 * (kColGroups - 1) < n_in;
+  const int ml = xs_in0, mr = nsx - (xs_in0 + n_in);          // canvas columns of the span left / right of the clip
+  // (pointers opaque to the compiler, which otherwise rebuilds every address as ring base + 64-bit offset)
+  asm volatile("" : "+l"(xp));
+  asm volatile("" : "+l"(zp));
   // Rows are taken kRowBatch at a time per warp and ALL their global loads are issued before any
-  // arithmetic, so a warp keeps 2 * kRowBatch * ceil(nsx/32) loads in flight instead of 2.
+  // arithmetic, so a warp keeps 2 * kRowBatch * G loads in flight instead of 2.
   constexpr int kRowBatch = 2;
-  constexpr int kColGroups = G;                               // 32 * G >= nsx (chosen per CTA)
   for (int yb = warp * kRowBatch; yb < h; yb += (kViewThreads / 32) * kRowBatch) {
     float xv[kRowBatch][kColGroups], zv[kRowBatch][kColGroups];
 #pragma unroll
     for (int r = 0; r < kRowBatch; ++r) {
-      const int ly = ci + yb + r - a.y0;
-      const bool row_in = (yb + r < h) && ly >= 0 && ly < F;     // warp-uniform
-      const float* xr = xp + ly * T + lx0;
-      const float* zr = zp + ly * T + lx0;
+      const int lyc = min(max(ci + yb + r - a.y0, 0), F - 1);  // warp-uniform; rows outside the clip are zero-filled below
+      const float* xr = xp + (lyc * T + col0);
+      const float* zr = zp + (lyc * T + col0);
 #pragma unroll
-      for (int c = 0; c < kColGroups; ++c) {
-        const int xs = lane + 32 * c;
-        const bool in = row_in && xs >= xs_in0 && xs < xs_in1;
-        xv[r][c] = in ? __ldg(xr + xs) : 0.f;
-        zv[r][c] = (in && mix) ? __ldg(zr + xs) : 0.f;
+      for (int c = 0; c < kColGroups - 1; ++c) {
+        xv[r][c] = __ldg(xr + 32 * c);
+        zv[r][c] = 0.f;
+        if (mix) zv[r][c] = __ldg(zr + 32 * c);                // CTA-uniform (compile-time true for LOGMIX)
       }
+      xv[r][kColGroups - 1] = __ldg(xp + (lyc * T + col_last));
+      zv[r][kColGroups - 1] = 0.f;
+      if (mix) zv[r][kColGroups - 1] = __ldg(zp + (lyc * T + col_last));
     }
 #pragma unroll
     for (int r = 0; r < kRowBatch; ++r) {
       const int y = yb + r;
       const int ly = ci + y - a.y0;
-      const bool row_in = ly >= 0 && ly < F;
-      float* drow = s_src + y * a.src_w;
+      float* row = s_src + y * a.src_w;
       if (y < h) {
+        if (ly >= 0 && ly < F) {                               // warp-uniform
+          float* drow = row + xs_in0 + lane;
 #pragma unroll
-        for (int c = 0; c < kColGroups; ++c) {
-          const int xs = lane + 32 * c;
-          // lanes outside the pasted clip computed on zeros and then selected away: no divergent region
-          const bool in = row_in && xs >= xs_in0 && xs < xs_in1;
-          const float xn = fmaf(xv[r][c], xa, xb);
-          float val;
-          if (logmix) {                                        // CTA-uniform
-            const float zn = fmaf(zv[r][c], za, zb);
-            val = kLn2 * lg2_approx(fmaf(wx, ex2_approx(xn), fmaf(wz, ex2_approx(zn), kLogEps)));
-          } else if (mix) {
-            val = fmaf(wz, fmaf(zv[r][c], za, zb), wx * xn);
-          } else {
-            val = xn;
+          for (int c = 0; c < kColGroups; ++c) {
+            const float xn = fmaf(xv[r][c], xa, xb);
+            float val;
+            if (LOGMIX) {
+              const float zn = fmaf(zv[r][c], za, zb);
+              val = kLn2 * lg2_approx(fmaf(wx, ex2_approx(xn), fmaf(wz, ex2_approx(zn), kLogEps)));
+            } else if (mix) {
+              val = fmaf(wz, fmaf(zv[r][c], za, zb), wx * xn);
+            } else {
+              val = xn;
+            }
+            if (c < kColGroups - 1 || last_ok) drow[32 * c] = val;
           }
-          if (xs < nsx) drow[xs] = in ? val : 0.f;             // zero canvas outside the pasted clip
+          if (lane < ml) row[lane] = 0.f;                      // zero canvas left and right of the pasted clip
+          if (lane < mr) row[xs_in0 + n_in + lane] = 0.f;
+          if (ml > 32 || mr > 32) {                            // (long clips: a tile that mostly misses the clip)
+#pragma unroll 1
+            for (int x = 32 + lane; x < ml; x += 32) row[x] = 0.f;
+#pragma unroll 1
+            for (int x = 32 + lane; x < mr; x += 32) row[xs_in0 + n_in + x] = 0.f;
+          }
+        } else {
+#pragma unroll 1
+          for (int x = lane; x < nsx; x += 32) row[x] = 0.f;   // canvas row above / below the clip
         }
       }
     }
   }
+}
+
+template <int G, bool GB>
+__device__ __forceinline__ void mix_crop_span_any(const ViewArgs& a, float* s_src, long long b, int v, int h, int ci,
+                                                  int lx_in0, int xs_in0, int n_in, int nsx, int lane, int warp) {
+  const bool logmix = a.mix_slot[b * 2 + v] >= 0 && a.c.log_mixup;          // CTA-uniform
+  if (logmix) mix_crop_span<G, GB, true>(a, s_src, b, v, h, ci, lx_in0, xs_in0, n_in, nsx, lane, warp);
+  else mix_crop_span<G, GB, false>(a, s_src, b, v, h, ci, lx_in0, xs_in0, n_in, nsx, lane, warp);
 }
 
 // TW = output frames per tile; CG = 32-column groups of the staged crop span a warp loads per row
@@ -179,6 +207,8 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   long long blk = blockIdx.x;
   const int tile = static_cast<int>(blk % a.tiles_t); blk /= a.tiles_t;
+  pdl_launch_dependents();                     // the next kernel may take SMs as this grid's last wave drains
+  pdl_wait();                                  // nothing global is read before the previous grid has completed
   if (a.order) blk = a.order[blk];             // CTAs start in launch order: the host puts the big crops first
   const int v = static_cast<int>(blk & 1);
   const long long b = blk >> 1;
@@ -210,13 +240,27 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
                          min(max(iy + 1, 0), h - 1), min(max(iy + 2, 0), h - 1));
   }
 
-  // ---- stage A, with as many 32-column groups as THIS crop span needs (the span follows the drawn crop width)
-  switch ((nsx + 31) >> 5) {
-    case 1: mix_crop_span<1, GB>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
-    case 2: mix_crop_span<(CG >= 2 ? 2 : CG), GB>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
-    case 3: mix_crop_span<(CG >= 3 ? 3 : CG), GB>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
-    case 4: mix_crop_span<(CG >= 4 ? 4 : CG), GB>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
-    default: mix_crop_span<CG, GB>(a, s_src, b, v, h, ci, cj, xs_lo, nsx, lane, warp); break;
+  // ---- stage A, with as many 32-column groups as the part of THIS crop span inside the clip needs
+  {
+    // columns of the span that fall inside the pasted clip: lx = cj + xs_lo + xs - x0 in [0, T)
+    const int lx0 = cj + xs_lo - a.x0;
+    const int xs_in0 = min(max(0, -lx0), nsx), xs_in1 = max(min(nsx, T - lx0), xs_in0);
+    const int n_in = xs_in1 - xs_in0, lx_in0 = lx0 + xs_in0;
+#define ASSL_STAGE_A(G) mix_crop_span_any<G, GB>(a, s_src, b, v, h, ci, lx_in0, xs_in0, n_in, nsx, lane, warp)
+    const int g = min((n_in + 31) >> 5, CG);                     // (the launcher guarantees CG >= ceil(n_in / 32))
+    if (g == 0) {                                                // the tile's span misses the clip: all canvas
+      for (int y = warp; y < h; y += kViewThreads / 32) {
+#pragma unroll 1
+        for (int x = lane; x < nsx; x += 32) s_src[y * a.src_w + x] = 0.f;
+      }
+    } else if (g == 1) { ASSL_STAGE_A(1); }
+    else if (CG >= 2 && g == 2) { ASSL_STAGE_A((CG >= 2 ? 2 : 1)); }
+    else if (CG >= 3 && g == 3) { ASSL_STAGE_A((CG >= 3 ? 3 : 1)); }
+    else if (CG >= 4 && g == 4) { ASSL_STAGE_A((CG >= 4 ? 4 : 1)); }
+    else if (CG >= 5 && g == 5) { ASSL_STAGE_A((CG >= 5 ? 5 : 1)); }
+    else if (CG >= 6 && g == 6) { ASSL_STAGE_A((CG >= 6 ? 6 : 1)); }
+    else if (CG >= 7) { ASSL_STAGE_A((CG >= 7 ? 7 : 1)); }
+#undef ASSL_STAGE_A
   }
   __syncthreads();
 
@@ -281,7 +325,7 @@ template <int TW, int CG, bool GB>
 int launch_views_kernel(ViewArgs& a, size_t smem, unsigned grid, cudaStream_t st) {
   if (cudaFuncSetAttribute(two_views_kernel<TW, CG, GB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
     return ASSL_ERR_CUDA;
-  two_views_kernel<TW, CG, GB><<<grid, kViewThreads, smem, st>>>(a);
+  if (launch_pdl(two_views_kernel<TW, CG, GB>, dim3(grid), dim3(kViewThreads), smem, st, a) != cudaSuccess) return ASSL_ERR_CUDA;
   return launch_status();
 }
 
