@@ -194,6 +194,120 @@ __device__ __forceinline__ void mix_crop_span_any(const ViewArgs& a, float* s_sr
   else mix_crop_span<G, GB, false>(a, s_src, b, v, h, ci, lx_in0, xs_in0, n_in, nsx, lane, warp);
 }
 
+// ---- stage B (along time: lanes <-> output columns, taps and weights in registers, warps <-> crop rows, each row
+//      overwritten in place by the warp that owns it) and stage C (along frequency, coalesced stores: lanes <->
+//      columns, warps <-> output rows).  NCM groups of 32 columns go through that mapping; with LEFT the tile has
+//      32 * NCM + n_left columns, 1 <= n_left <= kLeftMax, and the left-over columns are handled 32 / n_left rows
+//      at a time (lane -> (row, column)), so no lane idles on a mostly empty column group.
+constexpr int kLeftMax = 8;
+
+template <int NCM, bool LEFT>
+__device__ __forceinline__ void resample_tile(const ViewArgs& a, float* s_src, const float4* s_wy, const int4* s_ya,
+                                              float* outp, int h, int w, int ncol, int ox0, int xs_lo, int nsx, int bil,
+                                              int lane, int warp) {
+  const int F = a.c.n_freq, T = a.c.n_time;
+  constexpr int kWarps = kViewThreads / 32;
+  // left-over columns: lane -> (row rr of the iteration, column cc)
+  const int n_left = LEFT ? ncol - 32 * NCM : 1;
+  const int rpi = 32 / n_left;                                 // rows per iteration
+  const int rr = lane / n_left, cc = lane - rr * n_left;
+  const bool lv = LEFT && rr < rpi;
+  {
+    int xi[NCM][4];
+    float wt[NCM][4];
+#pragma unroll
+    for (int c = 0; c < NCM; ++c) {
+      const int col = LEFT ? lane + 32 * c : min(lane + 32 * c, ncol - 1);
+      int ix; float tx;
+      source_index(ox0 + col, w, T, &ix, &tx);
+      tap_weights(tx, bil, wt[c]);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) xi[c][q] = min(max(min(max(ix - 1 + q, 0), w - 1) - xs_lo, 0), nsx - 1);
+    }
+    float accl[2] = {0.f, 0.f};
+    if (LEFT) {                                                // every left-over output of this warp's rows, before
+      int ix; float tx;                                        // any of those rows is overwritten
+      float wl[4];
+      int xl[4];
+      source_index(ox0 + 32 * NCM + cc, w, T, &ix, &tx);
+      tap_weights(tx, bil, wl);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) xl[q] = min(max(min(max(ix - 1 + q, 0), w - 1) - xs_lo, 0), nsx - 1);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int y = warp + kWarps * (j * rpi + rr);
+        const float* row = s_src + ((lv && y < h) ? y : 0) * a.src_w;
+        float acc = row[xl[0]] * wl[0];
+        acc = fmaf(row[xl[1]], wl[1], acc);
+        acc = fmaf(row[xl[2]], wl[2], acc);
+        accl[j] = fmaf(row[xl[3]], wl[3], acc);
+      }
+      __syncwarp();
+    }
+    for (int y = warp; y < h; y += kWarps) {                   // a warp owns the row: read every tap, then overwrite
+      float* row = s_src + y * a.src_w;
+      float acc[NCM];
+#pragma unroll
+      for (int c = 0; c < NCM; ++c) {
+        acc[c] = row[xi[c][0]] * wt[c][0];
+        acc[c] = fmaf(row[xi[c][1]], wt[c][1], acc[c]);
+        acc[c] = fmaf(row[xi[c][2]], wt[c][2], acc[c]);
+        acc[c] = fmaf(row[xi[c][3]], wt[c][3], acc[c]);
+      }
+      __syncwarp();
+#pragma unroll
+      for (int c = 0; c < NCM; ++c)
+        if (LEFT || lane + 32 * c < ncol) row[lane + 32 * c] = acc[c];
+    }
+    if (LEFT) {
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int y = warp + kWarps * (j * rpi + rr);
+        if (lv && y < h) s_src[y * a.src_w + 32 * NCM + cc] = accl[j];
+      }
+    }
+  }
+  __syncthreads();
+
+  {
+    for (int oy = warp; oy < F; oy += kWarps) {
+      const float4 wy = s_wy[oy];
+      const int4 ya = s_ya[oy];
+      const float* r0 = s_src + ya.x * a.src_w + lane;
+      const float* r1 = s_src + ya.y * a.src_w + lane;
+      const float* r2 = s_src + ya.z * a.src_w + lane;
+      const float* r3 = s_src + ya.w * a.src_w + lane;
+      float* orow = outp + static_cast<long long>(oy) * T + lane;
+#pragma unroll
+      for (int c = 0; c < NCM; ++c) {
+        if (LEFT || lane + 32 * c < ncol) {
+          float acc = r0[32 * c] * wy.x;
+          acc = fmaf(r1[32 * c], wy.y, acc);
+          acc = fmaf(r2[32 * c], wy.z, acc);
+          acc = fmaf(r3[32 * c], wy.w, acc);
+          orow[32 * c] = acc;
+        }
+      }
+    }
+    if (LEFT) {
+      const int col = 32 * NCM + cc;
+      for (int k0 = 0; warp + kWarps * k0 < F; k0 += rpi) {
+        const int oy = warp + kWarps * (k0 + rr);
+        if (lv && oy < F) {
+          const float4 wy = s_wy[oy];
+          const int4 ya = s_ya[oy];
+          float acc = s_src[ya.x * a.src_w + col] * wy.x;
+          acc = fmaf(s_src[ya.y * a.src_w + col], wy.y, acc);
+          acc = fmaf(s_src[ya.z * a.src_w + col], wy.z, acc);
+          acc = fmaf(s_src[ya.w * a.src_w + col], wy.w, acc);
+          outp[static_cast<long long>(oy) * T + col] = acc;
+        }
+      }
+    }
+  }
+}
+
 // TW = output frames per tile; CG = 32-column groups of the staged crop span a warp loads per row
 template <int TW, int CG, bool GB>
 __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewArgs a) {
@@ -264,61 +378,15 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
   }
   __syncthreads();
 
+  // ---- stages B and C.  T = 101 is three full groups of 32 output columns and 5 left over: those are resampled
+  //      with lanes <-> (row, column) instead of wasting 27 lanes of a fourth group on every row
   constexpr int NC = TW / 32;                                  // output columns per lane: lane + 32*c
-  // ---- stage B: along time.  lanes <-> output columns (taps and weights in registers), warps <-> crop rows
-  {
-    int xi[NC][4];
-    float wt[NC][4];
-#pragma unroll
-    for (int c = 0; c < NC; ++c) {
-      const int col = min(lane + 32 * c, ncol - 1);
-      int ix; float tx;
-      source_index(ox0 + col, w, T, &ix, &tx);
-      tap_weights(tx, bil, wt[c]);
-#pragma unroll
-      for (int q = 0; q < 4; ++q) xi[c][q] = min(max(min(max(ix - 1 + q, 0), w - 1) - xs_lo, 0), nsx - 1);
-    }
-    for (int y = warp; y < h; y += kViewThreads / 32) {      // a warp owns the row: read every tap, then overwrite
-      float* row = s_src + y * a.src_w;
-      float acc[NC];
-#pragma unroll
-      for (int c = 0; c < NC; ++c) {
-        acc[c] = row[xi[c][0]] * wt[c][0];
-        acc[c] = fmaf(row[xi[c][1]], wt[c][1], acc[c]);
-        acc[c] = fmaf(row[xi[c][2]], wt[c][2], acc[c]);
-        acc[c] = fmaf(row[xi[c][3]], wt[c][3], acc[c]);
-      }
-      __syncwarp();
-#pragma unroll
-      for (int c = 0; c < NC; ++c)
-        if (lane + 32 * c < ncol) row[lane + 32 * c] = acc[c];
-    }
-  }
-  __syncthreads();
-
-  // ---- stage C: along frequency, coalesced stores.  lanes <-> columns, warps <-> output rows
-  {
-    float* outp = (v == 0 ? a.view1 : a.view2) + b * (static_cast<long long>(F) * T) + ox0 + lane;
-    for (int oy = warp; oy < F; oy += kViewThreads / 32) {
-      const float4 wy = s_wy[oy];
-      const int4 ya = s_ya[oy];
-      const float* r0 = s_src + ya.x * a.src_w + lane;
-      const float* r1 = s_src + ya.y * a.src_w + lane;
-      const float* r2 = s_src + ya.z * a.src_w + lane;
-      const float* r3 = s_src + ya.w * a.src_w + lane;
-      float* orow = outp + static_cast<long long>(oy) * T;
-#pragma unroll
-      for (int c = 0; c < NC; ++c) {
-        if (lane + 32 * c < ncol) {
-          float acc = r0[32 * c] * wy.x;
-          acc = fmaf(r1[32 * c], wy.y, acc);
-          acc = fmaf(r2[32 * c], wy.z, acc);
-          acc = fmaf(r3[32 * c], wy.w, acc);
-          orow[32 * c] = acc;
-        }
-      }
-    }
-  }
+  float* outp = (v == 0 ? a.view1 : a.view2) + b * (static_cast<long long>(F) * T) + ox0;
+  const int n_left = ncol - 32 * (NC - 1);
+  if (NC > 1 && n_left >= 1 && n_left <= kLeftMax && (a.c.canvas_h + 7) / 8 <= 2 * (32 / n_left))
+    resample_tile<(NC > 1 ? NC - 1 : 1), true>(a, s_src, s_wy, s_ya, outp, h, w, ncol, ox0, xs_lo, nsx, bil, lane, warp);
+  else
+    resample_tile<NC, false>(a, s_src, s_wy, s_ya, outp, h, w, ncol, ox0, xs_lo, nsx, bil, lane, warp);
 }
 
 template <int TW, int CG, bool GB>
