@@ -84,3 +84,26 @@ def test_extract_window_and_l2():
     assert np.array_equal(w, y[7:47])
     z = frontend.l2_normalize(y)
     np.testing.assert_allclose(np.linalg.norm(z), 1.0, rtol=1e-6)
+
+
+def test_against_transformers_audio_utils():
+    """Second independent cross-check (librosa itself is not installable here): transformers.audio_utils is a numpy
+    implementation written to reproduce librosa's filterbank and STFT (Slaney scale + area norm, centred reflect
+    padding, periodic Hann, fp64 FFT).  Filterbank to 1e-8, log-mel of a noise clip and of a chirp to 2e-6."""
+    au = pytest.importorskip("transformers.audio_utils")
+    fb = au.mel_filter_bank(num_frequency_bins=513, num_mel_filters=64, min_frequency=60, max_frequency=7800,
+                            sampling_rate=16000, norm="slaney", mel_scale="slaney")
+    assert np.abs(fb.T - frontend.mel_filterbank()).max() < 1e-8
+    win = au.window_function(1024, "hann", periodic=True)
+    assert np.abs(win - frontend.hann_periodic(1024)).max() < 1e-15
+    rng = np.random.default_rng(7)
+    t = np.arange(15200) / 16000.0
+    clips = [(rng.standard_normal(16000) * 0.1).astype(np.float32),
+             (0.5 * np.sin(2 * np.pi * (50.0 + 4000.0 * t) * t) + 1e-3 * rng.standard_normal(15200)).astype(np.float32)]
+    for y in clips:
+        power = au.spectrogram(y.astype(np.float64), win, frame_length=1024, hop_length=160, fft_length=1024, power=2.0,
+                               center=True, pad_mode="reflect", onesided=True, mel_filters=fb, mel_floor=1e-30)
+        theirs = np.log(power + 1.1920928955078125e-07)
+        ours = frontend.log_mel(y)
+        assert ours.shape == theirs.shape == (64, frontend.num_frames(len(y)))
+        assert np.abs(ours - theirs).max() < 2e-6
