@@ -113,9 +113,24 @@ __device__ __forceinline__ ulonglong2 lds128(unsigned addr) {
   asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(addr) : "memory");
   return v;
 }
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, void* bar) {
+// The waveform is read once (its 6.4x frame overlap is served while the neighbouring warps work on it): evict-first
+// in L2, so that it does not push the log-mel ring out (the two-view kernel reads its bank entries from there).
+#ifndef ASSL_WAVE_EVICT_FIRST
+#define ASSL_WAVE_EVICT_FIRST 1
+#endif
+__device__ __forceinline__ unsigned long long l2_evict_first_policy() {
+  unsigned long long pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, void* bar, unsigned long long pol) {
+#if ASSL_WAVE_EVICT_FIRST
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+#else
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+#endif
 }
 
 // Frame pair p of the flattened list: clip, pair inside the clip, and the part of its span [base, base + span)
@@ -161,11 +176,12 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   const int span = kNfft + a.hop;                    // samples the two frames of a pair touch
   const int stride = static_cast<int>(gridDim.x) * n_warps;
   // producer side of the warp's pipeline (lane 0): bulk-copy the in-range part of a pair's span
+  const unsigned long long wave_policy = l2_evict_first_policy();
   auto issue = [&](int p) {
     const PairSpan s = pair_span(a, p, span);
     const unsigned bytes = static_cast<unsigned>(s.hi - s.lo) * 4u;
     mbar_expect_tx(bar, bytes);
-    if (bytes) bulk_g2s(buf + s.lo, a.wave + s.clip * a.ld + s.base + s.lo, bytes, bar);
+    if (bytes) bulk_g2s(buf + s.lo, a.wave + s.clip * a.ld + s.base + s.lo, bytes, bar, wave_policy);
   };
   // warp-major numbering: consecutive pairs go to different SMs, so the last, partial round (52224 pairs over 2368
   // warps = 22.05 rounds) is one uncontended warp on each of 128 SMs instead of 16 contending warps on 8 of them

@@ -54,6 +54,19 @@ __device__ __forceinline__ float lg2_approx(float x) {    // MUFU.LG2 without th
   return y;
 }
 
+// The views are written once and read by another kernel much later: streaming stores (evict-first in L2) keep them
+// from pushing the log-mel ring -- the bank entries the next steps read -- out of the 126 MB L2.
+#ifndef ASSL_VIEWS_STREAM_STORES
+#define ASSL_VIEWS_STREAM_STORES 1
+#endif
+__device__ __forceinline__ void store_view(float* p, float v) {
+#if ASSL_VIEWS_STREAM_STORES
+  __stcs(p, v);
+#else
+  *p = v;
+#endif
+}
+
 __device__ __forceinline__ float cubic1(float x) {   // |x| <= 1
   const float A = -0.75f;
   return ((A + 2.f) * x - (A + 3.f)) * x * x + 1.f;
@@ -286,7 +299,7 @@ __device__ __forceinline__ void resample_tile(const ViewArgs& a, float* s_src, c
           acc = fmaf(r1[32 * c], wy.y, acc);
           acc = fmaf(r2[32 * c], wy.z, acc);
           acc = fmaf(r3[32 * c], wy.w, acc);
-          orow[32 * c] = acc;
+          store_view(orow + 32 * c, acc);
         }
       }
     }
@@ -301,7 +314,7 @@ __device__ __forceinline__ void resample_tile(const ViewArgs& a, float* s_src, c
           acc = fmaf(s_src[ya.y * a.src_w + col], wy.y, acc);
           acc = fmaf(s_src[ya.z * a.src_w + col], wy.z, acc);
           acc = fmaf(s_src[ya.w * a.src_w + col], wy.w, acc);
-          outp[static_cast<long long>(oy) * T + col] = acc;
+          store_view(outp + static_cast<long long>(oy) * T + col, acc);
         }
       }
     }
