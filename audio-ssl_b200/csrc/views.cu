@@ -142,7 +142,7 @@ __device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, l
   asm volatile("" : "+l"(zp));
   // Rows are taken kRowBatch at a time per warp and ALL their global loads are issued before any
   // arithmetic, so a warp keeps 2 * kRowBatch * G loads in flight instead of 2.
-  constexpr int kRowBatch = 2;
+  constexpr int kRowBatch = 2;                               // (3 or 4 rows for the narrow instances: no gain measured)
   for (int yb = warp * kRowBatch; yb < h; yb += (kViewThreads / 32) * kRowBatch) {
     float xv[kRowBatch][kColGroups], zv[kRowBatch][kColGroups];
 #pragma unroll

@@ -34,11 +34,17 @@ def _dist_world():
     return 0, 1
 
 
-def heavy_first(crop):
+def heavy_first(crop, n_time=None, canvas_w=None):
     """Launch order of the views of a batch for ``assl_two_views_ordered_f32``: [2B] int32, view ids (2*clip + view)
-    sorted by decreasing cost.  A view stages h crop rows in ceil((w + 4) / 32) groups of 32 columns."""
+    sorted by decreasing cost.  A view mixes h crop rows over the columns of its crop that lie inside the pasted clip
+    (``n_time`` columns centred in a canvas of ``canvas_w``), in groups of 32, and resamples the h rows along time;
+    without the canvas geometry the whole crop width counts."""
     c = np.asarray(crop, np.int64).reshape(-1, 4)
-    cost = c[:, 2] * (20 * ((c[:, 3] + 4 + 31) // 32) + 45)
+    width = c[:, 3]
+    if n_time is not None and canvas_w is not None:
+        x0 = (int(canvas_w) - int(n_time)) // 2
+        width = np.clip(np.minimum(c[:, 1] + c[:, 3], x0 + int(n_time)) - np.maximum(c[:, 1], x0), 0, None)
+    cost = c[:, 2] * (15 * ((width + 31) // 32) + 55)
     return np.argsort(-cost, kind="stable").astype(np.int32)
 
 
@@ -252,7 +258,7 @@ class ViewEngine:
         d_clip = torch.from_numpy(clip_slot).to(device, non_blocking=True)
         d_alpha = torch.from_numpy(np.ascontiguousarray(params.alpha, np.float32)).to(device, non_blocking=True)
         d_crop = torch.from_numpy(np.ascontiguousarray(params.crop, np.int32)).to(device, non_blocking=True)
-        d_order = torch.from_numpy(heavy_first(params.crop)).to(device, non_blocking=True)
+        d_order = torch.from_numpy(heavy_first(params.crop, self.t, cw)).to(device, non_blocking=True)
         v1 = torch.empty((batch, 1, self.f, self.t), dtype=torch.float32, device=device)
         v2 = torch.empty_like(v1)
         vcfg = _native.ViewCfg(self.f, self.t, ch, cw, INTERP[self.interp], 1 if self.log_mixup else 0)
@@ -293,7 +299,7 @@ class ViewEngine:
         w = self.world
         d_alpha = to_dev(np.ascontiguousarray(params.alpha, np.float32))
         d_crop = to_dev(np.ascontiguousarray(params.crop, np.int32))
-        d_order = to_dev(heavy_first(params.crop))
+        d_order = to_dev(heavy_first(params.crop, self.t, cw))
         v1 = torch.empty((batch, 1, self.f, self.t), dtype=torch.float32, device=device)
         v2 = torch.empty_like(v1)
         vcfg = _native.ViewCfg(self.f, self.t, ch, cw, INTERP[self.interp], 1 if self.log_mixup else 0)

@@ -210,14 +210,14 @@ def run_ours(args):
         mix = np.where(p.src_clip >= 0, p.src_clip % cap, -1).astype(np.int32)
         clip = ((clips_done + np.arange(B, dtype=np.int64)) % cap).astype(np.int32)
         return [torch.from_numpy(a).to(dev) for a in (clip, mix, np.ascontiguousarray(p.alpha), np.ascontiguousarray(p.crop),
-                                                      heavy_first(p.crop))]
+                                                      heavy_first(p.crop, T, int(T * 1.5)))]
 
     def upload_global(step):
         """Global bank: every rank draws the global batch from the same generator and keeps its slice (global clip ids)."""
         p = tf.sampler.draw(step * B * world, B * world, N_MELS, T)
         lo, hi = rank * B, (rank + 1) * B
         idx = eng.global_indices(np.asarray(p.src_clip[lo:hi], np.int64), step)
-        arrs = list(idx) + [np.ascontiguousarray(p.alpha[lo:hi]), np.ascontiguousarray(p.crop[lo:hi]), heavy_first(p.crop[lo:hi])]
+        arrs = list(idx) + [np.ascontiguousarray(p.alpha[lo:hi]), np.ascontiguousarray(p.crop[lo:hi]), heavy_first(p.crop[lo:hi], T, int(T * 1.5))]
         return [torch.from_numpy(a).to(dev) for a in arrs]
 
     # steps [0, W) warm up, [W, W+K) are the timed region (no event between the kernels: an event record would

@@ -143,4 +143,8 @@ def test_global_bank_index_mapping():
                     assert (g // (world * b)) * b + g % b + cap > step * b + b - 1
     from audiossl_b200.engine import heavy_first
     crop = np.array([[[0, 0, 40, 60], [0, 0, 64, 151]], [[0, 0, 64, 100], [0, 0, 38, 61]]], np.int32)
-    assert heavy_first(crop).tolist() == [1, 2, 3, 0]      # rows x 32-column groups: 64x5, 64x4, 38x3, 40x2
+    assert heavy_first(crop).tolist() == [1, 2, 0, 3]      # rows x 32-column groups: 64x5, 64x4, 40x2, 38x2
+    # with the canvas geometry only the columns inside the pasted clip (canvas columns 25..125) count: 101, 75, 35, 36
+    assert heavy_first(crop, 101, 151).tolist() == [1, 2, 0, 3]
+    assert heavy_first(np.array([[[0, 0, 64, 60], [0, 40, 64, 60]]], np.int32), 101, 151).tolist() == [0, 1]
+    assert heavy_first(np.array([[[0, 0, 64, 50], [0, 40, 64, 50]]], np.int32), 101, 151).tolist() == [1, 0]
