@@ -1,0 +1,79 @@
+"""Programmatic dependent launch (csrc/common.cuh): the kernels of the path may be scheduled before the previous
+kernel on the stream has finished; they must still see everything it wrote.  Producers here are FOREIGN kernels
+(torch element-wise ops) on a side stream with no synchronisation before the call, and the whole pipeline is compared
+bit for bit with ASSL_PDL=0 (ordinary launches) in a second process."""
+import os
+import subprocess
+import sys
+import zlib
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+CFG = {"pretrain": {"normalization": "mean_var", "augmentations": {
+    "MixupBYOLA": {"ratio": 0.4, "log_mixup_exp": True},
+    "RandomResizeCrop": {"virtual_crop_scale": [1.0, 1.5], "freq_crop_scale": [0.6, 1.5],
+                         "time_crop_scale": [0.6, 1.5]}}}}
+
+
+def test_inputs_written_by_foreign_kernels_right_before_the_call():
+    import audiossl_b200 as A
+    mel = A.MelSpectrogramLibrosa()
+    g = torch.Generator(device="cpu").manual_seed(5)
+    base = (torch.randn(256, 16000, generator=g) * 0.1).cuda()
+    scales = [0.25 + 0.05 * i for i in range(12)]
+    want = []
+    for s in scales:                                   # reference results: one step at a time, synchronised
+        w = base * s
+        torch.cuda.synchronize()
+        want.append(A.extract_log_mel_spectrogram(w, mel).clone())
+        torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    got = []
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        buf = torch.empty_like(base)
+        for s in scales:                               # producer kernel -> log-mel kernel, back to back, one buffer
+            torch.mul(base, s, out=buf)
+            got.append(A.extract_log_mel_spectrogram(buf, mel).clone())
+    side.synchronize()
+    for a, b in zip(got, want):
+        assert torch.equal(a, b)
+
+
+_SCRIPT = r"""
+import random, sys, zlib
+import numpy as np, torch
+sys.path.insert(0, {root!r})
+import audiossl_b200 as A
+cfg = {cfg!r}
+g = torch.Generator(device="cpu").manual_seed(11)
+waves = (torch.randn(6, 96, 15200, generator=g) * 0.1).cuda()
+np.random.seed(31); random.seed(31)
+pipe = A.UpstreamInputPipeline(cfg, 10 ** 6)
+crc = 0
+for k in range(6):                                     # six steps streamed without a sync: every kernel follows a kernel
+    v1, v2 = pipe(waves[k])
+    keep = (v1, v2) if k == 0 else keep + (v1, v2)
+torch.cuda.synchronize()
+for v in keep:
+    crc = zlib.crc32(v.cpu().numpy().tobytes(), crc)
+print("CRC", crc)
+"""
+
+
+def _run(pdl):
+    env = dict(os.environ, ASSL_PDL=pdl)
+    res = subprocess.run([sys.executable, "-c", _SCRIPT.format(root=ROOT, cfg=CFG)], env=env, capture_output=True,
+                         text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    return [l for l in res.stdout.splitlines() if l.startswith("CRC")][-1]
+
+
+def test_pipeline_is_bit_identical_with_and_without_pdl():
+    assert _run("1") == _run("0")
