@@ -81,6 +81,7 @@ SIGNATURES = {
                                              _P, _P, _P]),
     "assl_two_views_f32": (C.c_int, [C.POINTER(ViewCfg), _P, _P, _I64, _P, _P, _P, _P, _I64, _P, _P, _P]),
     "assl_two_views_ordered_f32": (C.c_int, [C.POINTER(ViewCfg), _P, _P, _I64, _P, _P, _P, _P, _P, _I64, _P, _P, _P]),
+    "assl_two_views_deferred_f32": (C.c_int, [C.POINTER(ViewCfg), _P, _P, _I64, _P, _P, _P, _P, _P, _I64, _P, _P, _P]),
     "assl_clip_clusters_f32": (C.c_int, [_P, _I64, C.c_int32, C.c_int32, _P, C.c_int32, _P, _P, _P]),
     "assl_batch_sums": (C.c_int, [_P, _I64, _P, _P]),
     "assl_normalize_apply_f32": (C.c_int, [_P, _P, _I64, _P, _P]),

@@ -189,7 +189,6 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   // Launched behind another kernel of the path (PDL) this CTA gets its SM while that grid's last wave drains and
   // loads the plan's tables (immutable, never written by a kernel) meanwhile; the waveform, the ring and the sums
   // are touched only after pdl_wait() below.
-  pdl_launch_dependents();
 
   // Inter-stage twiddles w^k2 (w = W_1024^lane): only w^8, w^16, w^24 and w^1..w^7 are kept per lane; the
   // other 21 are applied as two rotations, (z * w^b) * w^(8a), trading 42 FFMA2/FMUL2 per transform for two
@@ -211,6 +210,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   // (s_ex needs no clearing: every power bin a part reads is either written by this pair or selected away,
   //  never multiplied, and every interval total is started before it is read)
   pdl_wait();
+  // (after the wait, so that a kernel launched behind this one knows every older grid has completed: that is what lets
+  //  a deferred two-view launch, assl_two_views_deferred_f32, start without waiting for this grid)
+  pdl_launch_dependents();
   // the first copy flies while the other warps finish the tables (only this warp's lane 0 touches its barrier and buffer)
   if (a.bulk_ok && lane == 0 && first < a.total_pairs) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");

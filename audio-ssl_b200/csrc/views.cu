@@ -40,6 +40,7 @@ struct ViewArgs {
   int tiles_t;     // output-time tiles per view
   int src_w;       // staged source columns per tile (row stride of the source tile)
   int y0, x0;      // where the clip sits in the canvas (augmentations.py:47)
+  int deferred;    // assl_two_views_deferred_f32: may overlap the grid launched before it (waits for it at the END)
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {    // MUFU.EX2, flush-to-zero (|rel err| <= 2 ulp)
@@ -335,7 +336,7 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
   long long blk = blockIdx.x;
   const int tile = static_cast<int>(blk % a.tiles_t); blk /= a.tiles_t;
   pdl_launch_dependents();                     // the next kernel may take SMs as this grid's last wave drains
-  pdl_wait();                                  // nothing global is read before the previous grid has completed
+  if (!a.deferred) pdl_wait();                 // nothing global is read before the previous grid has completed
   if (a.order) blk = a.order[blk];             // CTAs start in launch order: the host puts the big crops first
   const int v = static_cast<int>(blk & 1);
   const long long b = blk >> 1;
@@ -400,6 +401,9 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
     resample_tile<(NC > 1 ? NC - 1 : 1), true>(a, s_src, s_wy, s_ya, outp, h, w, ncol, ox0, xs_lo, nsx, bil, lane, warp);
   else
     resample_tile<NC, false>(a, s_src, s_wy, s_ya, outp, h, w, ncol, ox0, xs_lo, nsx, bil, lane, warp);
+  // deferred launch: this grid ran beside the one launched before it; whoever waits for THIS grid to complete
+  // (the next kernel's pdl_wait) must also get that one's completion
+  if (a.deferred) pdl_wait();
 }
 
 template <int TW, int CG, bool GB>
@@ -449,11 +453,11 @@ extern "C" int assl_two_views_ordered_f32(const assl_view_cfg* vc, const float* 
                                    order, B, view1, view2, stream);
 }
 
-extern "C" int assl_two_views_global_f32(const assl_view_cfg* vc, const float* lms, const float* const* peer_lms,
-                                         int32_t world, const float* mean_std, const int32_t* clip_slot,
-                                         const int32_t* clip_stat, const int32_t* mix_slot, const int32_t* mix_rank,
-                                         const int32_t* mix_stat, const float* alpha, const int32_t* crop,
-                                         const int32_t* order, int64_t B, float* view1, float* view2, void* stream) {
+static int two_views_impl(const assl_view_cfg* vc, const float* lms, const float* const* peer_lms,
+                          int32_t world, const float* mean_std, const int32_t* clip_slot,
+                          const int32_t* clip_stat, const int32_t* mix_slot, const int32_t* mix_rank,
+                          const int32_t* mix_stat, const float* alpha, const int32_t* crop,
+                          const int32_t* order, int64_t B, float* view1, float* view2, int deferred, void* stream) {
   using namespace assl;
   const int64_t cap = 0;
   if (!vc || !lms || !clip_slot || !mix_slot || !alpha || !crop || !view1 || !view2 || B < 0) return ASSL_ERR_INVALID_ARG;
@@ -468,6 +472,7 @@ extern "C" int assl_two_views_global_f32(const assl_view_cfg* vc, const float* l
   a.mix_rank = world > 0 ? mix_rank : nullptr; a.clip_stat = clip_stat; a.mix_stat = mix_stat;
   for (int r = 0; r < ASSL_EXCHANGE_MAX_WORLD; ++r) a.peer_lms[r] = r < world ? peer_lms[r] : nullptr;
   a.view1 = view1; a.view2 = view2;
+  a.deferred = deferred;
   a.y0 = (vc->canvas_h - vc->n_freq) / 2;
   a.x0 = (vc->canvas_w - vc->n_time) / 2;
   // widest crop span a TW-column tile can touch: (TW-1) * max scale + 4 taps, never more than the canvas
@@ -484,4 +489,22 @@ extern "C" int assl_two_views_global_f32(const assl_view_cfg* vc, const float* l
   if (rc == ASSL_ERR_UNSUPPORTED && T > 32) { a.src_w = span(64); rc = launch_views<64>(a, as_stream(stream)); }
   if (rc == ASSL_ERR_UNSUPPORTED) { a.src_w = span(32); rc = launch_views<32>(a, as_stream(stream)); }
   return rc;
+}
+
+extern "C" int assl_two_views_global_f32(const assl_view_cfg* vc, const float* lms, const float* const* peer_lms,
+                                         int32_t world, const float* mean_std, const int32_t* clip_slot,
+                                         const int32_t* clip_stat, const int32_t* mix_slot, const int32_t* mix_rank,
+                                         const int32_t* mix_stat, const float* alpha, const int32_t* crop,
+                                         const int32_t* order, int64_t B, float* view1, float* view2, void* stream) {
+  return two_views_impl(vc, lms, peer_lms, world, mean_std, clip_slot, clip_stat, mix_slot, mix_rank, mix_stat, alpha, crop,
+                        order, B, view1, view2, 0, stream);
+}
+
+extern "C" int assl_two_views_deferred_f32(const assl_view_cfg* vc, const float* lms, const float* mean_std, int64_t cap,
+                                           const int32_t* clip_slot, const int32_t* mix_slot, const float* alpha,
+                                           const int32_t* crop, const int32_t* order, int64_t B, float* view1,
+                                           float* view2, void* stream) {
+  (void)cap;
+  return two_views_impl(vc, lms, nullptr, 0, mean_std, clip_slot, nullptr, mix_slot, nullptr, nullptr, alpha, crop, order, B,
+                        view1, view2, 1, stream);
 }

@@ -190,8 +190,10 @@ def run_ours(args):
     plan = A.Plan()
     T, tiles = plan.num_frames(L), plan.num_tiles(L)
     gbank = bool(args.global_bank) and world > 1
-    tf = A.AugmentationModule(CFG, len_of_files=10 ** 7, sampler="fast", max_batch=B, seed=1234 + (0 if gbank else rank),
-                              global_bank=gbank)
+    look = bool(args.lookahead) and not gbank
+    # (lookahead: the ring holds one more batch -- the log-mel kernel of batch k+1 writes while the views of batch k read)
+    tf = A.AugmentationModule(CFG, len_of_files=10 ** 7, sampler="fast", max_batch=2 * B if look else B,
+                              seed=1234 + (0 if gbank else rank), global_bank=gbank)
     eng = tf.engine
     eng.ensure(N_MELS, T, dev)
     cap = eng.cap
@@ -255,7 +257,12 @@ def run_ours(args):
             _native.check(lib.assl_running_stats(P(eng.state), P(sums), B, tiles, N_MELS * T, max_update, 0, B,
                                                  P(eng.stats), slot0, cap, stream()))
         e[2].record()
-        if gbank:
+        if look:                                     # views of the PREVIOUS batch, beside this batch's statistics
+            if s > 0:
+                clip, mix, alpha, crop, order = steps_params[s - 1]
+                _native.check(lib.assl_two_views_deferred_f32(C.byref(vcfg), P(eng.ring), P(eng.stats), cap, P(clip), P(mix),
+                                                              P(alpha), P(crop), P(order), B, P(v1), P(v2), stream()))
+        elif gbank:
             clip, cstat, mix, mrank, mstat, alpha, crop, order = steps_params[s]
             _native.check(lib.assl_two_views_global_f32(C.byref(vcfg), P(eng.ring), eng.peer_ring.ptrs, world, P(eng.stats),
                                                         P(clip), P(cstat), P(mix), P(mrank), P(mstat), P(alpha), P(crop),
@@ -396,6 +403,8 @@ def main():
     ap.add_argument("--rotate", type=int, default=4, help="distinct input batches cycled through (L2 hygiene)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="wall seconds of one CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--lookahead", type=int, default=0,
+                    help="1: software-pipelined step order log-mel(k), statistics(k), views(k-1)")
     ap.add_argument("--global-bank", action="store_true",
                     help="N > 1 only, not the headline configuration: mixup FIFO over the global clip order, bank entries read "
                          "from the peers' rings over NVLink (SURVEY 8e, optional mode)")

@@ -231,6 +231,21 @@ int assl_two_views_ordered_f32(const assl_view_cfg* cfg, const float* lms, const
                                const float* alpha, const int32_t* crop, const int32_t* order, int64_t B,
                                float* view1, float* view2, void* stream);
 
+/* The same as assl_two_views_ordered_f32 for a software-pipelined step order: log-mel(k) . statistics(k) . views(k-1).
+ * The launch does NOT wait for the kernel launched before it on the stream (it may run beside it, filling the SMs the
+ * log-mel kernel's tail leaves idle while the statistics kernel of the next batch runs); it waits for that kernel at
+ * its END, so whatever is launched next still sees stream order.  The caller guarantees (a) that the kernel launched
+ * immediately before neither writes anything this call reads (ring slots of this batch and of its bank entries, their
+ * mean/std pairs, the parameter arrays) nor touches view1/view2 -- with the ring that means cap >= bank clips + 2 B --
+ * and (b) that everything this call reads was produced by kernels launched BEFORE the last assl_logmel_f32 on this
+ * stream (that kernel releases its dependents only after everything older has completed).  Same results as
+ * assl_two_views_ordered_f32; replaces nothing in the reference (its DataLoader overlaps batches across workers,
+ * src/dataset/upstream_dataset.py:118-125).                                                                        */
+int assl_two_views_deferred_f32(const assl_view_cfg* cfg, const float* lms, const float* mean_std,
+                               int64_t cap, const int32_t* clip_slot, const int32_t* mix_slot,
+                               const float* alpha, const int32_t* crop, const int32_t* order, int64_t B,
+                               float* view1, float* view2, void* stream);
+
 /* -- Kmix cluster features ------------------------------------------------------------------
  * The data-dependent half of Kmix.get_index (src/augmentations/augmentations.py:142-165): per clip, the
  * per-band mean over time is assigned to the nearest of K centroids, once L2-normalised
