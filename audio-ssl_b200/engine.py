@@ -149,7 +149,7 @@ class PeerRing:
 class ViewEngine:
     def __init__(self, n_memory=2048, pushes_per_clip=2, ratio=0.4, log_mixup=True,
                  virtual_crop_scale=(1.0, 1.5), interp="bicubic", normalize=True, max_update=None,
-                 max_batch=4096, sync_stats=True, global_bank=False):
+                 max_batch=4096, sync_stats=True, global_bank=False, lookahead=False):
         if interp not in INTERP:
             raise ValueError(f"interp must be one of {sorted(INTERP)}")
         self.n_memory, self.nv = int(n_memory), int(pushes_per_clip)
@@ -159,12 +159,18 @@ class ViewEngine:
             raise ValueError("RunningNorm needs max_update >= 1 (epoch_samples * max_update_epochs)")
         self.max_batch, self.sync_stats = int(max_batch), sync_stats
         self.history = -(-self.n_memory // self.nv)          # distinct clips the FIFO can still hold
-        self.cap = self.history + self.max_batch
+        # lookahead (UpstreamInputPipeline(lookahead=True)): the front end of batch k+1 runs before the views of batch k,
+        # so the ring holds one more batch and the write head runs ``ahead`` clips in front of ``clips_done``
+        self.lookahead = bool(lookahead)
+        self.ahead = 0
+        self.cap = self.history + (2 if self.lookahead else 1) * self.max_batch
         # global bank (optional): the FIFO runs over the GLOBAL clip order; bank entries are read from the
         # peers' rings over NVLink.  Every step must bring exactly max_batch clips per rank.  The ring is
         # steps_back + 2 steps deep: a step's clips can be picked for steps_back more steps, and a rank is never
         # more than one statistics exchange ahead of the slowest reader.
         self.global_bank = bool(global_bank) and _dist_world()[1] > 1
+        if self.global_bank and self.lookahead:
+            raise ValueError("lookahead is not available with global_bank")
         if self.global_bank:
             if not (normalize and sync_stats):
                 raise ValueError("global_bank needs the synchronised running statistics (normalize and sync_stats)")
@@ -196,8 +202,13 @@ class ViewEngine:
             raise ValueError(f"clip shape changed from {(self.f, self.t)} to {(f, t)}: the mixup bank holds one shape")
 
     @property
+    def head(self):
+        """Global index of the next clip the front end writes."""
+        return self.clips_done + self.ahead
+
+    @property
     def slot0(self):
-        return self.clips_done % self.cap
+        return self.head % self.cap
 
     def ring_put(self, x):
         """Copy a [B, F, T] batch into the ring at the current head (at most two slice copies)."""
@@ -244,28 +255,41 @@ class ViewEngine:
     # ------------------------------------------------------------------ views
     def launch_views(self, params: ViewParams, batch: int, device):
         """Two views of the ``batch`` clips at the ring head, then advance the head."""
+        if self.global_bank:
+            ch, cw = canvas_size(self.f, self.t, self.vscale)
+            validate_crops(params.crop, ch, cw)
+            return self._launch_views_global(params, batch, device, ch, cw)
+        return self.launch_prepared(self.prepare_views(params, batch, device, self.clips_done))
+
+    def prepare_views(self, params: ViewParams, batch: int, device, g0: int):
+        """Validate and upload the parameters of the ``batch`` clips whose first global index is ``g0``."""
         ch, cw = canvas_size(self.f, self.t, self.vscale)
         validate_crops(params.crop, ch, cw)
-        if self.global_bank:
-            return self._launch_views_global(params, batch, device, ch, cw)
-        g0 = self.clips_done
         src = params.src_clip
         if np.any(src >= g0 + batch) or np.any((src >= 0) & (src < g0 + batch - self.cap)):
             raise ValueError("mixup source outside the bank ring")
         mix_slot = np.where(src >= 0, src % self.cap, -1).astype(np.int32)
         clip_slot = ((g0 + np.arange(batch, dtype=np.int64)) % self.cap).astype(np.int32)
-        d_mix = torch.from_numpy(mix_slot).to(device, non_blocking=True)
-        d_clip = torch.from_numpy(clip_slot).to(device, non_blocking=True)
-        d_alpha = torch.from_numpy(np.ascontiguousarray(params.alpha, np.float32)).to(device, non_blocking=True)
-        d_crop = torch.from_numpy(np.ascontiguousarray(params.crop, np.int32)).to(device, non_blocking=True)
-        d_order = torch.from_numpy(heavy_first(params.crop, self.t, cw)).to(device, non_blocking=True)
+        to_dev = lambda a: torch.from_numpy(a).to(device, non_blocking=True)   # noqa: E731
+        return dict(batch=batch, device=device, g0=g0, ch=ch, cw=cw, clip=to_dev(clip_slot), mix=to_dev(mix_slot),
+                    alpha=to_dev(np.ascontiguousarray(params.alpha, np.float32)),
+                    crop=to_dev(np.ascontiguousarray(params.crop, np.int32)),
+                    order=to_dev(heavy_first(params.crop, self.t, cw)))
+
+    def launch_prepared(self, prep, deferred=False):
+        """Launch the two-view kernel for a prepared batch (the oldest one not yet turned into views).  ``deferred``:
+        the launch may run beside the kernel launched before it (assl_two_views_deferred_f32, include/assl.h)."""
+        if prep["g0"] != self.clips_done:
+            raise RuntimeError("views must be launched in clip order")
+        batch, device = prep["batch"], prep["device"]
         v1 = torch.empty((batch, 1, self.f, self.t), dtype=torch.float32, device=device)
         v2 = torch.empty_like(v1)
-        vcfg = _native.ViewCfg(self.f, self.t, ch, cw, INTERP[self.interp], 1 if self.log_mixup else 0)
-        _native.check(_native.lib().assl_two_views_ordered_f32(
+        vcfg = _native.ViewCfg(self.f, self.t, prep["ch"], prep["cw"], INTERP[self.interp], 1 if self.log_mixup else 0)
+        name = "assl_two_views_deferred_f32" if deferred else "assl_two_views_ordered_f32"
+        _native.check(getattr(_native.lib(), name)(
             C.byref(vcfg), _ptr(self.ring), _ptr(self.stats if self.normalize else None), self.cap,
-            _ptr(d_clip), _ptr(d_mix), _ptr(d_alpha), _ptr(d_crop), _ptr(d_order), batch, _ptr(v1), _ptr(v2),
-            _stream_ptr()), "assl_two_views_ordered_f32")
+            _ptr(prep["clip"]), _ptr(prep["mix"]), _ptr(prep["alpha"]), _ptr(prep["crop"]), _ptr(prep["order"]), batch,
+            _ptr(v1), _ptr(v2), _stream_ptr()), name)
         self.clips_done += batch
         return v1, v2
 
@@ -312,6 +336,8 @@ class ViewEngine:
 
     # ------------------------------------------------------------------ checkpointing (the reference saves none of this)
     def state_dict(self):
+        if self.ahead:
+            raise RuntimeError("a batch is still waiting for its views: call flush() before state_dict()")
         return {"clips_done": self.clips_done, "cap": self.cap,
                 "ring": None if self.ring is None else self.ring.cpu(),
                 "stats": None if self.stats is None else self.stats.cpu(),

@@ -35,7 +35,7 @@ class AugmentationModule:
     """
 
     def __init__(self, config, len_of_files, *, interpolation="bicubic", sampler="reference",
-                 max_batch=4096, seed=0, sync_stats=True, global_bank=False):
+                 max_batch=4096, seed=0, sync_stats=True, global_bank=False, lookahead=False):
         pre = config["pretrain"]
         aug = pre["augmentations"]
         self.kmix = None
@@ -62,7 +62,7 @@ class AugmentationModule:
         self.engine = ViewEngine(n_memory=2048 if mix else 0, pushes_per_clip=2, ratio=ratio, log_mixup=log_mixup,
                                  virtual_crop_scale=vscale, interp=interpolation, normalize=self.pre_norm,
                                  max_update=max_update, max_batch=max_batch, sync_stats=sync_stats,
-                                 global_bank=global_bank and mix is not None)
+                                 global_bank=global_bank and mix is not None, lookahead=lookahead)
         kw = dict(ratio=ratio, n_memory=2048, freq_scale=fscale, time_scale=tscale, virtual_crop_scale=vscale,
                   pushes_per_clip=2, mixup=self.has_mix, crop=self.has_crop)
         if sampler == "reference":
@@ -101,8 +101,9 @@ class AugmentationModule:
         both = both.reshape(v1.shape[0], 2, *v1.shape[1:])
         return both[:, 0], both[:, 1]
 
-    def _params(self, params, lo, hi):
+    def _params(self, params, lo, hi, g0=None):
         eng = self.engine
+        g0 = eng.clips_done if g0 is None else g0
         if params is None and eng.global_bank:
             # the FIFO runs over the global clip order: every rank draws the parameters of the WHOLE global batch
             # from the same generator state (same seed on every rank) and keeps its slice; src_clip = global ids
@@ -111,7 +112,7 @@ class AugmentationModule:
             a, b = eng.rank * n, (eng.rank + 1) * n
             p = ViewParams(everyone.alpha[a:b], everyone.src_clip[a:b], everyone.bank_index[a:b], everyone.crop[a:b])
         elif params is None:
-            p = self.sampler.draw(self.engine.clips_done, hi - lo, self.engine.f, self.engine.t)
+            p = self.sampler.draw(g0, hi - lo, self.engine.f, self.engine.t)
         else:
             p = ViewParams(params.alpha[lo:hi], params.src_clip[lo:hi], params.bank_index[lo:hi], params.crop[lo:hi])
         self.last_params = p
@@ -146,8 +147,11 @@ class UpstreamInputPipeline:
         self.unit_length = int(unit_length) if unit_length is not None else \
             (int(length_wave * 16000) if length_wave else None)          # utils.py:168-169
         self.last_lms = None
+        self._pending = None                 # lookahead: the batch whose front end has run, waiting for its views
 
     def __call__(self, waveforms, params: ViewParams = None):
+        if self.tfms.engine.lookahead:
+            return self._call_lookahead(waveforms, params)
         if isinstance(waveforms, PackedClips):
             return self._ragged(waveforms, params)
         if isinstance(waveforms, (list, tuple)):
@@ -172,6 +176,60 @@ class UpstreamInputPipeline:
                 v1s.append(a); v2s.append(c)
         v1 = v1s[0] if len(v1s) == 1 else torch.cat(v1s)
         v2 = v2s[0] if len(v2s) == 1 else torch.cat(v2s)
+        return self.tfms._post(v1, v2)
+
+    # -- lookahead=True: software-pipelined step order  log-mel(k) . statistics(k) . views(k-1)
+    def _call_lookahead(self, waveforms, params):
+        """Run the front end and the statistics of THIS batch and return the two views of the PREVIOUS one (``None`` on
+        the first call; ``flush()`` returns the last batch's).  The views of batch k-1 are launched right behind the
+        statistics kernel of batch k with assl_two_views_deferred_f32: they fill the SMs the log-mel kernel's tail
+        leaves idle and run beside the statistics kernel (and, across GPUs, beside its exchange).  Same views as the
+        ordinary order, one call later; the draws happen in the same clip order."""
+        if isinstance(waveforms, (list, tuple, PackedClips)):
+            raise ValueError("lookahead takes equal-length windows [B, L]")
+        wave = as_cuda_f32(waveforms)
+        if wave.dim() == 1:
+            wave = wave.unsqueeze(0)
+        eng, tf = self.tfms.engine, self.tfms
+        from . import _native
+        from .frontend import _ptr, _stream_ptr
+        b = wave.shape[0]
+        if b > eng.max_batch:
+            raise ValueError(f"lookahead takes at most max_batch = {eng.max_batch} clips per call")
+        with torch.cuda.device(wave.device):
+            eng.ensure(self.plan.n_mels, self.plan.num_frames(wave.shape[1]), wave.device)
+            # parameters of this batch: drawn and uploaded before its kernels, used one call later
+            prep = eng.prepare_views(tf._params(params, 0, b, g0=eng.head), b, wave.device, eng.head)
+            gain = None
+            if self.l2:
+                gain = torch.empty(b, dtype=torch.float32, device=wave.device)
+                _native.check(_native.lib().assl_wave_l2_gain_f32(_ptr(wave), b, wave.shape[1], wave.stride(0), _ptr(gain),
+                                                                  _stream_ptr()))
+            tiles = self.plan.num_tiles(wave.shape[1])
+            sums = torch.empty((b, tiles, 2), dtype=torch.float64, device=wave.device) if tf.pre_norm else None
+            self.plan.logmel_into(wave, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain)
+            if tf.pre_norm:
+                eng.update_stats(sums, tiles)
+            eng.ahead += b
+            out = None
+            if self._pending is not None:
+                # (deferred only right behind the statistics kernel; without pre-norm the log-mel kernel of THIS batch
+                #  is the predecessor, which the deferred launch may overlap just the same)
+                v1, v2 = eng.launch_prepared(self._pending, deferred=True)
+                eng.ahead -= self._pending["batch"]
+                out = tf._post(v1, v2)
+            self._pending = prep
+        return out
+
+    def flush(self):
+        """Views of the last batch given to a ``lookahead`` pipeline (``None`` if nothing is pending)."""
+        if self._pending is None:
+            return None
+        eng = self.tfms.engine
+        with torch.cuda.device(self._pending["device"]):
+            v1, v2 = eng.launch_prepared(self._pending, deferred=False)
+        eng.ahead -= self._pending["batch"]
+        self._pending = None
         return self.tfms._post(v1, v2)
 
     def _windows_to_views(self, part, gain, draw):

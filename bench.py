@@ -364,6 +364,9 @@ def run_ours(args):
         "config": dict(workload_config(args, B), stats_exchange=("none (one GPU)" if world == 1 else
                                                                  "peer memory over NVLink, fused into the statistics kernel"
                                                                  if exchange is not None else "NCCL all-gather"),
+                    step_order=("log-mel(k), statistics(k), views(k-1): the views of the previous batch are launched "
+                                "deferred (assl_two_views_deferred_f32, UpstreamInputPipeline(lookahead=True)); every step "
+                                "runs all three kernels" if look else "log-mel(k), statistics(k), views(k)"),
                     mixup_bank=("global FIFO, bank entries read from the peers' rings over NVLink (optional mode)" if gbank
                                 else "rank-local FIFO (as each reference worker's)")),
         "roofline": {"bound": "hbm", "kernel": "logmel_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
@@ -403,7 +406,7 @@ def main():
     ap.add_argument("--rotate", type=int, default=4, help="distinct input batches cycled through (L2 hygiene)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="wall seconds of one CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--lookahead", type=int, default=0,
+    ap.add_argument("--lookahead", type=int, default=1,
                     help="1: software-pipelined step order log-mel(k), statistics(k), views(k-1)")
     ap.add_argument("--global-bank", action="store_true",
                     help="N > 1 only, not the headline configuration: mixup FIFO over the global clip order, bank entries read "

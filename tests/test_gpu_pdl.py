@@ -77,3 +77,39 @@ def _run(pdl):
 
 def test_pipeline_is_bit_identical_with_and_without_pdl():
     assert _run("1") == _run("0")
+
+
+def test_lookahead_pipeline_returns_the_same_views_one_call_later():
+    """Step order log-mel(k), statistics(k), views(k-1) (assl_two_views_deferred_f32) vs the ordinary order: same
+    draws, same running statistics, same bank -> bit-identical views, delivered one call later; flush() gives the last."""
+    import random
+
+    import audiossl_b200 as A
+    g = torch.Generator(device="cpu").manual_seed(21)
+    sizes = [64, 64, 17, 64, 40, 64, 64, 64, 64, 64, 64, 64, 64, 64, 64, 64, 64, 64, 64, 64, 33]   # > 1024 clips: bank wraps
+    batches = [(torch.randn(n, 15200, generator=g) * 0.1).cuda() for n in sizes]
+
+    np.random.seed(31); random.seed(31)
+    plain = A.UpstreamInputPipeline(CFG, 10 ** 6, max_batch=64)
+    want = [plain(w) for w in batches]
+    torch.cuda.synchronize()
+
+    np.random.seed(31); random.seed(31)
+    look = A.UpstreamInputPipeline(CFG, 10 ** 6, max_batch=64, lookahead=True)
+    assert look.tfms.engine.cap == plain.tfms.engine.cap + 64
+    got = []
+    for k, w in enumerate(batches):                    # streamed, no synchronisation between the calls
+        out = look(w)
+        assert (out is None) == (k == 0)
+        if out is not None:
+            got.append(out)
+    with pytest.raises(RuntimeError):
+        look.tfms.state_dict()                          # a batch is still pending
+    got.append(look.flush())
+    assert look.flush() is None
+    torch.cuda.synchronize()
+    assert len(got) == len(want)
+    for (a1, a2), (b1, b2) in zip(got, want):
+        assert a1.shape == b1.shape and torch.equal(a1, b1) and torch.equal(a2, b2)
+    sd = look.tfms.state_dict()
+    assert sd["clips_done"] == sum(sizes)
