@@ -156,8 +156,12 @@ class DeviceBatchLoader:
                 packed.ready.synchronize()                           # upload done -> the pinned slot may be refilled
                 released[k % n_slots].set()
                 packed.raw.record_stream(torch.cuda.current_stream(device))
-                v1, v2 = self.pipeline(packed)
-                yield v1, v2
+                out = self.pipeline(packed)
+                if out is not None:                                  # (a lookahead pipeline returns batch k-1 at call k)
+                    yield out
+            last = self.pipeline.flush() if getattr(self.pipeline, "flush", None) else None
+            if last is not None:
+                yield last
         finally:
             for e in released:
                 e.set()

@@ -239,6 +239,9 @@ class ViewEngine:
             local = torch.empty((b, 2), dtype=torch.float64, device=sums.device)
             _native.check(lib.assl_clip_sums(_ptr(sums), b, n_parts, _ptr(local), _stream_ptr()))
             gathered = gather_clip_sums(local)
+            # (kept until the next call: a deferred two-view launch may run beside this statistics kernel, and its
+            #  freshly allocated outputs must not land in a block the caching allocator got back from here)
+            self._keep = (local, gathered)
             _native.check(lib.assl_running_stats(_ptr(self.state), _ptr(gathered), world * b, 1, elems,
                                                  int(self.max_update), rank * b, b, _ptr(self.stats),
                                                  self.slot0, self.cap, _stream_ptr()), "assl_running_stats")

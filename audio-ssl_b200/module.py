@@ -150,12 +150,12 @@ class UpstreamInputPipeline:
         self._pending = None                 # lookahead: the batch whose front end has run, waiting for its views
 
     def __call__(self, waveforms, params: ViewParams = None):
-        if self.tfms.engine.lookahead:
-            return self._call_lookahead(waveforms, params)
         if isinstance(waveforms, PackedClips):
             return self._ragged(waveforms, params)
         if isinstance(waveforms, (list, tuple)):
             return self._ragged(list(waveforms), params)
+        if self.tfms.engine.lookahead:
+            return self._call_lookahead(waveforms, params)
         wave = as_cuda_f32(waveforms)
         if wave.dim() == 1:
             wave = wave.unsqueeze(0)
@@ -185,8 +185,6 @@ class UpstreamInputPipeline:
         statistics kernel of batch k with assl_two_views_deferred_f32: they fill the SMs the log-mel kernel's tail
         leaves idle and run beside the statistics kernel (and, across GPUs, beside its exchange).  Same views as the
         ordinary order, one call later; the draws happen in the same clip order."""
-        if isinstance(waveforms, (list, tuple, PackedClips)):
-            raise ValueError("lookahead takes equal-length windows [B, L]")
         wave = as_cuda_f32(waveforms)
         if wave.dim() == 1:
             wave = wave.unsqueeze(0)
@@ -198,27 +196,33 @@ class UpstreamInputPipeline:
             raise ValueError(f"lookahead takes at most max_batch = {eng.max_batch} clips per call")
         with torch.cuda.device(wave.device):
             eng.ensure(self.plan.n_mels, self.plan.num_frames(wave.shape[1]), wave.device)
-            # parameters of this batch: drawn and uploaded before its kernels, used one call later
-            prep = eng.prepare_views(tf._params(params, 0, b, g0=eng.head), b, wave.device, eng.head)
             gain = None
             if self.l2:
                 gain = torch.empty(b, dtype=torch.float32, device=wave.device)
                 _native.check(_native.lib().assl_wave_l2_gain_f32(_ptr(wave), b, wave.shape[1], wave.stride(0), _ptr(gain),
                                                                   _stream_ptr()))
-            tiles = self.plan.num_tiles(wave.shape[1])
-            sums = torch.empty((b, tiles, 2), dtype=torch.float64, device=wave.device) if tf.pre_norm else None
-            self.plan.logmel_into(wave, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain)
-            if tf.pre_norm:
-                eng.update_stats(sums, tiles)
-            eng.ahead += b
-            out = None
-            if self._pending is not None:
-                # (deferred only right behind the statistics kernel; without pre-norm the log-mel kernel of THIS batch
-                #  is the predecessor, which the deferred launch may overlap just the same)
-                v1, v2 = eng.launch_prepared(self._pending, deferred=True)
-                eng.ahead -= self._pending["batch"]
-                out = tf._post(v1, v2)
-            self._pending = prep
+            return self._front_then_previous_views(wave, gain, tf._params(params, 0, b, g0=eng.head))
+
+    def _front_then_previous_views(self, part, gain, p):
+        """[b, L] windows of THIS batch -> log-mel into the ring -> statistics; then the views of the pending batch."""
+        eng, tf = self.tfms.engine, self.tfms
+        b = part.shape[0]
+        # parameters of this batch: uploaded before its kernels, used one call later
+        prep = eng.prepare_views(p, b, part.device, eng.head)
+        tiles = self.plan.num_tiles(part.shape[1])
+        sums = torch.empty((b, tiles, 2), dtype=torch.float64, device=part.device) if tf.pre_norm else None
+        self.plan.logmel_into(part, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain)
+        if tf.pre_norm:
+            eng.update_stats(sums, tiles)
+        eng.ahead += b
+        out = None
+        if self._pending is not None:
+            # (deferred: right behind the statistics kernel -- or, without pre-norm, the log-mel kernel -- of THIS batch,
+            #  which the launch may overlap; everything it reads was complete before that log-mel kernel started)
+            v1, v2 = eng.launch_prepared(self._pending, deferred=True)
+            eng.ahead -= self._pending["batch"]
+            out = tf._post(v1, v2)
+        self._pending = prep
         return out
 
     def flush(self):
@@ -263,10 +267,12 @@ class UpstreamInputPipeline:
         v1s, v2s = [], []
         with torch.cuda.device(device):
             eng.ensure(self.plan.n_mels, self.plan.num_frames(self.unit_length), device)
+            if eng.lookahead and len(lengths) > eng.max_batch:
+                raise ValueError(f"lookahead takes at most max_batch = {eng.max_batch} clips per call")
             for lo, hi in _chunks(len(lengths), eng.max_batch):
                 adj = lengths[lo:hi] - self.unit_length
                 if params is None:       # the window offset of a clip is drawn before its view parameters
-                    p = tf.sampler.draw(eng.clips_done, hi - lo, eng.f, eng.t, window_adj=adj)
+                    p = tf.sampler.draw(eng.head, hi - lo, eng.f, eng.t, window_adj=adj)
                 else:
                     p = ViewParams(params.alpha[lo:hi], params.src_clip[lo:hi], params.bank_index[lo:hi],
                                    params.crop[lo:hi], None if params.start is None else params.start[lo:hi])
@@ -277,6 +283,8 @@ class UpstreamInputPipeline:
                 else:
                     win = extract_windows(clips[lo:hi], self.unit_length, starts=p.start, with_gain=self.l2, device=device)
                 part, gain = win if self.l2 else (win, None)
+                if eng.lookahead:
+                    return self._front_then_previous_views(part, gain, p)
                 a, c = self._windows_to_views(part, gain, lambda p=p: p)
                 v1s.append(a); v2s.append(c)
         v1 = v1s[0] if len(v1s) == 1 else torch.cat(v1s)

@@ -129,3 +129,15 @@ def test_shard_bounds(A):
         assert all(cuts[i][1] == cuts[i + 1][0] for i in range(w - 1))
         sizes = [b - a for a, b in cuts]
         assert max(sizes) - min(sizes) <= 1
+
+
+def test_lookahead_ring_bookkeeping_on_the_host():
+    """ViewEngine(lookahead=True): one more batch of ring, the write head runs ``ahead`` clips in front of the views."""
+    from audiossl_b200.engine import ViewEngine
+    plain = ViewEngine(max_update=100, max_batch=64)
+    look = ViewEngine(max_update=100, max_batch=64, lookahead=True)
+    assert plain.cap == 1024 + 64 and look.cap == 1024 + 2 * 64
+    look.clips_done, look.ahead = 5 * 64, 64
+    assert look.head == 6 * 64 and look.slot0 == (6 * 64) % look.cap
+    with pytest.raises(RuntimeError):
+        look.state_dict()

@@ -137,3 +137,26 @@ def test_device_batch_loader_matches_reference_epoch():
             for have, ref in ((got[k][0][r], a), (got[k][1][r], b)):
                 d = np.abs(have.numpy() - ref.numpy())
                 assert (d <= 5e-5 + 1e-4 * np.abs(ref.numpy())).all(), (k, r, d.max())
+
+
+def test_device_batch_loader_with_a_lookahead_pipeline_yields_the_same_epoch():
+    """Raw clips through a lookahead pipeline (extract_window, log-mel, statistics of batch k; views of batch k-1,
+    deferred launch; flush at the end of the epoch): the same batches, bit for bit, as the ordinary order."""
+    import audiossl_b200 as A
+    bs = 4
+    lengths = [8000, 12000, 3000, 8001, 20000, 8000, 9500, 16000, 100, 11000, 8000, 30000, 7000, 9000, 8000, 8000, 12345]
+    clips = [c.numpy() for c in _raw_clips(lengths, 33)]
+
+    def epoch(lookahead):
+        torch.manual_seed(7); np.random.seed(31); random.seed(31)
+        pipe = A.UpstreamInputPipeline(CFG, len(clips), max_batch=8, lookahead=lookahead)
+        dm = A.BaselineDataModule(CFG, None, pipe, data_csv=clips, batch_size=bs, num_workers=2)
+        dm.setup()
+        out = [(a.clone(), b.clone()) for a, b in dm.train_dataloader()]
+        torch.cuda.synchronize()
+        return out
+
+    want, got = epoch(False), epoch(True)
+    assert len(got) == len(want) == len(clips) // bs
+    for (a1, a2), (b1, b2) in zip(got, want):
+        assert torch.equal(a1, b1) and torch.equal(a2, b2)
