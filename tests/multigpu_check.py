@@ -95,12 +95,28 @@ def main():
         src = sharded.tfms.last_params.src_clip
         remote += int(np.sum((src >= 0) & ((src % (world * b)) // b != rank)))
     assert remote > 0                                             # bank entries really came from other GPUs
+    # ---- lookahead step order across GPUs: the deferred views of batch k-1 run beside the statistics EXCHANGE of batch k.
+    #      Sharded lookahead pipeline (rank-local banks, global statistics) == the same pipeline in the ordinary order.
+    import random
+    rng_state = (np.random.get_state(), random.getstate())
+    batches = [(torch.randn(b, 8000, generator=g) * 0.1).to(dev) for _ in range(14)]          # > 1024 clips: the bank wraps
+    np.random.seed(31 + rank); random.seed(31 + rank)
+    plain = A.UpstreamInputPipeline(cfg_mix, 10 ** 6, max_batch=b)
+    want = [plain(w) for w in batches]
+    np.random.seed(31 + rank); random.seed(31 + rank)
+    look = A.UpstreamInputPipeline(cfg_mix, 10 ** 6, max_batch=b, lookahead=True)
+    got = [look(w) for w in batches][1:] + [look.flush()]
+    torch.cuda.synchronize()
+    assert look.tfms.engine._exchange is not None
+    for (a1, a2), (b1, b2) in zip(got, want):
+        assert torch.equal(a1, b1) and torch.equal(a2, b2)
+    np.random.set_state(rng_state[0]); random.setstate(rng_state[1])
     assert float(sharded.tfms.engine.state[7]) == 0.0
     dist.barrier()
     ex.close()
     if rank == 0:
         print(f"multigpu_check: OK on {world} GPUs (peer exchange == NCCL path == single stream, bit for bit; "
-              f"global bank == unsharded run, {remote} remote bank entries on rank 0)")
+              f"global bank == unsharded run, {remote} remote bank entries on rank 0; lookahead order == ordinary order)")
     dist.destroy_process_group()
 
 
