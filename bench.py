@@ -113,7 +113,7 @@ def run_reference_arm(args):
     arm.close()
     val = clips / wall
     sample = f"{clips} clips in {args.steps} steps of {step_s:.1f} s, {args.seconds:g} s 16 kHz noise clips"
-    print(json.dumps({
+    _emit(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32 (fp64 FFT)", "data": "synthetic",
@@ -398,12 +398,28 @@ def run_ours(args):
                                "sample": f"{n_done} clips of {args.seconds:g} s noise in {dt:.1f} s, "
                                          f"one single-threaded process per core (oracle port: numpy librosa restatement + "
                                          f"restated reference augmentations)"}
-    print(json.dumps(out))
+    _emit(json.dumps(out))
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def _emit(line):
+    """The one JSON line goes to the process's original stdout."""
+    out = _REAL_STDOUT or sys.stdout
+    out.write(line + "\n")
+    out.flush()
+
+
 def main():
+    # stdout carries exactly one line: anything a library prints there (NCCL's version banner on the first collective)
+    # is sent to stderr instead
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
