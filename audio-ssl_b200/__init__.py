@@ -9,8 +9,8 @@ from . import _native
 from .augmentations import (Kmix, MixupBYOLA, NormalizeBatch, PrecomputedNorm, RandomResizeCrop,  # noqa: F401
                             RunningNorm)
 from .datamodule import BaselineDataModule, DeviceBatchLoader, PackedClips, WaveformDataset  # noqa: F401
-from .engine import ViewEngine, shard_bounds  # noqa: F401
-from .frontend import (MelSpectrogramLibrosa, Plan, extract_log_mel_spectrogram, extract_window,  # noqa: F401
+from .engine import StatsExchange, ViewEngine, shard_bounds  # noqa: F401
+from .frontend import (HostPipeline, MelSpectrogramLibrosa, Plan, extract_log_mel_spectrogram, extract_window,  # noqa: F401
                        extract_windows, extract_windows_packed)
 from .module import AugmentationModule, UpstreamInputPipeline  # noqa: F401
 from .sampler import FastSampler, ReferenceSampler, ViewParams  # noqa: F401

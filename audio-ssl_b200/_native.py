@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.environ.get("ASSL_LIB") or os.path.join(CSRC, "libassl.so")   # ASSL_LIB: an experimental build
 SOURCES = ["plan.cu", "logmel.cu", "window.cu", "stats.cu", "views.cu", "kmix.cu", "pipeline.cu"]
-HEADERS = ["common.cuh", "fft32_gen.cuh", "fft32p_gen.cuh", "f32x2.cuh", os.path.join("..", "..", "include", "assl.h")]
+HEADERS = ["common.cuh", "fft32p_gen.cuh", "f32x2.cuh", os.path.join("..", "..", "include", "assl.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC"]
 
@@ -72,6 +72,12 @@ SIGNATURES = {
     "assl_exchange_create": (C.c_int, [C.POINTER(_P), C.c_int32, C.c_int32, _I64, _P]),
     "assl_exchange_connect": (C.c_int, [_P, _P]),
     "assl_exchange_destroy": (C.c_int, [_P]),
+    "assl_exchange_use_staging": (C.c_int, [_P]),
+    "assl_exchange_staging": (C.c_int, [_P, _I64, C.POINTER(_P), C.POINTER(_I64)]),
+    "assl_exchange_set_timeout": (C.c_int, [_P, C.c_double]),
+    "assl_exchange_error": (C.c_int, [_P]),
+    "assl_exchange_send": (C.c_int, [_P, _P, _I64, _I64, _P]),
+    "assl_running_stats_exchange_scan": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _I64, C.c_int32, C.c_int32, _P]),
     "assl_running_stats_exchange": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P, _I64, _I64, C.c_int32, _P]),
     "assl_peer_alloc": (C.c_int, [C.POINTER(_P), _I64, _P]),
     "assl_peer_free": (C.c_int, [_P]),
@@ -86,6 +92,8 @@ SIGNATURES = {
     "assl_batch_sums": (C.c_int, [_P, _I64, _P, _P]),
     "assl_normalize_apply_f32": (C.c_int, [_P, _P, _I64, _P, _P]),
     "assl_affine_norm_f32": (C.c_int, [_P, _P, _I64, _F, _F, _P]),
+    "assl_pipeline_create": (C.c_int, [C.POINTER(_P), _P, _P]),
+    "assl_pipeline_destroy": (C.c_int, [_P]),
     "assl_pipeline_workspace_bytes": (_I64, [_P, _I64, _I64, _I64]),
     "assl_pipeline_host_sync": (C.c_int, [_P]),
     "assl_pipeline_host_f32": (C.c_int, [_P, C.POINTER(ViewCfg), _P, _I64, _P, _I64, _I64, _I64, _I64, _I64,

@@ -5,6 +5,7 @@
 #include <stdint.h>
 #include <stdlib.h>
 
+#include <atomic>
 #include <vector>
 
 #include "../../include/assl.h"
@@ -59,7 +60,9 @@ __host__ __device__ inline long long ring_slot(long long slot0, long long b, lon
 
 }  // namespace assl
 
-// Plan: immutable after creation.  Device tables are owned by the library.
+// Plan: immutable after creation (the log-mel kernel's work-claiming counters are scratch that every launch hands back
+// zeroed; the slot a launch uses is drawn from an atomic, so concurrent callers are safe).  Device tables are owned by
+// the library.
 struct assl_plan {
   assl_cfg cfg;
   int device;
@@ -69,18 +72,14 @@ struct assl_plan {
   int4* d_lane_iv;              // [slots][32]  interval part owned by (slot, lane) in the log-mel kernel:
                                 //              {first bin (even) | valid-bin mask << 10 | scratch entry << 18 |
                                 //               starts-the-total << 26 | owns-a-part << 27, alpha, beta, 0}
-  float2* d_mel_const;          // [n_mels]     {enorm, 2.22e-16 * sum of the band's weights (folded "+ eps" of utils.py:28)}
+  int4* d_band;                 // [n_mels]     {byte offset of U(m) / of D(m+1) in a warp's interval totals, enorm,
+                                //              2.22e-16 * sum of the band's weights (folded "+ eps" of utils.py:28)}
   std::vector<float> h_fb;      // dense [n_mels][513] copy for assl_plan_filterbank
   std::vector<int4> h_lane_iv;  // host copy of d_lane_iv
   std::vector<int> h_iv_pos;    // [n_mels+1] scratch entry of every interval's total
-  int* d_iv_pos = nullptr;
-  // Copy streams + events of assl_pipeline_host_f32 (created on first use; that entry point is
-  // single-caller per plan, everything else on a plan is read-only and thread-safe).
-  static constexpr int kMaxChunks = 8;
-  mutable bool aux_ready = false;
-  mutable cudaStream_t s_in = nullptr, s_out = nullptr;
-  mutable cudaEvent_t ev_fork = nullptr;
-  mutable cudaEvent_t ev_in[kMaxChunks] = {}, ev_out[kMaxChunks] = {};
-  mutable cudaEvent_t ev_kern[2] = {}, ev_d2h[2] = {};   // per buffer parity: kernels / downloads of that call done
-  mutable long long calls = 0;
+  // work-claiming counters of the log-mel kernel: {next ticket, warps done} per slot, zero between launches (the
+  // kernel resets its own); the slot a launch uses is drawn here, so concurrent callers never share one
+  static constexpr unsigned kTicketSlots = 64;
+  unsigned* d_tickets = nullptr;
+  mutable std::atomic<unsigned> ticket_seq{0};
 };

@@ -49,7 +49,7 @@ __device__ __forceinline__ c32 neg2(c32 b) { float r, i; upk(b, r, i); return pk
 __device__ __forceinline__ c32 swp(c32 b) { float r, i; upk(b, r, i); return pk(i, r); }
 __device__ __forceinline__ c32 bc(float s) { return pk(s, s); }
 
-// butterfly pieces used by the generated FFT (tools/gen_fft32.py --packed)
+// butterfly pieces used by the generated FFT (tools/gen_fft32.py)
 __device__ __forceinline__ c32 c_add(c32 a, c32 b) { return add2(a, b); }
 __device__ __forceinline__ c32 c_sub(c32 a, c32 b) { return sub2(a, b); }
 __device__ __forceinline__ c32 c_add_mj(c32 a, c32 b) { return add2(a, mj(b)); }          // a + (-i) b

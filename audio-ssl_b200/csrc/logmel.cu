@@ -70,8 +70,13 @@ struct LogmelArgs {
   int n_slots;        // rows of lane_iv in use
   const float2* tw;
   const int4* lane_iv;   // [kIvSlots][32] interval part owned by (slot, lane), see assl_plan::d_lane_iv
-  const int* iv_pos;     // [n_mels + 1] scratch entry holding interval j's total
-  const float2* mconst;  // [n_mels] {enorm, 2.22e-16 * sum of the band's weights (the "+ eps" of utils.py:28, folded)}
+  const int4* band;      // [n_mels] {byte offset of U(m) in the warp's scratch, of D(m+1), enorm, 2.22e-16 * sum of the
+                         //           band's weights (the "+ eps" of utils.py:28, folded)} (fp32 bits)
+  unsigned* ticket;      // {next ticket, warps done}: pairs beyond the first two rounds are claimed, not dealt; the last
+                         // warp to finish zeroes both (assl_plan::d_tickets, one pair per launch in flight); null = dealt
+  int q_edge_lo, q_edge_hi;   // pairs q < q_edge_lo / q >= q_edge_hi of a clip touch the reflect padding (or the tail
+                              // remainder of an L that is not a multiple of 4): their span is patched by the warp
+  int span4;             // (n_fft + hop) & ~3: what one bulk copy covers for every other pair
 };
 
 __host__ __device__ inline size_t logmel_smem_bytes(int warps, int wave_floats) {
@@ -79,10 +84,9 @@ __host__ __device__ inline size_t logmel_smem_bytes(int warps, int wave_floats) 
   b += sizeof(float2) * warps * kExWarp;    // exchange / power / interval-sum buffers
   b += sizeof(float2) * 32 * kTwStride;     // twiddles
   b += sizeof(float) * warps * wave_floats; // staging
-  b += sizeof(float2) * kMaxMels;           // per-band {enorm, folded eps}
+  b += sizeof(int4) * kMaxMels;             // per-band {scratch offsets of its two edges, enorm, folded eps}
   b += sizeof(int4) * kIvSlots * 32;        // interval ownership
-  b += sizeof(int) * (kMaxMels + 4);        // scratch entry per interval
-  b += sizeof(unsigned long long) * kMaxWarps;   // one mbarrier per warp
+  b += sizeof(unsigned long long) * (kMaxWarps + 32);  // one mbarrier per warp + the ticket counter's address, per lane
   return b;
 }
 
@@ -107,6 +111,15 @@ __device__ __forceinline__ float ln_ftz(float x) {           // MUFU.LG2 * ln 2,
   float y;
   asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y * 0.6931471805599453f;
+}
+// One ticket, drawn by the calling lane alone.  (atomicAdd() would be warp-aggregated by the compiler: vote + popc + one
+// ATOMG + a SHFL that hands the base to the active lanes -- and that SHFL waits for the atomic's round trip on the spot,
+// while the whole point here is to consume the value a pair of compute later.  ptxas does the same to a PTX atom on an
+// address it can prove warp-uniform, so each lane reads the counter's address from its own shared-memory word.)
+__device__ __forceinline__ unsigned draw_ticket(unsigned* counter) {
+  unsigned t;
+  asm volatile("atom.global.add.u32 %0, [%1], 1;" : "=r"(t) : "l"(counter) : "memory");
+  return t;
 }
 __device__ __forceinline__ ulonglong2 lds128(unsigned addr) {
   ulonglong2 v;
@@ -133,25 +146,29 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
 #endif
 }
 
-// Frame pair p of the flattened list: clip, pair inside the clip, and the part of its span [base, base + span)
-// (clip-relative samples, base = 2 q hop - n_fft/2) a bulk copy can cover: [lo, hi) span-relative, multiples of 4.
-struct PairSpan {
-  int clip, q, lo, hi;
-  long long base;
+// Frame pair p of the flattened list -> clip and pair inside the clip (one multiply-high, see assl_logmel_f32).
+struct PairPos {
+  int clip, q;
 };
-__device__ __forceinline__ PairSpan pair_span(const LogmelArgs& a, int p, int span) {
-  PairSpan s;
+__device__ __forceinline__ PairPos pair_pos(const LogmelArgs& a, int p) {
+  PairPos s;
   const unsigned t = __umulhi(a.ppc_mul, static_cast<unsigned>(p));
   s.clip = static_cast<int>((t + ((static_cast<unsigned>(p) - t) >> a.ppc_sh1)) >> a.ppc_sh2);
   s.q = p - s.clip * a.ppc;
-  s.base = 2ll * s.q * a.hop - kNfft / 2;
-  const long long l = s.base < 0 ? -s.base : 0;
-  long long h = a.L - s.base;
-  h = h > span ? span : h;
-  h &= ~3ll;
-  s.lo = a.bulk_ok ? static_cast<int>(l) : 0;
-  s.hi = a.bulk_ok ? static_cast<int>(h > l ? h : l) : 0;      // no bulk copy: the whole span goes through the patch loop
   return s;
+}
+// The part [lo, hi) (span-relative samples, multiples of 4) of a pair's span [base, base + span), base = 2 q hop -
+// n_fft/2 clip-relative, that a bulk copy can cover.  Everything fits 32 bits: L < 2^31 - 4096 (assl_logmel_f32).
+__device__ __forceinline__ void pair_cover(const LogmelArgs& a, int q, int span, int* lo, int* hi) {
+  *lo = 0; *hi = a.span4;
+  if (q < a.q_edge_lo || q >= a.q_edge_hi) {         // warp-uniform; ~5 of the 51 pairs of a 1-s clip
+    const int base = 2 * q * a.hop - kNfft / 2;
+    const int l = base < 0 ? -base : 0;
+    int h = static_cast<int>(a.L) - base;
+    h = (h > span ? span : h) & ~3;
+    *lo = l; *hi = h > l ? h : l;
+  }
+  if (!a.bulk_ok) { *lo = 0; *hi = 0; }              // no bulk copy: the whole span goes through the patch loop
 }
 
 // H32 = hop / 32 when hop is a multiple of 32 (both frames of a pair share registers), else 0
@@ -162,10 +179,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   float2* s_ex = reinterpret_cast<float2*>(smem_raw);
   float2* s_tw = s_ex + n_warps * kExWarp;
   float* s_wave = reinterpret_cast<float*>(s_tw + 32 * kTwStride);
-  float2* s_mconst = reinterpret_cast<float2*>(s_wave + n_warps * a.wave_floats);
-  int4* s_lane = reinterpret_cast<int4*>(s_mconst + kMaxMels);             // [kIvSlots][32]
-  int* s_pos = reinterpret_cast<int*>(s_lane + kIvSlots * 32);              // [n_mels + 1]
-  unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_pos + kMaxMels + 4);
+  int4* s_band = reinterpret_cast<int4*>(s_wave + n_warps * a.wave_floats);   // [n_mels]
+  int4* s_lane = s_band + kMaxMels;                                          // [kIvSlots][32]
+  unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_lane + kIvSlots * 32);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n_threads = blockDim.x;
@@ -173,18 +189,24 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   float* buf = s_wave + warp * a.wave_floats;
 
   if (lane == 0) mbar_init(bar, 1);
+  if (tid < 32) s_bar[kMaxWarps + tid] = reinterpret_cast<unsigned long long>(a.ticket);   // (see draw_ticket)
   const int span = kNfft + a.hop;                    // samples the two frames of a pair touch
   const int stride = static_cast<int>(gridDim.x) * n_warps;
   // producer side of the warp's pipeline (lane 0): bulk-copy the in-range part of a pair's span
   const unsigned long long wave_policy = l2_evict_first_policy();
-  auto issue = [&](int p) {
-    const PairSpan s = pair_span(a, p, span);
-    const unsigned bytes = static_cast<unsigned>(s.hi - s.lo) * 4u;
+  auto issue = [&](PairPos s) {
+    int lo, hi;
+    pair_cover(a, s.q, span, &lo, &hi);
+    const unsigned bytes = static_cast<unsigned>(hi - lo) * 4u;
     mbar_expect_tx(bar, bytes);
-    if (bytes) bulk_g2s(buf + s.lo, a.wave + s.clip * a.ld + s.base + s.lo, bytes, bar, wave_policy);
+    if (bytes) bulk_g2s(buf + lo, a.wave + (s.clip * a.ld + (2 * s.q * a.hop - kNfft / 2 + lo)), bytes, bar, wave_policy);
   };
-  // warp-major numbering: consecutive pairs go to different SMs, so the last, partial round (52224 pairs over 2368
-  // warps = 22.05 rounds) is one uncontended warp on each of 128 SMs instead of 16 contending warps on 8 of them
+  // Pair -> warp.  The first two rounds are dealt (warp-major numbering: consecutive pairs go to different SMs, so
+  // that the resident warps work on neighbouring frames and the 6.4x overlap of hop-160 frames is served by L2);
+  // every later pair is CLAIMED from a ticket counter, one atomic per pair fired a whole pair of compute before its
+  // value is needed.  52224 pairs over 2368 warps are 22.05 rounds: dealt statically, the 23rd round (one warp per SM)
+  // and every SM that got its CTA late set the kernel's duration; claimed, the warps all run out of work within one
+  // pair of each other, and an SM that starts early (under the tail of the kernel before) simply takes more pairs.
   const int first = warp * static_cast<int>(gridDim.x) + static_cast<int>(blockIdx.x);
   // Launched behind another kernel of the path (PDL) this CTA gets its SM while that grid's last wave drains and
   // loads the plan's tables (immutable, never written by a kernel) meanwhile; the waveform, the ring and the sums
@@ -204,38 +226,46 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   float wa, wb;
   sincospif(static_cast<float>(lane) * (1.0f / 512.0f), &wb, &wa);
   wa *= -0.25f; wb *= 0.25f;
-  for (int i = tid; i < a.n_mels; i += n_threads) s_mconst[i] = a.mconst[i];
+  for (int i = tid; i < a.n_mels; i += n_threads) s_band[i] = a.band[i];
   for (int i = tid; i < kIvSlots * 32; i += n_threads) s_lane[i] = a.lane_iv[i];
-  for (int i = tid; i <= a.n_mels; i += n_threads) s_pos[i] = a.iv_pos[i];
   // (s_ex needs no clearing: every power bin a part reads is either written by this pair or selected away,
   //  never multiplied, and every interval total is started before it is read)
   pdl_wait();
   // (after the wait, so that a kernel launched behind this one knows every older grid has completed: that is what lets
   //  a deferred two-view launch, assl_two_views_deferred_f32, start without waiting for this grid)
   pdl_launch_dependents();
+  int cur = first, nxt = first + stride;             // the pair in work; the pair whose span is being copied
+  PairPos pc = pair_pos(a, cur);
+  unsigned ticket = 0;                               // lane 0: the claim in flight (becomes the pair after nxt)
   // the first copy flies while the other warps finish the tables (only this warp's lane 0 touches its barrier and buffer)
-  if (a.bulk_ok && lane == 0 && first < a.total_pairs) {
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    issue(first);
+  if (lane == 0 && cur < a.total_pairs) {
+    if (a.bulk_ok) {
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      issue(pc);
+    }
   }
   __syncthreads();                                   // the only CTA-wide barrier
+  unsigned* const ticket_ctr = reinterpret_cast<unsigned*>(s_bar[kMaxWarps + lane]);
+  if (lane == 0 && a.ticket && nxt < a.total_pairs) ticket = draw_ticket(ticket_ctr);
 
   c32* ex = reinterpret_cast<c32*>(s_ex + warp * kExWarp);
+  const unsigned scratch_addr = smem_u32(ex + kScratch);
   unsigned it = 0;
-  for (int pair = first; pair < a.total_pairs; pair += stride, ++it) {
-    const PairSpan sp = pair_span(a, pair, span);
-    const int clip = sp.clip, wpair = sp.q;
-
+  while (cur < a.total_pairs) {
+    const int clip = pc.clip, wpair = pc.q;
     // ---- waveform span: wait for the bulk copy, patch what it could not cover (reflect padding of
     //      np.pad(mode='reflect'): p<0 -> -p, p>L-1 -> 2(L-1)-p; tail remainder when L % 4 != 0)
     if (a.bulk_ok) mbar_wait(bar, it & 1);
-    if (sp.lo > 0 || sp.hi < span) {                 // warp-uniform: ~5 of 51 pairs of a 1-s clip
+    if (wpair < a.q_edge_lo || wpair >= a.q_edge_hi || !a.bulk_ok) {   // warp-uniform
+      int lo, hi;
+      pair_cover(a, wpair, span, &lo, &hi);
+      const int base = 2 * wpair * a.hop - kNfft / 2;
       const int last = static_cast<int>(a.L - 1);
-      const int n_fix = sp.lo + (span - sp.hi);
+      const int n_fix = lo + (span - hi);
       const float* src = a.wave + clip * a.ld;
       for (int q = lane; q < n_fix; q += 32) {
-        const int i = q < sp.lo ? q : sp.hi + (q - sp.lo);
-        long long p = sp.base + i;
+        const int i = q < lo ? q : hi + (q - lo);
+        long long p = static_cast<long long>(base) + i;
         if (p < 0) p = -p;
         if (p > last) p = 2ll * last - p;
         p = p < 0 ? 0 : (p > last ? last : p);       // only frames >= T can land here; never read back
@@ -274,7 +304,14 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
     }
     // the span is in registers: the next pair's copy may overwrite the buffer and lands behind this pair's compute
     __syncwarp();
-    if (a.bulk_ok && lane == 0 && pair + stride < a.total_pairs) issue(pair + stride);
+    const PairPos pn = pair_pos(a, nxt);
+    if (a.bulk_ok && lane == 0 && nxt < a.total_pairs) issue(pn);
+    // the pair after that: the ticket drawn one pair ago has long arrived; draw the next one
+    int nn = nxt + stride;
+    if (a.ticket) {
+      nn = 2 * stride + static_cast<int>(__shfl_sync(0xffffffffu, ticket, 0));
+      if (lane == 0 && nn < a.total_pairs) ticket = draw_ticket(ticket_ctr);
+    }
 
     fft32p(z);                                       // over n2 -> k2, this lane is n1
     {   // inter-stage twiddles W^(n1 k2), k2 = 8a + b: z * t = z * t.re + (i z) * t.im
@@ -334,7 +371,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
     //      one part (kPartBins bins) of an interval per slot: S0 = sum P, S1 = sum r P over the part's own bins,
     //      U = sum t P = alpha S1 + beta S0, D = S0 - U.  Interval totals {D(j), U(j)} live behind the power
     //      spectra, one 16-byte entry each at a plan-chosen position; band m = enorm(m) (U(m) + D(m+1)).
-    c32* scratch = ex + kScratch;
+    //      (Bins of a part that belong to the neighbouring interval are zeroed by selects, R2P + 2 SEL per bin.  Guarding
+    //      the adds instead -- ``if``, or @p in PTX -- buys nothing: ptxas turns either into FADD2 + 2 MOV/SEL.)
     for (int s = 0; s < a.n_slots; ++s) {
       const int4 iv = s_lane[s * 32 + lane];         // the same interval parts for the whole launch
       const unsigned pv = smem_u32(ex + (iv.x & 0x3ff));
@@ -352,9 +390,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
         const c32 S0 = add2(s0a, s0b), S1 = add2(s1a, s1b);
         c32 su = fma2(bc(__int_as_float(iv.y)), S1, mul2(bc(__int_as_float(iv.z)), S0));
         c32 sd = sub2(S0, su);
-        ulonglong2* tot = reinterpret_cast<ulonglong2*>(scratch) + ((iv.x >> 18) & 0xff);
-        if (!(iv.x & (1 << 26))) { const ulonglong2 o = *tot; sd = add2(o.x, sd); su = add2(o.y, su); }
-        *tot = make_ulonglong2(sd, su);
+        const unsigned tot = scratch_addr + (static_cast<unsigned>(iv.x >> 14) & 0xff0u);   // 16-byte entry (iv.x >> 18) & 0xff
+        if (!(iv.x & (1 << 26))) { const ulonglong2 o = lds128(tot); sd = add2(o.x, sd); su = add2(o.y, su); }
+        asm volatile("st.shared.v2.u64 [%0], {%1, %2};" ::"r"(tot), "l"(sd), "l"(su) : "memory");
       }
       __syncwarp();
     }
@@ -365,22 +403,23 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
     long long slot = a.slot0 + clip;
     if (a.cap > 0 && slot >= a.cap) slot -= a.cap;
     const bool power = a.out_kind & 1, tmajor = a.out_kind & 2;      // [n_mels, T] rows, or time-major [T, n_mels]
-    float* out = a.lms + slot * (static_cast<long long>(a.n_mels) * a.T) + (tmajor ? ta * a.n_mels : ta);
     const int band_stride = tmajor ? 1 : a.T, frame_stride = tmajor ? a.n_mels : 1;
+    float* dst = a.lms + slot * (static_cast<long long>(a.n_mels) * a.T) + (tmajor ? ta * a.n_mels : ta) + lane * band_stride;
     float g2 = 1.f;
     if (a.gain) { const float g = a.gain[clip]; g2 = g * g; }   // |g x|^2 = g^2 |x|^2: per-clip gain applied here
     float s1 = 0.f, s2 = 0.f;
-    for (int m = lane; m < a.n_mels; m += 32) {
-      const c32 su = scratch[2 * s_pos[m] + 1], sd = scratch[2 * s_pos[m + 1]];   // rising edge + falling edge
+    for (int m = lane; m < a.n_mels; m += 32, dst += 32 * band_stride) {
+      const int4 bd = s_band[m];                     // {offset of U(m), offset of D(m+1), enorm, folded eps}
+      c32 su, sd;                                    // rising edge + falling edge
+      asm volatile("ld.shared.u64 %0, [%1];" : "=l"(su) : "r"(scratch_addr + bd.x) : "memory");
+      asm volatile("ld.shared.u64 %0, [%1];" : "=l"(sd) : "r"(scratch_addr + bd.y) : "memory");
       float acc0, acc1;
       upk(add2(su, sd), acc0, acc1);
-      const float2 c = s_mconst[m];                  // {enorm, folded eps}
-      const float e = c.x * g2;
-      acc0 = fmaf(acc0, e, c.y);
-      acc1 = fmaf(acc1, e, c.y);
+      const float e = __int_as_float(bd.z) * g2, eps = __int_as_float(bd.w);
+      acc0 = fmaf(acc0, e, eps);
+      acc1 = fmaf(acc1, e, eps);
       const float l0 = power ? acc0 : ln_ftz(acc0 + kLogEps);      // the argument is >= 1.19e-7: no denormal path needed
       const float l1 = power ? acc1 : ln_ftz(acc1 + kLogEps);
-      float* dst = out + m * band_stride;
       dst[0] = l0;
       s1 += l0; s2 = fmaf(l0, l0, s2);
       if (two) { dst[frame_stride] = l1; s1 += l1; s2 = fmaf(l1, l1, s2); }
@@ -391,8 +430,15 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
         s1 += __shfl_xor_sync(0xffffffffu, s1, o);
         s2 += __shfl_xor_sync(0xffffffffu, s2, o);
       }
-      if (lane == 0) reinterpret_cast<double2*>(a.pair_sums)[pair] = make_double2(s1, s2);
+      if (lane == 0) reinterpret_cast<double2*>(a.pair_sums)[cur] = make_double2(s1, s2);
     }
+    cur = nxt; nxt = nn; pc = pn; ++it;
+  }
+  // the ticket counter is handed back zeroed: every warp counts itself out after its last claim has returned, the
+  // last one resets (the next launch on this counter is many launches away, see assl_plan::d_tickets)
+  if (a.ticket && lane == 0) {
+    const unsigned total_warps = static_cast<unsigned>(stride);
+    if (atomicAdd(a.ticket + 1, 1u) == total_warps - 1) { a.ticket[0] = 0u; a.ticket[1] = 0u; }
   }
 }
 
@@ -461,7 +507,14 @@ extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const floa
   // the bulk (TMA) copy needs 16-byte aligned global addresses: clip starts and span starts (2*q*hop - 512)
   a.bulk_ok = (reinterpret_cast<uintptr_t>(wave) % 16 == 0) && (ld % 4 == 0) && (p->cfg.hop % 2 == 0);
   a.tw = p->d_twiddle;
-  a.lane_iv = p->d_lane_iv; a.iv_pos = p->d_iv_pos; a.mconst = p->d_mel_const;
+  a.lane_iv = p->d_lane_iv; a.band = p->d_band;
+  {   // which pairs of a clip touch the reflect padding / the unaligned tail (pair_cover)
+    const int64_t span = kNfft + a.hop;
+    a.span4 = static_cast<int>(span & ~3ll);
+    a.q_edge_lo = (kNfft / 2 + 2 * a.hop - 1) / (2 * a.hop);                 // 2 q hop < n_fft / 2
+    const int64_t room = L - span + kNfft / 2;                                // 2 q hop <= room: the span ends inside the clip
+    a.q_edge_hi = (span % 4 != 0 || room < 0) ? 0 : static_cast<int>(room / (2 * a.hop) + 1);
+  }
   // as many warps per CTA (one CTA per SM) as shared memory allows
   int warps = kMaxWarps;
   if (const char* e = getenv("ASSL_LOGMEL_WARPS")) { const int w = atoi(e); if (w >= 1 && w <= kMaxWarps) warps = w; }
@@ -470,6 +523,13 @@ extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const floa
   if (smem > 227 * 1024) return ASSL_ERR_UNSUPPORTED;
   const int64_t ctas = (total_pairs + warps - 1) / warps;
   const unsigned grid = static_cast<unsigned>(ctas < p->sm_count ? ctas : p->sm_count);
+  // pairs beyond the first two rounds are claimed from a ticket counter (ASSL_LOGMEL_TICKETS=0: dealt, for A/B runs).
+  // Counters are handed out round-robin; a launch leaves its counter zeroed, and kTicketSlots launches would have to be
+  // in flight at once for two of them to share one.
+  a.ticket = nullptr;
+  static const bool tickets_on = [] { const char* e = getenv("ASSL_LOGMEL_TICKETS"); return !(e && e[0] == '0'); }();
+  if (tickets_on && total_pairs > 2ll * grid * warps)
+    a.ticket = p->d_tickets + 2 * (p->ticket_seq.fetch_add(1u, std::memory_order_relaxed) % assl_plan::kTicketSlots);
   if (a.hop == 160) return launch_logmel<5>(a, smem, grid, warps, as_stream(stream));
   return launch_logmel<0>(a, smem, grid, warps, as_stream(stream));
 }

@@ -9,6 +9,7 @@
 // computes and chunk c-1 downloads (in a stream of calls whole-batch copies are faster, see below).  Kernels stay in order on the caller's stream (statistics scan and bank are sequential
 // in clip order).  Host result buffers are complete after assl_pipeline_host_sync().
 #include <cstdlib>
+#include <new>
 
 #include "common.cuh"
 
@@ -48,51 +49,78 @@ __global__ void iota_slots_kernel(int32_t* slot, long long B, long long slot0, l
   if (b < B) slot[b] = static_cast<int32_t>(assl::ring_slot(slot0, b, cap));
 }
 
-int ensure_aux(const assl_plan* p) {
-  if (p->aux_ready) return ASSL_OK;
-  bool ok = cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking) == cudaSuccess &&
-            cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking) == cudaSuccess;
+}  // namespace
+
+// The host-buffer pipeline's own state: copy streams, events, call parity.  One caller at a time per pipeline; the
+// plan it was created on stays immutable and can be shared.
+struct assl_pipeline {
+  static constexpr int kMaxChunks = 8;
+  const assl_plan* plan = nullptr;
+  assl_exchange* exchange = nullptr;       // statistics exchange of a clip-sharded multi-GPU run, or null
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ev_fork = nullptr;
+  cudaEvent_t ev_in[kMaxChunks] = {}, ev_out[kMaxChunks] = {};
+  cudaEvent_t ev_kern[2] = {}, ev_d2h[2] = {};   // per buffer parity: kernels / downloads of that call done
+  long long calls = 0;
+};
+
+extern "C" int assl_pipeline_create(assl_pipeline** out, const assl_plan* plan, assl_exchange* exchange) {
+  if (!out || !plan) return ASSL_ERR_INVALID_ARG;
+  *out = nullptr;
+  assl_pipeline* pipe = new (std::nothrow) assl_pipeline();
+  if (!pipe) return ASSL_ERR_CUDA;
+  pipe->plan = plan; pipe->exchange = exchange;
+  bool ok = cudaStreamCreateWithFlags(&pipe->s_in, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaStreamCreateWithFlags(&pipe->s_out, cudaStreamNonBlocking) == cudaSuccess;
   auto mk = [&](cudaEvent_t* e) { ok = ok && cudaEventCreateWithFlags(e, cudaEventDisableTiming) == cudaSuccess; };
-  mk(&p->ev_fork);
-  for (int i = 0; i < 2; ++i) { mk(&p->ev_kern[i]); mk(&p->ev_d2h[i]); }
-  for (int i = 0; i < assl_plan::kMaxChunks; ++i) { mk(&p->ev_in[i]); mk(&p->ev_out[i]); }
-  if (!ok) return ASSL_ERR_CUDA;
-  p->aux_ready = true;
+  mk(&pipe->ev_fork);
+  for (int i = 0; i < 2; ++i) { mk(&pipe->ev_kern[i]); mk(&pipe->ev_d2h[i]); }
+  for (int i = 0; i < assl_pipeline::kMaxChunks; ++i) { mk(&pipe->ev_in[i]); mk(&pipe->ev_out[i]); }
+  if (!ok) { assl_pipeline_destroy(pipe); cudaGetLastError(); return ASSL_ERR_CUDA; }
+  *out = pipe;
   return ASSL_OK;
 }
 
-}  // namespace
+extern "C" int assl_pipeline_destroy(assl_pipeline* pipe) {
+  if (!pipe) return ASSL_OK;
+  if (pipe->s_in) cudaStreamDestroy(pipe->s_in);
+  if (pipe->s_out) cudaStreamDestroy(pipe->s_out);
+  auto rm = [](cudaEvent_t e) { if (e) cudaEventDestroy(e); };
+  rm(pipe->ev_fork);
+  for (int i = 0; i < 2; ++i) { rm(pipe->ev_kern[i]); rm(pipe->ev_d2h[i]); }
+  for (int i = 0; i < assl_pipeline::kMaxChunks; ++i) { rm(pipe->ev_in[i]); rm(pipe->ev_out[i]); }
+  delete pipe;
+  return ASSL_OK;
+}
 
 extern "C" int64_t assl_pipeline_workspace_bytes(const assl_plan* p, int64_t B, int64_t L, int64_t cap) {
   if (!p || B < 1 || cap < B || L <= p->cfg.n_fft / 2) return -1;
   return static_cast<int64_t>(layout(p, B, L, cap).total);
 }
 
-extern "C" int assl_pipeline_host_sync(const assl_plan* p) {
-  if (!p) return ASSL_ERR_INVALID_ARG;
-  if (!p->aux_ready) return ASSL_OK;
-  bool ok = cudaStreamSynchronize(p->s_in) == cudaSuccess;
-  ok = cudaStreamSynchronize(p->s_out) == cudaSuccess && ok;
+extern "C" int assl_pipeline_host_sync(assl_pipeline* pipe) {
+  if (!pipe) return ASSL_ERR_INVALID_ARG;
+  bool ok = cudaStreamSynchronize(pipe->s_in) == cudaSuccess;
+  ok = cudaStreamSynchronize(pipe->s_out) == cudaSuccess && ok;
   return ok ? ASSL_OK : ASSL_ERR_CUDA;
 }
 
-extern "C" int assl_pipeline_host_f32(const assl_plan* p, const assl_view_cfg* vc, void* ws, int64_t ws_bytes,
+extern "C" int assl_pipeline_host_f32(assl_pipeline* pipe, const assl_view_cfg* vc, void* ws, int64_t ws_bytes,
                                       const float* host_wave, int64_t B, int64_t L, int64_t slot0, int64_t cap,
                                       int64_t max_update, const int32_t* host_mix_slot, const float* host_alpha,
                                       const int32_t* host_crop, float* host_view1, float* host_view2,
                                       float** dev_view1, float** dev_view2, void* stream) {
   using namespace assl;
-  if (!p || !vc || !ws || !host_wave || !host_mix_slot || !host_alpha || !host_crop) return ASSL_ERR_INVALID_ARG;
+  if (!pipe || !vc || !ws || !host_wave || !host_mix_slot || !host_alpha || !host_crop) return ASSL_ERR_INVALID_ARG;
+  const assl_plan* p = pipe->plan;
   if (B < 1 || cap < B || slot0 < 0 || slot0 >= cap || L <= p->cfg.n_fft / 2) return ASSL_ERR_INVALID_ARG;
   const int64_t T = 1 + L / p->cfg.hop;
   if (vc->n_freq != p->cfg.n_mels || vc->n_time != T) return ASSL_ERR_INVALID_ARG;
   const WsLayout w = layout(p, B, L, cap);
   if (static_cast<size_t>(ws_bytes) < w.total) return ASSL_ERR_INVALID_ARG;
-  int rc = ensure_aux(p);
-  if (rc != ASSL_OK) return rc;
-
+  int rc = ASSL_OK;
   cudaStream_t st = as_stream(stream);
-  const int par = static_cast<int>(p->calls & 1);
+  const int par = static_cast<int>(pipe->calls & 1);
   char* base = static_cast<char*>(ws);
   double* state = reinterpret_cast<double*>(base + w.state);
   float* stats = reinterpret_cast<float*>(base + w.stats_ring);
@@ -113,8 +141,9 @@ extern "C" int assl_pipeline_host_f32(const assl_plan* p, const assl_view_cfg* v
   // upload with call k's kernels and download, and whole-batch copies use the link better than quarter-batch ones
   // (measured on B200, 1024 x 1 s: 0.78 M clips/s with one chunk, 0.70 M with four).
   int n_chunks = B >= 256 ? 4 : (B >= 32 ? 2 : 1);
-  if (p->calls > 0 && cudaEventQuery(p->ev_d2h[par ^ 1]) == cudaErrorNotReady) n_chunks = 1;
-  if (const char* e = getenv("ASSL_PIPE_CHUNKS")) { const int v = atoi(e); if (v >= 1 && v <= assl_plan::kMaxChunks && v <= B) n_chunks = v; }
+  if (pipe->calls > 0 && cudaEventQuery(pipe->ev_d2h[par ^ 1]) == cudaErrorNotReady) n_chunks = 1;
+  if (pipe->exchange) n_chunks = 1;        // one exchange per call: every rank brings its whole batch to it
+  if (const char* e = getenv("ASSL_PIPE_CHUNKS")) { const int v = atoi(e); if (v >= 1 && v <= assl_pipeline::kMaxChunks && v <= B) n_chunks = v; }
 
   bool ok = true;
   auto cp = [&](void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t s) {
@@ -122,43 +151,45 @@ extern "C" int assl_pipeline_host_f32(const assl_plan* p, const assl_view_cfg* v
   };
   // order the uploads against whatever the caller queued on its stream before the first calls (its own
   // zero-fill of the workspace state ...), later against the kernels of the call that last used this parity
-  if (p->calls < 2) {
-    ok = ok && cudaEventRecord(p->ev_fork, st) == cudaSuccess;
-    ok = ok && cudaStreamWaitEvent(p->s_in, p->ev_fork, 0) == cudaSuccess;
+  if (pipe->calls < 2) {
+    ok = ok && cudaEventRecord(pipe->ev_fork, st) == cudaSuccess;
+    ok = ok && cudaStreamWaitEvent(pipe->s_in, pipe->ev_fork, 0) == cudaSuccess;
   } else {
-    ok = ok && cudaStreamWaitEvent(p->s_in, p->ev_kern[par], 0) == cudaSuccess;
+    ok = ok && cudaStreamWaitEvent(pipe->s_in, pipe->ev_kern[par], 0) == cudaSuccess;
   }
-  cp(mix_slot, host_mix_slot, static_cast<size_t>(B) * 2 * sizeof(int32_t), cudaMemcpyHostToDevice, p->s_in);
-  cp(alpha, host_alpha, static_cast<size_t>(B) * 2 * sizeof(float), cudaMemcpyHostToDevice, p->s_in);
-  cp(crop, host_crop, static_cast<size_t>(B) * 8 * sizeof(int32_t), cudaMemcpyHostToDevice, p->s_in);
+  cp(mix_slot, host_mix_slot, static_cast<size_t>(B) * 2 * sizeof(int32_t), cudaMemcpyHostToDevice, pipe->s_in);
+  cp(alpha, host_alpha, static_cast<size_t>(B) * 2 * sizeof(float), cudaMemcpyHostToDevice, pipe->s_in);
+  cp(crop, host_crop, static_cast<size_t>(B) * 8 * sizeof(int32_t), cudaMemcpyHostToDevice, pipe->s_in);
   iota_slots_kernel<<<static_cast<unsigned>((B + 255) / 256), 256, 0, st>>>(clip_slot, B, slot0, cap);
   // the view buffers of this parity were downloaded two calls ago; kernels that overwrite them wait for that
-  if (p->calls >= 2) ok = ok && cudaStreamWaitEvent(st, p->ev_d2h[par], 0) == cudaSuccess;
+  if (pipe->calls >= 2) ok = ok && cudaStreamWaitEvent(st, pipe->ev_d2h[par], 0) == cudaSuccess;
 
   for (int c = 0; c < n_chunks && ok && rc == ASSL_OK; ++c) {
     const int64_t b0 = B * c / n_chunks, b1 = B * (c + 1) / n_chunks, nb = b1 - b0;
     if (nb == 0) continue;
-    cp(wave + b0 * L, host_wave + b0 * L, static_cast<size_t>(nb) * L * sizeof(float), cudaMemcpyHostToDevice, p->s_in);
-    ok = ok && cudaEventRecord(p->ev_in[c], p->s_in) == cudaSuccess;
-    ok = ok && cudaStreamWaitEvent(st, p->ev_in[c], 0) == cudaSuccess;
+    cp(wave + b0 * L, host_wave + b0 * L, static_cast<size_t>(nb) * L * sizeof(float), cudaMemcpyHostToDevice, pipe->s_in);
+    ok = ok && cudaEventRecord(pipe->ev_in[c], pipe->s_in) == cudaSuccess;
+    ok = ok && cudaStreamWaitEvent(st, pipe->ev_in[c], 0) == cudaSuccess;
     const int64_t s0 = (slot0 + b0) % cap;
     rc = assl_logmel_f32(p, wave + b0 * L, nullptr, nb, L, L, lms, s0, cap, tsums + b0 * n_parts * 2, 0, stream);
-    if (rc == ASSL_OK)
+    if (rc == ASSL_OK && pipe->exchange)   // sharded run: this rank's clips + every peer's, in global clip order
+      rc = assl_running_stats_exchange(pipe->exchange, state, tsums, nb, n_parts, elems, max_update, stats, s0, cap, 0, stream);
+    else if (rc == ASSL_OK)
       rc = assl_running_stats(state, tsums + b0 * n_parts * 2, nb, n_parts, elems, max_update, 0, nb, stats, s0, cap, stream);
     if (rc == ASSL_OK)
       rc = assl_two_views_f32(vc, lms, stats, cap, clip_slot + b0, mix_slot + b0 * 2, alpha + b0 * 2, crop + b0 * 8, nb,
                               v1 + b0 * elems, v2 + b0 * elems, stream);
     if (rc == ASSL_OK && (host_view1 || host_view2)) {
-      ok = ok && cudaEventRecord(p->ev_out[c], st) == cudaSuccess;
-      ok = ok && cudaStreamWaitEvent(p->s_out, p->ev_out[c], 0) == cudaSuccess;
-      if (host_view1) cp(host_view1 + b0 * elems, v1 + b0 * elems, static_cast<size_t>(nb) * plane, cudaMemcpyDeviceToHost, p->s_out);
-      if (host_view2) cp(host_view2 + b0 * elems, v2 + b0 * elems, static_cast<size_t>(nb) * plane, cudaMemcpyDeviceToHost, p->s_out);
+      ok = ok && cudaEventRecord(pipe->ev_out[c], st) == cudaSuccess;
+      ok = ok && cudaStreamWaitEvent(pipe->s_out, pipe->ev_out[c], 0) == cudaSuccess;
+      if (host_view1) cp(host_view1 + b0 * elems, v1 + b0 * elems, static_cast<size_t>(nb) * plane, cudaMemcpyDeviceToHost, pipe->s_out);
+      if (host_view2) cp(host_view2 + b0 * elems, v2 + b0 * elems, static_cast<size_t>(nb) * plane, cudaMemcpyDeviceToHost, pipe->s_out);
     }
   }
   if (rc != ASSL_OK) return rc;
-  ok = ok && cudaEventRecord(p->ev_kern[par], st) == cudaSuccess;
-  ok = ok && cudaEventRecord(p->ev_d2h[par], p->s_out) == cudaSuccess;
-  p->calls += 1;
+  ok = ok && cudaEventRecord(pipe->ev_kern[par], st) == cudaSuccess;
+  ok = ok && cudaEventRecord(pipe->ev_d2h[par], pipe->s_out) == cudaSuccess;
+  pipe->calls += 1;
   if (dev_view1) *dev_view1 = v1;
   if (dev_view2) *dev_view2 = v2;
   return ok ? launch_status() : ASSL_ERR_CUDA;

@@ -50,6 +50,7 @@ extern "C" const char* assl_status_string(int status) {
     case ASSL_ERR_UNSUPPORTED: return "unsupported shape or configuration";
     case ASSL_ERR_CUDA: return "CUDA runtime error";
     case ASSL_ERR_NO_DEVICE: return "no CUDA device";
+    case ASSL_ERR_PEER_TIMEOUT: return "a peer's statistics records did not arrive in time";
     default: return "unknown status";
   }
 }
@@ -237,12 +238,17 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
     p->n_slots = n_slots;
     p->h_lane_iv = lane_iv;
   }
-  // per band {area normalisation enorm(m), 2.22e-16 * sum of the band's weights (the "+ eps" of utils.py:28, folded)}
-  std::vector<float2> mconst(n_mels);
+  // per band {where its rising edge U(m) and its falling edge D(m+1) sit among a warp's interval totals (byte offsets:
+  // entry pos[j] = 16 bytes {D(j), U(j)}, each a {frame 2q, frame 2q+1} pair), area normalisation enorm(m),
+  // 2.22e-16 * sum of the band's weights (the "+ eps" of utils.py:28, folded)}
+  std::vector<int4> band(n_mels);
   for (int m = 0; m < n_mels; ++m) {
     float acc = 0.f;
     for (int k = 0; k < n_bins; ++k) acc += p->h_fb[static_cast<size_t>(m) * n_bins + k] * assl::kPowerEps;
-    mconst[m] = make_float2(static_cast<float>(2.0 / (mel_f[m + 2] - mel_f[m])), acc);
+    const float enorm = static_cast<float>(2.0 / (mel_f[m + 2] - mel_f[m]));
+    int ie, ia;
+    std::memcpy(&ie, &enorm, 4); std::memcpy(&ia, &acc, 4);
+    band[m] = make_int4(16 * p->h_iv_pos[m] + 8, 16 * p->h_iv_pos[m + 1], ie, ia);
   }
 
   // ---- window: scipy get_window('hann', fftbins=True) = 0.5 - 0.5 cos(2 pi n / n_fft) needs no table; the
@@ -257,8 +263,8 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
 
   int rc = upload(&p->d_twiddle, tw);
   if (rc == ASSL_OK) rc = upload(&p->d_lane_iv, p->h_lane_iv);
-  if (rc == ASSL_OK) rc = upload(&p->d_iv_pos, p->h_iv_pos);
-  if (rc == ASSL_OK) rc = upload(&p->d_mel_const, mconst);
+  if (rc == ASSL_OK) rc = upload(&p->d_band, band);
+  if (rc == ASSL_OK) rc = upload(&p->d_tickets, std::vector<unsigned>(2 * assl_plan::kTicketSlots, 0u));
   if (rc != ASSL_OK) { assl_plan_destroy(p); return rc; }
   *out = p;
   return ASSL_OK;
@@ -268,14 +274,8 @@ extern "C" int assl_plan_destroy(assl_plan* p) {
   if (!p) return ASSL_OK;
   cudaFree(p->d_twiddle);
   cudaFree(p->d_lane_iv);
-  cudaFree(p->d_iv_pos);
-  cudaFree(p->d_mel_const);
-  if (p->aux_ready) {
-    cudaStreamDestroy(p->s_in); cudaStreamDestroy(p->s_out);
-    cudaEventDestroy(p->ev_fork);
-    for (int i = 0; i < 2; ++i) { cudaEventDestroy(p->ev_kern[i]); cudaEventDestroy(p->ev_d2h[i]); }
-    for (int i = 0; i < assl_plan::kMaxChunks; ++i) { cudaEventDestroy(p->ev_in[i]); cudaEventDestroy(p->ev_out[i]); }
-  }
+  cudaFree(p->d_band);
+  cudaFree(p->d_tickets);
   delete p;
   return ASSL_OK;
 }

@@ -70,19 +70,26 @@ __device__ inline void clip_total8(const double* sums, long long idx, long long 
   *sx = a; *sxx = b;
 }
 
-// Peer-memory exchange of the per-clip sums (assl_running_stats_exchange): where every rank's buffer of the
-// current parity is, as mapped into this process.  A record is 32 bytes per clip, written and read as 8-byte
-// words {32 bits of data, 32-bit call number} -- each word carries its own flag, so the receiver needs no fence
-// and no separate flag round trip: it polls the record until all four words show this call's number (the way
-// NCCL's LL protocol moves small messages).
-struct PeerArgs {
+// ---- exchange of the per-clip sums between the GPUs of a node (assl_exchange_send / assl_running_stats_exchange_scan /
+// assl_running_stats_exchange).  Every rank owns a buffer of ``world`` SEGMENTS (one per sender) per parity; a segment
+// is ``seg`` records of 32 bytes: record 0 = header {clips the sender brought this call}, records 1.. = per-clip
+// (sum x, sum x^2).  A record is written and read as 8-byte words {32 bits of data, 32-bit call number} -- each word
+// carries its own flag, so the receiver needs no fence and no separate flag round trip: it polls a record until all four
+// words show this call's number (the way NCCL's LL protocol moves small messages).  Ranks may bring different numbers
+// of clips (an uneven block split, a ragged last batch): the headers say how many.
+struct ExArgs {
   int world = 0;                 // 0 = single process, no exchange
   int rank = 0;
-  long long b_local = 0;         // clips of this rank (the same on every rank)
-  long long n_parts_local = 0;
-  const double* pair_sums = nullptr;                          // this rank's [b_local, n_parts_local, 2]
-  unsigned seq = 0;                                           // this call's number (never 0)
-  uint4* peer_rec[ASSL_EXCHANGE_MAX_WORLD] = {};              // rank j's records [world * b_local][2]
+  long long seg = 0;             // records per segment (max_clips + 1)
+  unsigned seq = 0;              // this call's number (never 0)
+  int n_dst = 0;                 // SEND: the buffers this rank's segment is stored into -- every rank's (peer transport:
+  uint4* dst[ASSL_EXCHANGE_MAX_WORLD] = {};   //  stores over NVLink) or only its own (staged: the caller all-gathers)
+  const uint4* src = nullptr;    // SCAN: this rank's buffer of the call's parity
+  int* host_err = nullptr;       // mapped host word, set when a peer's records did not arrive in time
+  unsigned long long timeout_ns = 0;
+  long long b_local = 0;         // SCAN: clips this rank brought to the call (known on the host since the send)
+  int write_all = 0;             // SCAN: (mean, std) of every clip of the global batch, not only this rank's
+  int deferred = 0;              // SCAN: does not wait for the grid before it at its start, but at its end
 };
 
 __device__ __forceinline__ void st_volatile_v4(uint4* p, uint4 v) {
@@ -93,6 +100,50 @@ __device__ __forceinline__ uint4 ld_volatile_v4(const uint4* p) {
   asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// one record = (a, b) as two flagged 16-byte words
+__device__ __forceinline__ void put_record(const ExArgs& x, long long index, double a, double b) {
+  const uint4 ra = make_uint4(__double2loint(a), x.seq, __double2hiint(a), x.seq);
+  const uint4 rb = make_uint4(__double2loint(b), x.seq, __double2hiint(b), x.seq);
+  for (int j = 0; j < x.n_dst; ++j) {
+    uint4* rec = x.dst[j] + 2 * (x.rank * x.seg + index);
+    st_volatile_v4(rec, ra);
+    st_volatile_v4(rec + 1, rb);
+  }
+}
+// wait until record ``index`` of sender ``from`` shows this call's number; false after timeout_ns
+__device__ __forceinline__ bool await_record(const ExArgs& x, int from, long long index, double* a, double* b) {
+  const uint4* rec = x.src + 2 * (from * x.seg + index);
+  unsigned long long t0 = 0;
+  for (unsigned spins = 0;; ++spins) {
+    const uint4 ra = ld_volatile_v4(rec), rb = ld_volatile_v4(rec + 1);
+    if (ra.y == x.seq && ra.w == x.seq && rb.y == x.seq && rb.w == x.seq) {
+      *a = __hiloint2double(ra.z, ra.x); *b = __hiloint2double(rb.z, rb.x);
+      return true;
+    }
+    if (spins == 64) t0 = global_ns();               // (the common case never reads the timer)
+    if (spins > 64) {
+      if (global_ns() - t0 > x.timeout_ns) return false;
+      __nanosleep(256);
+    }
+  }
+}
+
+// Sending side on its own (assl_exchange_send): totals of this rank's clips -> its segment in every destination buffer.
+// Issued right behind the log-mel kernel; nobody waits here.
+__global__ void __launch_bounds__(256) stats_send_kernel(const ExArgs x, const double* pair_sums, long long b, long long n_parts) {
+  pdl_launch_dependents();
+  pdl_wait();                                        // the log-mel kernel's per-pair sums are complete and visible
+  const long long idx = blockIdx.x * 32ll + (threadIdx.x >> 3);          // 8 lanes per clip
+  double sx, sxx;
+  clip_total8(pair_sums, idx, b, n_parts, threadIdx.x & 7, &sx, &sxx);
+  if ((threadIdx.x & 7) == 0 && idx < b) put_record(x, 1 + idx, sx, sxx);
+  if (blockIdx.x == 0 && threadIdx.x == 0) put_record(x, 0, static_cast<double>(b), 0.0);
+}
 
 // state: [0] n_put  [1] sum of m_j (j>=1)  [2] sum of v_j (j>=1)  [3] mean  [4] std  [5..6] reserved  [7] exchange error
 //
@@ -100,15 +151,18 @@ __device__ __forceinline__ uint4 ld_volatile_v4(const uint4* p) {
 // chunk of 1024 per CTA:
 //   1. per-clip (m, q) = (sum x, sum x^2) / elems of every chunk land in the owning CTA's shared memory -- for
 //      per-pair sums all CTAs reduce 128 clips of each chunk and hand the result over through DSMEM (that read is
-//      the bulk of the bytes and a single SM cannot keep enough of it in flight); gathered per-clip sums
-//      (n_parts = 1) are simply loaded by the owner;
+//      the bulk of the bytes and a single SM cannot keep enough of it in flight); per-clip sums (n_parts = 1, or the
+//      records of an exchange) are simply loaded by the owner;
 //   2. every CTA scans its chunk, the chunk totals are exchanged through DSMEM and added in chunk order, so the
 //      result is bit-identical to a sequential walk over the chunks while a global batch of 8 GPUs x 1024 clips
 //      costs the time of one chunk.
+// With an exchange (x.world > 0) the clips are the records in this rank's buffer, sender after sender (= global clip
+// order of a contiguous block split); ``send_sums`` != null: this rank's own records are produced and sent here first
+// (the fused form, assl_running_stats_exchange).  n_clips / first / count then come from the headers.
 __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads) running_stats_kernel(
     double* state, const double* sums, long long n_clips, long long n_parts, double inv_elems,
     long long max_update, long long first, long long count, float* mean_std, long long slot0, long long cap,
-    const PeerArgs px) {
+    const ExArgs x, const double* send_sums, long long send_b, long long send_parts) {
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned rank = cluster.block_rank();
@@ -116,32 +170,77 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
   __shared__ double s_m[kScanThreads], s_q[kScanThreads];
   __shared__ double s_tot[2][kStatCtas];           // chunk totals of m / of v, a full copy in every CTA
   __shared__ float s_frozen[2];
+  __shared__ long long s_off[ASSL_EXCHANGE_MAX_WORLD + 1];   // first global clip of every sender
+  __shared__ int s_late, s_late_all[kStatCtas];
   const int tid = threadIdx.x;
   pdl_launch_dependents();                           // (the two-view kernel's CTAs wait for this grid to complete)
-  pdl_wait();                                        // the log-mel kernel's per-pair sums are complete and visible
+  if (!x.deferred) pdl_wait();                       // the log-mel kernel's per-pair sums are complete and visible
   const long long n0 = static_cast<long long>(state[0]);
   double carry_m = state[1], carry_v = state[2];
-  if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); }
+  if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); s_late = 0; }
 
-  __shared__ int s_late;
-  if (tid == 0) s_late = 0;
-  if (px.world > 0) {
-    // ---- exchange, sending side: totals of this rank's clips -> the records [rank * b_local, ...) of EVERY rank's
-    //      buffer (stores over NVLink for the peers; the local copy goes the same way)
-    for (long long base = 0; base < px.b_local; base += kScanThreads) {
-      const long long idx = base + rank * (kScanThreads / 8) + (tid >> 3);
-      double sx, sxx;
-      clip_total8(px.pair_sums, idx, px.b_local, px.n_parts_local, tid & 7, &sx, &sxx);
-      if ((tid & 7) == 0 && idx < px.b_local) {
-        const uint4 ra = make_uint4(__double2loint(sx), px.seq, __double2hiint(sx), px.seq);
-        const uint4 rb = make_uint4(__double2loint(sxx), px.seq, __double2hiint(sxx), px.seq);
-        for (int j = 0; j < px.world; ++j) {
-          uint4* rec = px.peer_rec[j] + 2 * (px.rank * px.b_local + idx);
-          st_volatile_v4(rec, ra);
-          st_volatile_v4(rec + 1, rb);
-        }
+  if (x.world > 0) {
+    if (send_sums) {
+      // ---- fused form, sending side: totals of this rank's clips -> its segment in EVERY rank's buffer
+      //      (stores over NVLink for the peers; the local copy goes the same way)
+      for (long long base = 0; base < send_b; base += kScanThreads) {
+        const long long idx = base + rank * (kScanThreads / 8) + (tid >> 3);
+        double sx, sxx;
+        clip_total8(send_sums, idx, send_b, send_parts, tid & 7, &sx, &sxx);
+        if ((tid & 7) == 0 && idx < send_b) put_record(x, 1 + idx, sx, sxx);
+      }
+      if (rank == 0 && tid == 0) put_record(x, 0, static_cast<double>(send_b), 0.0);
+    }
+    // ---- receiving side.  Headers first: how many clips every sender brought
+    __syncthreads();
+    if (tid < x.world) {
+      double c = 0.0, unused;
+      const bool ok = await_record(x, tid, 0, &c, &unused);
+      const long long cnt = static_cast<long long>(c);
+      if (!ok || cnt < 0 || cnt >= x.seg) { s_late = 1; s_off[tid + 1] = 0; } else s_off[tid + 1] = cnt;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      s_off[0] = 0;
+      for (int j = 0; j < x.world; ++j) s_off[j + 1] += s_off[j];
+    }
+    __syncthreads();
+    n_clips = s_off[x.world];
+    first = x.write_all ? 0 : s_off[x.rank];
+    count = x.write_all ? n_clips : s_off[x.rank + 1] - s_off[x.rank];
+    // then every record of the call has to be here before any of them is consumed: a peer that does not show up must
+    // leave the running statistics untouched, not half updated
+    if (!s_late) {
+      for (long long idx = rank * kScanThreads + tid; idx < n_clips; idx += static_cast<long long>(kStatCtas) * kScanThreads) {
+        int j = 0;
+        while (j + 1 < x.world && idx >= s_off[j + 1]) ++j;
+        double u0, u1;
+        if (!await_record(x, j, 1 + idx - s_off[j], &u0, &u1)) { s_late = 1; break; }
       }
     }
+    __syncthreads();
+    if (tid < kStatCtas) cluster.map_shared_rank(&s_late_all[0], tid)[rank] = s_late;
+    cluster.sync();
+    int late = 0;
+    for (int c = 0; c < kStatCtas; ++c) late |= s_late_all[c];
+    if (late) {
+      // a peer's records did not arrive within the timeout (or a header is garbage): the statistics stay as they were,
+      // this rank's clips get the last published (mean, std), the error flag goes up (assl_exchange_error)
+      const long long mine = x.write_all ? 0 : x.b_local;
+      const bool any = n0 > 0;
+      for (long long i = rank * kScanThreads + tid; i < mine; i += static_cast<long long>(kStatCtas) * kScanThreads) {
+        const long long s = ring_slot(slot0, i, cap);
+        mean_std[2 * s] = any ? s_frozen[0] : 0.f;
+        mean_std[2 * s + 1] = any ? s_frozen[1] : 1.f;
+      }
+      if (rank == 0 && tid == 0) {
+        state[7] = 1.0;
+        if (x.host_err) { *reinterpret_cast<volatile int*>(x.host_err) = 1; __threadfence_system(); }
+      }
+      if (x.deferred) pdl_wait();
+      return;
+    }
+    n_parts = 1;
   }
 
   for (long long sbase = 0; sbase < n_clips; sbase += static_cast<long long>(kStatCtas) * kScanThreads) {
@@ -150,17 +249,12 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
                                               ? kStatCtas : (left + kScanThreads - 1) / kScanThreads);
     if (n_parts == 1) {                              // per-clip sums: the owner loads its chunk
       const long long idx = sbase + rank * kScanThreads + tid;
-      if (idx < n_clips && px.world > 0) {           // receiving side: poll this clip's record until it is this call's
-        const uint4* rec = px.peer_rec[px.rank] + 2 * idx;
-        const long long t0 = clock64();
-        uint4 ra, rb;
-        while (true) {
-          ra = ld_volatile_v4(rec); rb = ld_volatile_v4(rec + 1);
-          if (ra.y == px.seq && ra.w == px.seq && rb.y == px.seq && rb.w == px.seq) break;
-          if (clock64() - t0 > 4000000000ll) { s_late = 1; break; }   // ~2 s: a peer is gone; do not hang the GPU
-          __nanosleep(64);
-        }
-        s_m[tid] = __hiloint2double(ra.z, ra.x) * inv_elems; s_q[tid] = __hiloint2double(rb.z, rb.x) * inv_elems;
+      if (idx < n_clips && x.world > 0) {            // this call's records (all of them are known to have arrived)
+        int j = 0;
+        while (j + 1 < x.world && idx >= s_off[j + 1]) ++j;
+        double sx, sxx;
+        await_record(x, j, 1 + idx - s_off[j], &sx, &sxx);
+        s_m[tid] = sx * inv_elems; s_q[tid] = sxx * inv_elems;
       } else if (idx < n_clips) {
         const double2 v = reinterpret_cast<const double2*>(sums)[idx];
         s_m[tid] = v.x * inv_elems; s_q[tid] = v.y * inv_elems;
@@ -232,7 +326,6 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
       mean_std[2 * s + 1] = my_std;
     }
   }
-  if (tid == 0 && s_late) state[7] = 1.0;           // (CTAs that left early saw their records arrive)
   if (rank == 0 && tid == 0) {
     long long n1 = n0;
     if (n0 < max_update) n1 = (n0 + n_clips < max_update) ? n0 + n_clips : max_update;
@@ -240,6 +333,9 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
     state[1] = carry_m;
     state[2] = carry_v;
   }
+  // deferred launch: this grid ran beside the one launched before it; whoever waits for THIS grid to complete (the
+  // next kernel's pdl_wait) must also get that one's completion
+  if (x.deferred) pdl_wait();
 }
 
 __global__ void __launch_bounds__(256) clip_sums_kernel(const double* tile_sums, long long B, long long n_parts, double* clip_sums) {
@@ -336,7 +432,8 @@ extern "C" int assl_running_stats(double* state, const double* sums, int64_t n_c
   if (launch_pdl(running_stats_kernel, dim3(kStatCtas), dim3(kScanThreads), 0, as_stream(stream), state, sums,
                  static_cast<long long>(n_clips), static_cast<long long>(n_parts), 1.0 / static_cast<double>(elems),
                  static_cast<long long>(max_update), static_cast<long long>(first), static_cast<long long>(count), mean_std,
-                 static_cast<long long>(slot0), static_cast<long long>(cap), PeerArgs()) != cudaSuccess)
+                 static_cast<long long>(slot0), static_cast<long long>(cap), ExArgs(), static_cast<const double*>(nullptr),
+                 0ll, 0ll) != cudaSuccess)
     return ASSL_ERR_CUDA;
   return launch_status();
 }
@@ -388,16 +485,38 @@ extern "C" int assl_affine_norm_f32(const float* x, float* y, int64_t n, float m
   return assl::launch_status();
 }
 
-// ---- peer-memory exchange object -------------------------------------------------------------------------
+// ---- exchange object -------------------------------------------------------------------------------------
 struct assl_exchange {
   int rank = 0, world = 0;
-  long long max_clips = 0;
+  long long max_clips = 0, seg = 0;                       // seg = max_clips + 1 records per sender (record 0 = header)
   unsigned char* local = nullptr;                         // this rank's buffer (cudaMalloc: IPC-exportable)
   unsigned char* peer[ASSL_EXCHANGE_MAX_WORLD] = {};       // every rank's buffer as mapped here (peer[rank] = local)
-  size_t rec_bytes = 0, bytes = 0;                        // per parity: [world * max_clips] records of 32 bytes
-  unsigned long long seq = 0;
-  bool connected = false;
+  size_t rec_bytes = 0, bytes = 0;                        // per parity: world segments of seg records of 32 bytes
+  unsigned long long sent = 0, scanned = 0;               // calls sent / scanned so far (sent - scanned is 0 or 1)
+  long long sent_b[2] = {0, 0};                           // clips this rank brought to the call of either parity
+  bool connected = false, staged = false;
+  int* h_err = nullptr;                                   // mapped host word the scan kernel sets on a timeout
+  int* d_err = nullptr;
+  unsigned long long timeout_ns = 30000000000ull;         // 30 s: of the order of a collective watchdog, not of a step
 };
+
+namespace {
+unsigned seq_word(unsigned long long call) { return static_cast<unsigned>(call & 0x7fffffffu) | 0x80000000u; }   // never 0
+
+assl::ExArgs send_args(const assl_exchange* x, unsigned long long call) {
+  assl::ExArgs a;
+  a.world = x->world; a.rank = x->rank; a.seg = x->seg; a.seq = seq_word(call);
+  const size_t off = static_cast<size_t>(call & 1) * x->rec_bytes;
+  if (x->staged) { a.n_dst = 1; a.dst[0] = reinterpret_cast<uint4*>(x->local + off); }
+  else { a.n_dst = x->world; for (int r = 0; r < x->world; ++r) a.dst[r] = reinterpret_cast<uint4*>(x->peer[r] + off); }
+  return a;
+}
+void scan_args(const assl_exchange* x, unsigned long long call, assl::ExArgs* a) {
+  a->world = x->world; a->rank = x->rank; a->seg = x->seg; a->seq = seq_word(call);
+  a->src = reinterpret_cast<const uint4*>(x->local + static_cast<size_t>(call & 1) * x->rec_bytes);
+  a->host_err = x->d_err; a->timeout_ns = x->timeout_ns; a->b_local = x->sent_b[call & 1];
+}
+}  // namespace
 
 extern "C" int assl_exchange_create(assl_exchange** out, int32_t rank, int32_t world, int64_t max_clips, void* handle_out) {
   if (!out || !handle_out || world < 2 || world > ASSL_EXCHANGE_MAX_WORLD || rank < 0 || rank >= world || max_clips < 1)
@@ -406,13 +525,16 @@ extern "C" int assl_exchange_create(assl_exchange** out, int32_t rank, int32_t w
   *out = nullptr;
   assl_exchange* x = new (std::nothrow) assl_exchange();
   if (!x) return ASSL_ERR_CUDA;
-  x->rank = rank; x->world = world; x->max_clips = max_clips;
-  x->rec_bytes = (32 * static_cast<size_t>(world) * max_clips + 255) & ~static_cast<size_t>(255);
+  x->rank = rank; x->world = world; x->max_clips = max_clips; x->seg = max_clips + 1;
+  x->rec_bytes = (32 * static_cast<size_t>(world) * x->seg + 255) & ~static_cast<size_t>(255);
   x->bytes = 2 * x->rec_bytes;
   cudaIpcMemHandle_t h;
-  if (cudaMalloc(reinterpret_cast<void**>(&x->local), x->bytes) != cudaSuccess || cudaMemset(x->local, 0, x->bytes) != cudaSuccess ||
-      cudaIpcGetMemHandle(&h, x->local) != cudaSuccess) {
-    cudaFree(x->local); delete x; cudaGetLastError();
+  bool ok = cudaMalloc(reinterpret_cast<void**>(&x->local), x->bytes) == cudaSuccess && cudaMemset(x->local, 0, x->bytes) == cudaSuccess &&
+            cudaIpcGetMemHandle(&h, x->local) == cudaSuccess;
+  ok = ok && cudaHostAlloc(reinterpret_cast<void**>(&x->h_err), sizeof(int), cudaHostAllocMapped) == cudaSuccess;
+  if (ok) { *x->h_err = 0; ok = cudaHostGetDevicePointer(reinterpret_cast<void**>(&x->d_err), x->h_err, 0) == cudaSuccess; }
+  if (!ok) {
+    cudaFree(x->local); if (x->h_err) cudaFreeHost(x->h_err); delete x; cudaGetLastError();
     return ASSL_ERR_CUDA;
   }
   std::memcpy(handle_out, &h, sizeof(h));
@@ -422,51 +544,117 @@ extern "C" int assl_exchange_create(assl_exchange** out, int32_t rank, int32_t w
 }
 
 extern "C" int assl_exchange_connect(assl_exchange* x, const void* all_handles) {
-  if (!x || !all_handles) return ASSL_ERR_INVALID_ARG;
+  if (!x || !all_handles || x->staged) return ASSL_ERR_INVALID_ARG;
   if (x->connected) return ASSL_OK;
   for (int r = 0; r < x->world; ++r) {
     if (r == x->rank) continue;
     cudaIpcMemHandle_t h;
     std::memcpy(&h, static_cast<const unsigned char*>(all_handles) + static_cast<size_t>(r) * sizeof(h), sizeof(h));
     void* p = nullptr;
-    if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); return ASSL_ERR_CUDA; }
+    if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      cudaGetLastError();
+      for (int q = 0; q < r; ++q)
+        if (q != x->rank && x->peer[q]) { cudaIpcCloseMemHandle(x->peer[q]); x->peer[q] = nullptr; }
+      return ASSL_ERR_CUDA;
+    }
     x->peer[r] = static_cast<unsigned char*>(p);
   }
   x->connected = true;
   return ASSL_OK;
 }
 
+extern "C" int assl_exchange_use_staging(assl_exchange* x) {
+  if (!x || (x->connected && !x->staged)) return ASSL_ERR_INVALID_ARG;
+  x->staged = true; x->connected = true;
+  return ASSL_OK;
+}
+
+extern "C" int assl_exchange_staging(const assl_exchange* x, int64_t back, void** buffer, int64_t* segment_bytes) {
+  if (!x || !buffer || !segment_bytes || back < 0 || back > 1 || x->sent == 0) return ASSL_ERR_INVALID_ARG;
+  const unsigned long long call = x->sent - static_cast<unsigned long long>(back);
+  if (call == 0) return ASSL_ERR_INVALID_ARG;
+  *buffer = x->local + static_cast<size_t>(call & 1) * x->rec_bytes;
+  *segment_bytes = static_cast<int64_t>(32 * x->seg);
+  return ASSL_OK;
+}
+
+extern "C" int assl_exchange_set_timeout(assl_exchange* x, double seconds) {
+  if (!x || !(seconds > 0.0)) return ASSL_ERR_INVALID_ARG;
+  x->timeout_ns = static_cast<unsigned long long>(seconds * 1e9);
+  return ASSL_OK;
+}
+
+extern "C" int assl_exchange_error(const assl_exchange* x) {
+  if (!x) return ASSL_ERR_INVALID_ARG;
+  return *reinterpret_cast<volatile int*>(x->h_err) ? ASSL_ERR_PEER_TIMEOUT : ASSL_OK;
+}
+
 extern "C" int assl_exchange_destroy(assl_exchange* x) {
   if (!x) return ASSL_OK;
-  for (int r = 0; r < x->world; ++r)
-    if (r != x->rank && x->peer[r]) cudaIpcCloseMemHandle(x->peer[r]);
+  if (!x->staged)
+    for (int r = 0; r < x->world; ++r)
+      if (r != x->rank && x->peer[r]) cudaIpcCloseMemHandle(x->peer[r]);
   cudaFree(x->local);
+  if (x->h_err) cudaFreeHost(x->h_err);
   delete x;
   return ASSL_OK;
+}
+
+extern "C" int assl_exchange_send(assl_exchange* x, const double* pair_sums, int64_t B, int64_t n_parts, void* stream) {
+  using namespace assl;
+  if (!x || !x->connected || (!pair_sums && B > 0) || B < 0 || B > x->max_clips || n_parts < 1) return ASSL_ERR_INVALID_ARG;
+  if (reinterpret_cast<uintptr_t>(pair_sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;
+  if (x->sent != x->scanned) return ASSL_ERR_INVALID_ARG;              // the previous call has to be scanned first (two parities)
+  const unsigned long long call = x->sent + 1;
+  const ExArgs a = send_args(x, call);
+  const unsigned grid = static_cast<unsigned>(B > 0 ? (B + 31) / 32 : 1);
+  if (launch_pdl(stats_send_kernel, dim3(grid), dim3(256), 0, as_stream(stream), a, pair_sums, static_cast<long long>(B),
+                 static_cast<long long>(n_parts)) != cudaSuccess)
+    return ASSL_ERR_CUDA;
+  x->sent = call; x->sent_b[call & 1] = B;
+  return launch_status();
+}
+
+static int exchange_scan(assl_exchange* x, double* state, int64_t elems, int64_t max_update, float* mean_std, int64_t slot0,
+                         int64_t cap, int32_t write_all, int32_t deferred, const double* send_sums, int64_t send_b,
+                         int64_t send_parts, void* stream) {
+  using namespace assl;
+  const unsigned long long call = x->scanned + 1;
+  ExArgs a = send_sums ? send_args(x, call) : ExArgs();
+  scan_args(x, call, &a);
+  a.write_all = write_all ? 1 : 0; a.deferred = deferred ? 1 : 0;
+  if (launch_pdl(running_stats_kernel, dim3(kStatCtas), dim3(kScanThreads), 0, as_stream(stream), state,
+                 static_cast<const double*>(nullptr), 0ll, 1ll, 1.0 / static_cast<double>(elems), static_cast<long long>(max_update),
+                 0ll, 0ll, mean_std, static_cast<long long>(slot0), static_cast<long long>(cap), a, send_sums,
+                 static_cast<long long>(send_b), static_cast<long long>(send_parts)) != cudaSuccess)
+    return ASSL_ERR_CUDA;
+  x->scanned = call;
+  return launch_status();
+}
+
+extern "C" int assl_running_stats_exchange_scan(assl_exchange* x, double* state, int64_t elems, int64_t max_update,
+                                                float* mean_std, int64_t slot0, int64_t cap, int32_t write_all,
+                                                int32_t deferred, void* stream) {
+  if (!x || !x->connected || !state || !mean_std || elems < 1 || max_update < 1 || slot0 < 0 || cap < 0) return ASSL_ERR_INVALID_ARG;
+  if (x->scanned >= x->sent) return ASSL_ERR_INVALID_ARG;              // nothing sent that has not been scanned
+  const long long b = x->sent_b[(x->scanned + 1) & 1];
+  if (cap > 0 && ((write_all ? static_cast<long long>(x->world) * b : b) > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
+  return exchange_scan(x, state, elems, max_update, mean_std, slot0, cap, write_all, deferred, nullptr, 0, 0, stream);
 }
 
 extern "C" int assl_running_stats_exchange(assl_exchange* x, double* state, const double* pair_sums, int64_t B,
                                            int64_t n_parts, int64_t elems, int64_t max_update, float* mean_std,
                                            int64_t slot0, int64_t cap, int32_t write_all, void* stream) {
-  using namespace assl;
-  if (!x || !x->connected || !state || !pair_sums || !mean_std || B < 1 || B > x->max_clips || n_parts < 1 || elems < 1 ||
-      max_update < 1 || slot0 < 0 || cap < 0)
+  if (!x || !x->connected || x->staged || !state || !pair_sums || !mean_std || B < 1 || B > x->max_clips || n_parts < 1 ||
+      elems < 1 || max_update < 1 || slot0 < 0 || cap < 0)
     return ASSL_ERR_INVALID_ARG;
-  const long long n_all = static_cast<long long>(x->world) * B;
-  if (cap > 0 && ((write_all ? n_all : B) > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
+  if (x->sent != x->scanned) return ASSL_ERR_INVALID_ARG;              // a split send is still waiting for its scan
+  if (cap > 0 && ((write_all ? static_cast<long long>(x->world) * B : B) > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
   if (reinterpret_cast<uintptr_t>(pair_sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;
-  PeerArgs px;
-  px.world = x->world; px.rank = x->rank; px.b_local = B; px.n_parts_local = n_parts; px.pair_sums = pair_sums;
-  ++x->seq;
-  px.seq = static_cast<unsigned>(x->seq & 0x7fffffffu) | 0x80000000u;       // never 0 (the buffer starts zeroed)
-  const size_t parity = static_cast<size_t>(x->seq & 1);
-  for (int r = 0; r < x->world; ++r) px.peer_rec[r] = reinterpret_cast<uint4*>(x->peer[r] + parity * x->rec_bytes);
-  if (launch_pdl(running_stats_kernel, dim3(kStatCtas), dim3(kScanThreads), 0, as_stream(stream), state, pair_sums, n_all,
-                 1ll, 1.0 / static_cast<double>(elems), static_cast<long long>(max_update),
-                 write_all ? 0ll : static_cast<long long>(x->rank) * B, write_all ? n_all : static_cast<long long>(B), mean_std,
-                 static_cast<long long>(slot0), static_cast<long long>(cap), px) != cudaSuccess)
-    return ASSL_ERR_CUDA;
-  return launch_status();
+  x->sent_b[(x->sent + 1) & 1] = B;
+  const int rc = exchange_scan(x, state, elems, max_update, mean_std, slot0, cap, write_all, 0, pair_sums, B, n_parts, stream);
+  if (rc == ASSL_OK) x->sent += 1;
+  return rc;
 }
 
 // ---- IPC-exportable buffers (the log-mel ring of the global-bank mode)

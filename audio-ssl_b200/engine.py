@@ -9,8 +9,8 @@
   * the running-norm state (8 doubles) of ``RunningNorm`` (augmentations.py:259-282).
 
 One process per GPU; with ``torch.distributed`` initialised and ``sync_stats=True`` the per-clip
-(sum, sum of squares) pairs are all-gathered (rank-major = global clip order) so every rank runs the
-identical statistics scan; the bank stays rank-local, as each reference worker's does.
+(sum, sum of squares) pairs are exchanged (rank-major = global clip order; over peer memory, see ``StatsExchange``) so
+every rank runs the identical statistics scan; the bank stays rank-local, as each reference worker's does.
 """
 from __future__ import annotations
 
@@ -65,41 +65,97 @@ def gather_clip_sums(local):
     return gathered
 
 
-class StatsExchange:
-    """Per-clip sums across the GPUs of one node through peer memory (``assl_running_stats_exchange``): one kernel
-    per rank instead of reduce + NCCL all-gather + scan.  ``torch.distributed`` only carries the 64-byte IPC
-    handles once.  ``StatsExchange.open`` returns None when the devices cannot map each other's memory (no P2P,
-    more than one node) or ``ASSL_STATS_EXCHANGE=nccl`` is set: the caller keeps the all-gather path."""
+class _RawBytes:
+    """A device buffer of the C library as a uint8 ``__cuda_array_interface__`` object (torch.as_tensor wraps it)."""
 
-    def __init__(self, handle, rank, world, max_clips):
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False),
+                                         "version": 3, "strides": None}
+
+
+class StatsExchange:
+    """Per-clip sums across the GPUs of one node (``assl_exchange_*``): every rank stores flagged records straight into
+    every peer's buffer over NVLink and scans its own buffer -- one kernel (``run``: send + scan fused) or two
+    (``send`` right behind the log-mel kernel, ``scan`` one step later, when the records have long landed: the
+    lookahead order).  ``torch.distributed`` only carries the 64-byte IPC handles once.  When the devices cannot map
+    each other's memory (no P2P, more than one node) or ``ASSL_STATS_EXCHANGE=nccl`` is set, the same kernels run with
+    the STAGED transport: a rank writes its segment into its own buffer and an all-gather moves the segments.  Ranks
+    may bring different numbers of clips to a call (the records carry a header)."""
+
+    def __init__(self, handle, rank, world, max_clips, staged, device):
         self.handle, self.rank, self.world, self.max_clips = handle, rank, world, max_clips
+        self.staged, self.device = staged, device
 
     @classmethod
     def open(cls, max_clips, device):
         import os
         import torch.distributed as dist
         rank, world = _dist_world()
-        if world < 2 or world > 16 or os.environ.get("ASSL_STATS_EXCHANGE", "peer") == "nccl":
+        if world < 2 or world > 16:
             return None
         lib = _native.lib()
+        want_peer = os.environ.get("ASSL_STATS_EXCHANGE", "peer") != "nccl"
         mine = (C.c_ubyte * 64)()
         handle = C.c_void_p()
-        ok = lib.assl_exchange_create(C.byref(handle), rank, world, int(max_clips), mine) == 0
-        local = torch.tensor(list(mine) if ok else [0] * 64, dtype=torch.uint8, device=device)
+        _native.check(lib.assl_exchange_create(C.byref(handle), rank, world, int(max_clips), mine), "assl_exchange_create")
+        local = torch.tensor(list(mine), dtype=torch.uint8, device=device)
         everyone = torch.empty(world * 64, dtype=torch.uint8, device=device)
         dist.all_gather_into_tensor(everyone, local)
         raw = bytes(everyone.cpu().tolist())
-        if ok:
-            ok = lib.assl_exchange_connect(handle, raw) == 0
+        ok = want_peer and lib.assl_exchange_connect(handle, raw) == 0
         agree = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device)
-        dist.all_reduce(agree, op=dist.ReduceOp.MIN)               # all ranks take the same path
-        if int(agree.item()) == 0:
-            if handle:
+        dist.all_reduce(agree, op=dist.ReduceOp.MIN)               # all ranks take the same transport
+        staged = int(agree.item()) == 0
+        if staged:
+            if ok:                                                  # some other rank could not map: start over, staged
                 lib.assl_exchange_destroy(handle)
-            return None
-        return cls(handle, rank, world, int(max_clips))
+                handle = C.c_void_p()
+                _native.check(lib.assl_exchange_create(C.byref(handle), rank, world, int(max_clips), mine))
+            _native.check(lib.assl_exchange_use_staging(handle), "assl_exchange_use_staging")
+        secs = os.environ.get("ASSL_EXCHANGE_TIMEOUT_S")
+        ex = cls(handle, rank, world, int(max_clips), staged, device)
+        if secs:
+            ex.set_timeout(float(secs))
+        return ex
+
+    def set_timeout(self, seconds):
+        _native.check(_native.lib().assl_exchange_set_timeout(self.handle, float(seconds)), "assl_exchange_set_timeout")
+
+    def check(self):
+        """Raise once a scan gave up waiting for a peer (reads a host word the kernel sets: no synchronisation)."""
+        if self.handle and _native.lib().assl_exchange_error(self.handle) != 0:
+            raise RuntimeError("statistics exchange: a peer's records did not arrive within the timeout; the running "
+                               "statistics of this rank were left untouched by that step and no longer agree with the "
+                               "other ranks' (assl_exchange_error)")
+
+    def _gather(self):
+        """Staged transport: all-gather the segments of the call sent last into this rank's buffer."""
+        import torch.distributed as dist
+        buf, seg = C.c_void_p(), C.c_int64()
+        _native.check(_native.lib().assl_exchange_staging(self.handle, 0, C.byref(buf), C.byref(seg)), "assl_exchange_staging")
+        whole = torch.as_tensor(_RawBytes(buf.value, seg.value * self.world), device=self.device)
+        mine = whole[self.rank * seg.value:(self.rank + 1) * seg.value].clone()
+        dist.all_gather_into_tensor(whole, mine)
+        self._keep = mine
+
+    def send(self, sums, b, n_parts):
+        self.check()
+        _native.check(_native.lib().assl_exchange_send(self.handle, _ptr(sums), b, n_parts, _stream_ptr()), "assl_exchange_send")
+        if self.staged:
+            self._gather()
+
+    def scan(self, state, elems, max_update, stats, slot0, cap, write_all=False, deferred=False):
+        _native.check(_native.lib().assl_running_stats_exchange_scan(
+            self.handle, _ptr(state), elems, int(max_update), _ptr(stats), slot0, cap, 1 if write_all else 0,
+            1 if deferred else 0, _stream_ptr()), "assl_running_stats_exchange_scan")
 
     def run(self, state, sums, b, n_parts, elems, max_update, stats, slot0, cap, write_all=False):
+        """Send + scan of one call: ONE kernel over peer memory; send, all-gather, scan with the staged transport."""
+        self.check()
+        if self.staged:
+            self.send(sums, b, n_parts)
+            self.scan(state, elems, max_update, stats, slot0, cap, write_all)
+            return
         _native.check(_native.lib().assl_running_stats_exchange(
             self.handle, _ptr(state), _ptr(sums), b, n_parts, elems, int(max_update), _ptr(stats), slot0, cap,
             1 if write_all else 0, _stream_ptr()), "assl_running_stats_exchange")
@@ -219,36 +275,61 @@ class ViewEngine:
             self.ring[:b - first].copy_(x[first:])
 
     # ------------------------------------------------------------------ statistics
+    def exchange(self, device):
+        """The statistics exchange of a clip-sharded run (opened on first use), or None for one process / sync_stats=False."""
+        world = _dist_world()[1]
+        if world > 1 and self.sync_stats and self._exchange is False:
+            self._exchange = StatsExchange.open(self.max_batch, device)
+        return self._exchange if (world > 1 and self.sync_stats) else None
+
+    @property
+    def split_stats(self):
+        """Lookahead order across GPUs: the sums of batch k are SENT right behind its log-mel kernel and SCANNED one step
+        later (just before the views that need them), so no rank waits for the slowest one inside a step."""
+        return self.lookahead and self.normalize and self.sync_stats and _dist_world()[1] > 1
+
     def update_stats(self, sums, n_parts):
-        """sums: [B, n_parts, 2] fp64 on device for this rank's clips, in order."""
+        """sums: [B, n_parts, 2] fp64 on device for this rank's clips, in order: statistics of the batch at the ring head."""
         lib = _native.lib()
         b = sums.shape[0]
-        rank, world = _dist_world()
         elems = self.f * self.t
-        if world > 1 and self.sync_stats and self._exchange is False:
-            self._exchange = StatsExchange.open(self.max_batch, sums.device)
+        ex = self.exchange(sums.device)
+        if ex is not None and b > ex.max_clips:
+            raise ValueError(f"{b} clips in one call, the statistics exchange was opened for max_batch = {ex.max_clips}")
         if self.global_bank:
-            if self._exchange is None or b != self.max_batch:
+            if ex is None or ex.staged or b != self.max_batch:
                 raise RuntimeError("global_bank needs the peer-memory exchange and exactly max_batch clips per rank and step")
-            self._exchange.run(self.state, sums, b, n_parts, elems, self.max_update, self.stats,
-                               (self.clips_done * world) % self.gcap, self.gcap, write_all=True)
-            return
-        if world > 1 and self.sync_stats and self._exchange is not None and b <= self._exchange.max_clips:
-            self._exchange.run(self.state, sums, b, n_parts, elems, self.max_update, self.stats, self.slot0, self.cap)
-        elif world > 1 and self.sync_stats:
-            local = torch.empty((b, 2), dtype=torch.float64, device=sums.device)
-            _native.check(lib.assl_clip_sums(_ptr(sums), b, n_parts, _ptr(local), _stream_ptr()))
-            gathered = gather_clip_sums(local)
-            # (kept until the next call: a deferred two-view launch may run beside this statistics kernel, and its
-            #  freshly allocated outputs must not land in a block the caching allocator got back from here)
-            self._keep = (local, gathered)
-            _native.check(lib.assl_running_stats(_ptr(self.state), _ptr(gathered), world * b, 1, elems,
-                                                 int(self.max_update), rank * b, b, _ptr(self.stats),
-                                                 self.slot0, self.cap, _stream_ptr()), "assl_running_stats")
+            ex.run(self.state, sums, b, n_parts, elems, self.max_update, self.stats,
+                   (self.clips_done * ex.world) % self.gcap, self.gcap, write_all=True)
+        elif ex is not None:
+            ex.run(self.state, sums, b, n_parts, elems, self.max_update, self.stats, self.slot0, self.cap)
         else:
             _native.check(lib.assl_running_stats(_ptr(self.state), _ptr(sums), b, n_parts, elems,
                                                  int(self.max_update), 0, b, _ptr(self.stats),
                                                  self.slot0, self.cap, _stream_ptr()), "assl_running_stats")
+        self._keep = sums        # (a deferred launch may still run beside the kernel that reads them)
+
+    def send_stats(self, sums, n_parts):
+        """split_stats: this rank's sums of the batch at the ring head go out; ``scan_pending_stats`` completes the step."""
+        ex = self.exchange(sums.device)
+        b = sums.shape[0]
+        if b > ex.max_clips:
+            raise ValueError(f"{b} clips in one call, the statistics exchange was opened for max_batch = {ex.max_clips}")
+        ex.send(sums, b, n_parts)
+        self._sent = (self.slot0, b)
+        self._keep = sums
+
+    def scan_pending_stats(self, deferred=True):
+        """split_stats: the scan of the batch sent last (no-op when none is pending)."""
+        if getattr(self, "_sent", None) is None:
+            return
+        slot0, _ = self._sent
+        self._exchange.scan(self.state, self.f * self.t, self.max_update, self.stats, slot0, self.cap, deferred=deferred)
+        self._sent = None
+
+    def check_exchange(self):
+        if self._exchange not in (False, None):
+            self._exchange.check()
 
     def moments(self, x):
         sums = torch.empty((x.shape[0], 1, 2), dtype=torch.float64, device=x.device)
@@ -268,9 +349,12 @@ class ViewEngine:
         """Validate and upload the parameters of the ``batch`` clips whose first global index is ``g0``."""
         ch, cw = canvas_size(self.f, self.t, self.vscale)
         validate_crops(params.crop, ch, cw)
-        src = params.src_clip
-        if np.any(src >= g0 + batch) or np.any((src >= 0) & (src < g0 + batch - self.cap)):
-            raise ValueError("mixup source outside the bank ring")
+        src = np.asarray(params.src_clip)
+        clip = (g0 + np.arange(batch, dtype=np.int64)).reshape((-1,) + (1,) * (src.ndim - 1))
+        # the FIFO, not the ring, bounds a pick: the last ``history`` clips (and, for view 2, the clip itself)
+        if np.any(src > clip) or np.any((src >= 0) & (src < clip - self.history)):
+            raise ValueError("mixup source outside the bank (the FIFO holds the last "
+                             f"{self.history} clips)")
         mix_slot = np.where(src >= 0, src % self.cap, -1).astype(np.int32)
         clip_slot = ((g0 + np.arange(batch, dtype=np.int64)) % self.cap).astype(np.int32)
         to_dev = lambda a: torch.from_numpy(a).to(device, non_blocking=True)   # noqa: E731
@@ -341,6 +425,7 @@ class ViewEngine:
     def state_dict(self):
         if self.ahead:
             raise RuntimeError("a batch is still waiting for its views: call flush() before state_dict()")
+        self.check_exchange()
         return {"clips_done": self.clips_done, "cap": self.cap,
                 "ring": None if self.ring is None else self.ring.cpu(),
                 "stats": None if self.stats is None else self.stats.cpu(),

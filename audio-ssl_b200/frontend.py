@@ -77,6 +77,51 @@ class Plan:
             pass
 
 
+class HostPipeline:
+    """``assl_pipeline``: the whole path with HOST buffers (pinned waveforms in, both views back in pinned host memory;
+    uploads, kernels and downloads of consecutive calls overlap) -- what a DataLoader-side caller binds in place of
+    BaseDataset.__getitem__'s per-clip CPU work (/root/reference/src/dataset/upstream_dataset.py:65,82,86).  Owns the
+    copy streams and the call parity; the plan stays shareable.  ``exchange``: a ``StatsExchange`` over peer memory for a
+    clip-sharded multi-GPU run (every call then scans all ranks' clips)."""
+
+    def __init__(self, plan: Plan, exchange=None):
+        self.plan, self.exchange = plan, exchange
+        self.handle = C.c_void_p()
+        ex = exchange.handle if exchange is not None else None
+        _native.check(_native.lib().assl_pipeline_create(C.byref(self.handle), plan.handle, ex), "assl_pipeline_create")
+
+    def workspace_bytes(self, batch, n_samples, cap):
+        n = _native.lib().assl_pipeline_workspace_bytes(self.plan.handle, int(batch), int(n_samples), int(cap))
+        if n < 0:
+            raise ValueError("assl_pipeline_workspace_bytes: invalid batch / clip length / ring capacity")
+        return int(n)
+
+    def run(self, vcfg, ws, host_wave, batch, n_samples, slot0, cap, max_update, mix_slot, alpha, crop,
+            host_view1=None, host_view2=None, stream=None):
+        """One call.  ``ws`` device uint8 workspace; ``host_wave`` / ``host_view*`` pinned CPU tensors; ``mix_slot`` /
+        ``alpha`` / ``crop`` contiguous numpy arrays that stay alive until ``sync()``."""
+        hp = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)   # noqa: E731
+        _native.check(_native.lib().assl_pipeline_host_f32(
+            self.handle, C.byref(vcfg), _ptr(ws), ws.numel(), hp(host_wave), int(batch), int(n_samples), int(slot0), int(cap),
+            int(max_update), mix_slot.ctypes.data_as(C.c_void_p), alpha.ctypes.data_as(C.c_void_p),
+            crop.ctypes.data_as(C.c_void_p), hp(host_view1), hp(host_view2), None, None,
+            stream if stream is not None else _stream_ptr()), "assl_pipeline_host_f32")
+
+    def sync(self):
+        _native.check(_native.lib().assl_pipeline_host_sync(self.handle), "assl_pipeline_host_sync")
+
+    def close(self):
+        if self.handle:
+            _native.lib().assl_pipeline_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class MelSpectrogramLibrosa:
     """Mel spectrogram with librosa 0.8.1 semantics (utils.py:20-28), computed by the fused kernel.
 

@@ -179,6 +179,7 @@ class UpstreamInputPipeline:
         return self.tfms._post(v1, v2)
 
     # -- lookahead=True: software-pipelined step order  log-mel(k) . statistics(k) . views(k-1)
+    #    (across GPUs: scan(k-1) . log-mel(k) . send(k) . views(k-1), see ViewEngine.split_stats)
     def _call_lookahead(self, waveforms, params):
         """Run the front end and the statistics of THIS batch and return the two views of the PREVIOUS one (``None`` on
         the first call; ``flush()`` returns the last batch's).  The views of batch k-1 are launched right behind the
@@ -211,8 +212,15 @@ class UpstreamInputPipeline:
         prep = eng.prepare_views(p, b, part.device, eng.head)
         tiles = self.plan.num_tiles(part.shape[1])
         sums = torch.empty((b, tiles, 2), dtype=torch.float64, device=part.device) if tf.pre_norm else None
+        split = tf.pre_norm and eng.split_stats
+        if split:
+            # sharded run: the statistics of the PENDING batch are scanned now (every rank sent its sums a step ago, right
+            # behind its log-mel kernel, so nobody waits for the slowest rank here), this batch's sums go out below
+            eng.scan_pending_stats(deferred=True)
         self.plan.logmel_into(part, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain)
-        if tf.pre_norm:
+        if split:
+            eng.send_stats(sums, tiles)
+        elif tf.pre_norm:
             eng.update_stats(sums, tiles)
         eng.ahead += b
         out = None
@@ -231,6 +239,7 @@ class UpstreamInputPipeline:
             return None
         eng = self.tfms.engine
         with torch.cuda.device(self._pending["device"]):
+            eng.scan_pending_stats(deferred=False)          # (sharded lookahead run: the last batch's statistics)
             v1, v2 = eng.launch_prepared(self._pending, deferred=False)
         eng.ahead -= self._pending["batch"]
         self._pending = None

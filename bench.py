@@ -3,16 +3,21 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-A step = one pass of the hot path over one batch of synthetic waveforms per GPU (weak scaling:
-per-GPU batch fixed).  Workload at N=1: BASELINE config 2 -- n_fft 1024, hop 160, 64 mels, 60-7800 Hz,
-1 s 16 kHz clips, batch 1024.  ``value`` is measured with inputs resident in HBM (CUDA events, max over
-ranks); ``e2e`` goes through the C-ABI host entry point with pinned HOST buffers, H2D and D2H inside the
-timed region.  ``roofline`` is for the dominant kernel (log-mel) from its live CUDA-event time;
-``cpu_baseline`` times the CPU oracle port on this box's host cores on a bounded sample.
+A step = one pass of the hot path over one batch of synthetic waveforms per GPU.  Headline workload (``value``,
+``config.workload``): BASELINE config 2 -- n_fft 1024, hop 160, 64 mels, 60-7800 Hz, 1 s 16 kHz clips, batch 1024 per GPU
+(weak scaling).  ``value`` is measured with inputs resident in HBM (CUDA events, max over ranks); ``e2e`` goes through
+the C-ABI host entry point with pinned HOST buffers, H2D and D2H inside the timed region; ``roofline`` is for the
+dominant kernel (log-mel) from its live CUDA-event time; ``cpu_baseline`` times the CPU oracle port on this box's host
+cores on a bounded sample.  Behind the headline the same step loop is timed on BASELINE configs 3, 4 and three points of
+config 5 (``configs``: GLOBAL batches sharded by clip over the ranks), and with more than one rank the run first checks,
+through the product API, that the sharded pipeline equals one process on the unsharded batch
+(``sharded_equals_unsharded``; exit code 3 if it does not).
 """
 import argparse
 import ctypes as C
+import hashlib
 import json
+import math
 import os
 import statistics
 import subprocess
@@ -46,6 +51,28 @@ def measured_peak_gbs():
             return float(json.load(fh)["hbm_gbs"]), "MEASURED_PEAKS.json"
     except Exception:
         return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def kernel_source_hash():
+    """sha256 over the log-mel kernel's sources: a DRAM-traffic figure captured under ncu belongs to one version of them."""
+    h = hashlib.sha256()
+    for f in ("logmel.cu", "common.cuh", "f32x2.cuh", "fft32p_gen.cuh"):
+        with open(os.path.join(ROOT, "audio-ssl_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def recorded_traffic():
+    """profiles/traffic.json: dram bytes per launch of logmel_kernel from one `ncu --set full` capture of this very
+    workload -- used only while the kernel's sources still hash to what the capture was taken from."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+            t = json.load(fh)
+        if t.get("source_sha") == kernel_source_hash():
+            return t.get("logmel_kernel_bytes_per_launch"), t.get("capture")
+        return None, "profiles/traffic.json is from another version of the kernel (source hash differs): not reported"
+    except Exception:
+        return None, "no capture on file"
 
 
 # ----------------------------------------------------------------------------------------------
@@ -124,6 +151,7 @@ def run_reference_arm(args):
 
 
 def workload_config(args, per_gpu_batch):
+    """The same dict in both arms (the driver compares them)."""
     return {"workload": f"C2: log-mel (n_fft 1024, hop 160, 64 mels, 60-7800 Hz) + BYOL-A 2-view aug, "
                         f"{args.seconds:g} s 16 kHz clips, batch {per_gpu_batch} per GPU",
             "clip_seconds": args.seconds, "per_gpu_batch": per_gpu_batch, "global_batch": per_gpu_batch * args.gpus,
@@ -133,34 +161,257 @@ def workload_config(args, per_gpu_batch):
 
 # ----------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    """nvidia-smi clocks / throttle reasons sampled every 20 ms; ``mark()`` brackets the loaded periods and only
+    samples taken inside one are reported (B200_PROFILING.md: clocks DURING the timed region)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.loaded = index, [], None, []
 
     def run(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
-                self.rows.append([c.strip() for c in line.split(",")])
+                self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
         except Exception:
             pass
+
+    def mark(self, t0, t1):
+        self.loaded.append((t0, t1))
 
     def stop(self):
         if self.proc is not None:
             self.proc.terminate()
         self.join(timeout=2)
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        # a sample describes the ~20 ms before it arrived: keep those that arrived inside a loaded period
+        rows = [r for t, r in self.rows if any(a + 0.03 <= t <= b + 0.005 for a, b in self.loaded)]
+        num = lambda v: float(v) if v.replace(".", "", 1).isdigit() else None   # noqa: E731
+        sm = [num(r[0]) for r in rows if r and num(r[0]) is not None]
+        mx = [num(r[1]) for r in self.rows_all() if len(r) > 1 and num(r[1]) is not None]
+        pw = [num(r[2]) for r in rows if len(r) > 2 and num(r[2]) is not None]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows if len(r) >= 7 for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        reasons = sorted({n for r in rows if len(r) >= 7 for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_mhz_min": min(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "power_w_max": max(pw) if pw else None,
+                "reasons": reasons, "samples": len(sm), "samples_total": len(self.rows),
+                "loaded_seconds": round(sum(b - a for a, b in self.loaded), 3),
+                "how": "nvidia-smi -lms 20; only samples that arrived while the step loop was running on the GPU"}
+
+    def rows_all(self):
+        return [r for _, r in self.rows]
+
+
+# ----------------------------------------------------------------------------------------------
+class Workload:
+    """Device-resident step loop for one (per-GPU batch, clip length): the C ABI driven through ctypes with raw pointers
+    taken once (~5 us per call, so the host stays ahead of the GPU).  Step order with lookahead, one GPU:
+    log-mel(k) . statistics(k) . views(k-1); across GPUs: scan(k-1) . log-mel(k) . send(k) . views(k-1)."""
+
+    def __init__(self, A, lib, dev, rank, world, batch, n_samples, exchange_factory, lookahead=True, gbank=False,
+                 rotate_bytes=256 << 20, rotate_min=2, seed=1234):
+        import torch
+        from audiossl_b200 import _native
+        from audiossl_b200.engine import heavy_first
+        self.torch, self.lib, self.dev, self.rank, self.world = torch, lib, dev, rank, world
+        self.B, self.L = batch, n_samples
+        self.look, self.gbank = lookahead and not gbank, gbank
+        self.plan = A.Plan()
+        self.T, self.tiles = self.plan.num_frames(n_samples), self.plan.num_tiles(n_samples)
+        B, L, T = self.B, self.L, self.T
+        self.tf = A.AugmentationModule(CFG, len_of_files=10 ** 7, sampler="fast", max_batch=B,
+                                       seed=seed + (0 if gbank else rank), global_bank=gbank, lookahead=self.look)
+        eng = self.eng = self.tf.engine
+        eng.ensure(N_MELS, T, dev)
+        eng.ring.zero_()
+        self.cap = eng.cap
+        self.rotate = max(rotate_min, min(16, -(-rotate_bytes // (B * L * 4))))
+        gen = torch.Generator(device=dev).manual_seed(seed + 2 + rank)          # SURVEY §8(d): seed 1234 + config id
+        self.waves = [torch.randn(B, L, generator=gen, device=dev) * 0.1 for _ in range(self.rotate)]
+        self.v1 = torch.empty((B, N_MELS, T), dtype=torch.float32, device=dev)
+        self.v2 = torch.empty_like(self.v1)
+        self.sums = [torch.empty((B, self.tiles, 2), dtype=torch.float64, device=dev) for _ in range(2)]
+        ch, cw = int(N_MELS * 1.0), int(T * 1.5)
+        self.vcfg = _native.ViewCfg(N_MELS, T, ch, cw, 0, 1)
+        self.max_update = int(eng.max_update)
+        self.exchange = exchange_factory(B) if world > 1 else None
+        self.split = self.look and self.exchange is not None
+        # parameter sets: the ring position of step s repeats with period cap / gcd(B, cap); the draws are those of steps far
+        # into a run (bank full: every view mixes), so a set fits every step with the same ring position
+        gsz = B * world if gbank else B
+        period = self.cap // math.gcd(B, self.cap)
+        if gbank:
+            period = (eng.gcap // gsz) * period // math.gcd(eng.gcap // gsz, period)
+        self.n_sets = period * max(1, -(-6 // period))
+        s0 = self.n_sets * (-(-(4096 // B + 4) // self.n_sets))
+        self.sets = []
+        for j in range(self.n_sets):
+            s = s0 + j
+            if gbank:
+                p = self.tf.sampler.draw(s * gsz, gsz, N_MELS, T)
+                lo, hi = rank * B, (rank + 1) * B
+                idx = eng.global_indices(np.asarray(p.src_clip[lo:hi], np.int64), s)
+                arrs = list(idx) + [np.ascontiguousarray(p.alpha[lo:hi]), np.ascontiguousarray(p.crop[lo:hi]),
+                                    heavy_first(p.crop[lo:hi], T, cw)]
+            else:
+                p = self.tf.sampler.draw(s * B, B, N_MELS, T)
+                mix = np.where(p.src_clip >= 0, p.src_clip % self.cap, -1).astype(np.int32)
+                clip = ((s * B + np.arange(B, dtype=np.int64)) % self.cap).astype(np.int32)
+                arrs = [clip, mix, np.ascontiguousarray(p.alpha), np.ascontiguousarray(p.crop), heavy_first(p.crop, T, cw)]
+            self.sets.append([torch.from_numpy(a).to(dev) for a in arrs])
+        ptr = lambda t: int(t.data_ptr())  # noqa: E731
+        self.st = int(torch.cuda.current_stream().cuda_stream)
+        self.p_waves = [ptr(w) for w in self.waves]
+        self.p_ring, self.p_stats, self.p_state = ptr(eng.ring), ptr(eng.stats), ptr(eng.state)
+        self.p_v1, self.p_v2 = ptr(self.v1), ptr(self.v2)
+        self.p_sums = [ptr(t) for t in self.sums]
+        self.p_sets = [[ptr(t) for t in sp] for sp in self.sets]
+        self.vref = C.byref(self.vcfg)
+        self.elems = N_MELS * T
+        self.step_no = 0
+        self.check = _native.check
+
+    @property
+    def launches_per_step(self):
+        return 4 if self.split else 3
+
+    def step(self, events=None):
+        """One step; ``events`` = 4 CUDA events recorded around the three stages (serialises the dependent launches)."""
+        lib, chk, st, B, L, cap = self.lib, self.check, self.st, self.B, self.L, self.cap
+        s = self.step_no
+        self.step_no += 1
+        slot0 = (s * B) % cap
+        sums = self.p_sums[s & 1]
+        rec = (lambda i: events[i].record()) if events is not None else (lambda i: None)
+        rec(0)
+        if self.split and s > 0:       # statistics of the PREVIOUS batch: every rank sent its sums a step ago
+            chk(lib.assl_running_stats_exchange_scan(self.exchange.handle, self.p_state, self.elems, self.max_update,
+                                                     self.p_stats, ((s - 1) * B) % cap, cap, 0, 1, st))
+        chk(lib.assl_logmel_f32(self.plan.handle, self.p_waves[s % self.rotate], None, B, L, L, self.p_ring, slot0, cap,
+                                sums, 0, st))
+        rec(1)
+        if self.split:
+            chk(lib.assl_exchange_send(self.exchange.handle, sums, B, self.tiles, st))
+            if self.exchange.staged:
+                self.exchange._gather()
+        elif self.gbank:
+            self.exchange.run(self.eng.state, self.sums[s & 1], B, self.tiles, self.elems, self.max_update, self.eng.stats,
+                              (s * B * self.world) % self.eng.gcap, self.eng.gcap, write_all=True)
+        elif self.exchange is not None:
+            self.exchange.run(self.eng.state, self.sums[s & 1], B, self.tiles, self.elems, self.max_update, self.eng.stats,
+                              slot0, cap)
+        else:
+            chk(lib.assl_running_stats(self.p_state, sums, B, self.tiles, self.elems, self.max_update, 0, B, self.p_stats,
+                                       slot0, cap, st))
+        rec(2)
+        if self.look:                                # views of the PREVIOUS batch, beside this batch's statistics
+            if s > 0:
+                clip, mix, alpha, crop, order = self.p_sets[(s - 1) % self.n_sets]
+                chk(lib.assl_two_views_deferred_f32(self.vref, self.p_ring, self.p_stats, cap, clip, mix, alpha, crop, order,
+                                                    B, self.p_v1, self.p_v2, st))
+        elif self.gbank:
+            clip, cstat, mix, mrank, mstat, alpha, crop, order = self.p_sets[s % self.n_sets]
+            chk(lib.assl_two_views_global_f32(self.vref, self.p_ring, self.eng.peer_ring.ptrs, self.world, self.p_stats, clip,
+                                              cstat, mix, mrank, mstat, alpha, crop, order, B, self.p_v1, self.p_v2, st))
+        else:
+            clip, mix, alpha, crop, order = self.p_sets[s % self.n_sets]
+            chk(lib.assl_two_views_ordered_f32(self.vref, self.p_ring, self.p_stats, cap, clip, mix, alpha, crop, order, B,
+                                               self.p_v1, self.p_v2, st))
+        rec(3)
+
+    def warm(self, min_steps):
+        """At least ``min_steps`` untimed steps, and enough to fill the ring (every bank pick then reads a real log-mel)."""
+        for _ in range(max(min_steps, -(-self.cap // self.B) + 1)):
+            self.step()
+
+    def timed(self, steps, fence):
+        """``steps`` steps between two events, no event inside; returns (ms total, host enqueue ms per step)."""
+        torch = self.torch
+        fence()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        h0 = time.perf_counter()
+        for _ in range(steps):
+            self.step()
+        host_ms = 1e3 * (time.perf_counter() - h0) / steps
+        t1.record()
+        fence()
+        return t0.elapsed_time(t1), host_ms
+
+    def close(self):
+        if self.exchange is not None:
+            self.exchange.check()
+            self.exchange.close()
+
+
+def sharded_check(A, dev, rank, world):
+    """Through the product API, on small batches: (1) the sharded lookahead pipeline (rank-local banks switched off, i.e.
+    mixup off; running statistics exchanged over peer memory, send/scan split) == ONE process on the unsharded batch in
+    the ordinary order; (2) with the global mixup bank (bank entries read from the peers' rings over NVLink) and mixup
+    ON the sharded run == one process on the unsharded batch.  Bit for bit (torch.equal); returns (ok, max |diff|, note)."""
+    import torch
+    import torch.distributed as dist
+    b, L, steps = 64, 8000, 6
+    g = torch.Generator(device="cpu").manual_seed(77)
+    crop_only = {"pretrain": {"normalization": "mean_var", "augmentations": {
+        "RandomResizeCrop": CFG["pretrain"]["augmentations"]["RandomResizeCrop"]}}}
+    T = A.Plan().num_frames(L)
+    take = lambda p, lo, hi: A.ViewParams(p.alpha[lo:hi], p.src_clip[lo:hi], p.bank_index[lo:hi], p.crop[lo:hi])   # noqa: E731
+    worst, ok = 0.0, True
+
+    def compare(got, want):
+        nonlocal worst, ok
+        for a, w in zip(got, want):
+            w = w[rank * b:(rank + 1) * b]
+            if not torch.equal(a, w):
+                ok = False
+                worst = max(worst, float((a - w).abs().max()))
+
+    # (1) statistics exchange, lookahead order
+    sharded = A.UpstreamInputPipeline(crop_only, 10 ** 6, max_batch=b, lookahead=True)
+    single = A.UpstreamInputPipeline(crop_only, 10 ** 6, max_batch=world * b, sync_stats=False)
+    draws = A.FastSampler(mixup=False, seed=5)
+    got, want = [], []
+    for s in range(steps):
+        wave = (torch.randn(world * b, L, generator=g) * 0.1).to(dev)
+        p = draws.draw(s * world * b, world * b, N_MELS, T)
+        got.append(sharded(wave[rank * b:(rank + 1) * b], params=take(p, rank * b, (rank + 1) * b)))
+        want.append(single(wave, params=p))
+    got = got[1:] + [sharded.flush()]
+    torch.cuda.synchronize()
+    for a, w in zip(got, want):
+        compare(a, w)
+    staged = sharded.tfms.engine._exchange.staged
+    transport = "staged (all-gather)" if staged else "peer memory over NVLink"
+    sharded.tfms.engine.check_exchange()
+    dist.barrier()
+    sharded.tfms.engine._exchange.close()
+    # (2) global bank, mixup on
+    note = f"statistics exchange ({transport}, send/scan split, lookahead order), {steps} steps of {b} clips per rank"
+    if not staged:
+        sharded = A.UpstreamInputPipeline(CFG, 10 ** 6, max_batch=b, sampler="fast", seed=11, global_bank=True)
+        single = A.UpstreamInputPipeline(CFG, 10 ** 6, max_batch=world * b, sampler="fast", seed=11, sync_stats=False)
+        remote = 0
+        for s in range(steps):
+            wave = (torch.randn(world * b, L, generator=g) * 0.1).to(dev)
+            a = sharded(wave[rank * b:(rank + 1) * b])
+            w = single(wave)
+            torch.cuda.synchronize()
+            compare(a, w)
+            src = sharded.tfms.last_params.src_clip
+            remote += int(np.sum((src >= 0) & ((src % (world * b)) // b != rank)))
+        sharded.tfms.engine.check_exchange()
+        dist.barrier()
+        sharded.tfms.engine._exchange.close()
+        note += f"; global mixup bank with mixup on, {steps} steps, {remote} bank entries read from other GPUs by rank 0"
+    flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    w = torch.tensor([worst], dtype=torch.float64, device=dev)
+    dist.all_reduce(w, op=dist.ReduceOp.MAX)
+    return bool(int(flag.item())), float(w.item()), note
 
 
 def run_ours(args):
@@ -169,7 +420,7 @@ def run_ours(args):
 
     import audiossl_b200 as A
     from audiossl_b200 import _native
-    from audiossl_b200.engine import StatsExchange, gather_clip_sums, heavy_first
+    from audiossl_b200.engine import StatsExchange
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -179,105 +430,8 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":      # keeps NCCL's banner off stdout (one JSON line)
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     lib = _native.lib()
-    P = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)  # noqa: E731
-    stream = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)  # noqa: E731
-
-    B, L, W, K = args.batch, int(args.seconds * 16000), args.warmup, args.steps
-    plan = A.Plan()
-    T, tiles = plan.num_frames(L), plan.num_tiles(L)
-    gbank = bool(args.global_bank) and world > 1
-    look = bool(args.lookahead) and not gbank
-    # (lookahead: the ring holds one more batch -- the log-mel kernel of batch k+1 writes while the views of batch k read)
-    tf = A.AugmentationModule(CFG, len_of_files=10 ** 7, sampler="fast", max_batch=2 * B if look else B,
-                              seed=1234 + (0 if gbank else rank), global_bank=gbank)
-    eng = tf.engine
-    eng.ensure(N_MELS, T, dev)
-    cap = eng.cap
-    gen = torch.Generator(device="cpu").manual_seed(1234 + 2 + rank)          # seed 1234 + config id
-    host_waves = [(torch.randn(B, L, generator=gen) * 0.1).to(torch.float32).pin_memory() for _ in range(args.rotate)]
-    waves = [w.to(dev) for w in host_waves]
-    v1 = torch.empty((B, N_MELS, T), dtype=torch.float32, device=dev)
-    v2 = torch.empty_like(v1)
-    sums = torch.empty((B, tiles, 2), dtype=torch.float64, device=dev)
-    local_sums = torch.empty((B, 2), dtype=torch.float64, device=dev)
-    ch, cw = int(N_MELS * 1.0), int(T * 1.5)
-    vcfg = _native.ViewCfg(N_MELS, T, ch, cw, 0, 1)
-    max_update = int(eng.max_update)
-
-    def upload(p, clips_done):
-        mix = np.where(p.src_clip >= 0, p.src_clip % cap, -1).astype(np.int32)
-        clip = ((clips_done + np.arange(B, dtype=np.int64)) % cap).astype(np.int32)
-        return [torch.from_numpy(a).to(dev) for a in (clip, mix, np.ascontiguousarray(p.alpha), np.ascontiguousarray(p.crop),
-                                                      heavy_first(p.crop, T, int(T * 1.5)))]
-
-    def upload_global(step):
-        """Global bank: every rank draws the global batch from the same generator and keeps its slice (global clip ids)."""
-        p = tf.sampler.draw(step * B * world, B * world, N_MELS, T)
-        lo, hi = rank * B, (rank + 1) * B
-        idx = eng.global_indices(np.asarray(p.src_clip[lo:hi], np.int64), step)
-        arrs = list(idx) + [np.ascontiguousarray(p.alpha[lo:hi]), np.ascontiguousarray(p.crop[lo:hi]), heavy_first(p.crop[lo:hi], T, int(T * 1.5))]
-        return [torch.from_numpy(a).to(dev) for a in arrs]
-
-    # steps [0, W) warm up, [W, W+K) are the timed region (no event between the kernels: an event record would
-    # serialise the programmatic dependent launches), [W+K, W+2K) repeat the same work with an event between the
-    # kernels for the per-kernel durations (roofline.kernel_ms)
-    steps_params = [upload_global(s) if gbank else upload(tf.sampler.draw(s * B, B, N_MELS, T), s * B) for s in range(W + 2 * K)]
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(W + 2 * K)]
-
-    exchange = StatsExchange.open(B, dev) if world > 1 else None        # peer-memory path; None -> NCCL all-gather
-    if gbank and exchange is None:
-        raise RuntimeError("--global-bank needs the peer-memory exchange")
-
-    class _NoEvent:
-        def record(self):
-            pass
-
-    # raw pointers taken once: the timed loop only makes ctypes calls (~5 us each), so the host stays ahead of the GPU
-    ptr = lambda t: int(t.data_ptr())  # noqa: E731
-    st = int(torch.cuda.current_stream().cuda_stream)
-    p_waves = [ptr(w) for w in waves]
-    p_ring, p_sums, p_stats, p_state, p_v1, p_v2 = ptr(eng.ring), ptr(sums), ptr(eng.stats), ptr(eng.state), ptr(v1), ptr(v2)
-    p_params = [[ptr(t) for t in sp] for sp in steps_params]
-    vref = C.byref(vcfg)
-    elems = N_MELS * T
-
-    def device_step(s, instrument=False):
-        slot0 = (s * B) % cap
-        e = evs[s] if instrument else [_NoEvent()] * 4
-        e[0].record()
-        _native.check(lib.assl_logmel_f32(plan.handle, p_waves[s % args.rotate], None, B, L, L, p_ring, slot0, cap, p_sums, 0, st))
-        e[1].record()
-        if gbank:
-            exchange.run(eng.state, sums, B, tiles, elems, max_update, eng.stats, (s * B * world) % eng.gcap, eng.gcap,
-                         write_all=True)
-        elif exchange is not None:
-            exchange.run(eng.state, sums, B, tiles, elems, max_update, eng.stats, slot0, cap)
-        elif world > 1:
-            _native.check(lib.assl_clip_sums(p_sums, B, tiles, P(local_sums), st))
-            gathered = gather_clip_sums(local_sums)
-            _native.check(lib.assl_running_stats(p_state, P(gathered), world * B, 1, elems, max_update,
-                                                 rank * B, B, p_stats, slot0, cap, st))
-        else:
-            _native.check(lib.assl_running_stats(p_state, p_sums, B, tiles, elems, max_update, 0, B, p_stats, slot0, cap, st))
-        e[2].record()
-        if look:                                     # views of the PREVIOUS batch, beside this batch's statistics
-            if s > 0:
-                clip, mix, alpha, crop, order = p_params[s - 1]
-                _native.check(lib.assl_two_views_deferred_f32(vref, p_ring, p_stats, cap, clip, mix, alpha, crop, order, B,
-                                                              p_v1, p_v2, st))
-        elif gbank:
-            clip, cstat, mix, mrank, mstat, alpha, crop, order = p_params[s]
-            _native.check(lib.assl_two_views_global_f32(vref, p_ring, eng.peer_ring.ptrs, world, p_stats, clip, cstat, mix,
-                                                        mrank, mstat, alpha, crop, order, B, p_v1, p_v2, st))
-        else:
-            clip, mix, alpha, crop, order = p_params[s]
-            _native.check(lib.assl_two_views_ordered_f32(vref, p_ring, p_stats, cap, clip, mix, alpha, crop, order, B,
-                                                         p_v1, p_v2, st))
-        e[3].record()
 
     def fence():
         torch.cuda.synchronize()
@@ -285,39 +439,109 @@ def run_ours(args):
             dist.barrier()
             torch.cuda.synchronize()
 
-    for s in range(W):
-        device_step(s)
-    fence()
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    B, L, W, K = args.batch, int(args.seconds * 16000), max(args.warmup, 3), args.steps
+    gbank = bool(args.global_bank) and world > 1
+    peak, peak_src = measured_peak_gbs()
+
+    # ---- multi-GPU: the sharded run has to equal the single-stream run before anything is timed
+    shard_ok, shard_diff, shard_note = None, None, None
+    if world > 1 and not args.no_check:
+        shard_ok, shard_diff, shard_note = sharded_check(A, dev, rank, world)
+
+    open_exchange = lambda b: StatsExchange.open(b, dev)   # noqa: E731
+    wl = Workload(A, lib, dev, rank, world, B, L, open_exchange, lookahead=bool(args.lookahead), gbank=gbank,
+                  rotate_min=args.rotate)
+    if gbank and (wl.exchange is None or wl.exchange.staged):
+        raise RuntimeError("--global-bank needs the peer-memory exchange")
+    T = wl.T
+    a_fe, a_all = algorithmic_bytes(L, True), algorithmic_bytes(L)
+
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
-        time.sleep(0.3)
+    wl.warm(W)
     fence()
-    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t_begin.record()
-    h0 = time.perf_counter()
-    for s in range(W, W + K):
-        device_step(s)
-    host_enqueue_ms = 1e3 * (time.perf_counter() - h0) / K
-    t_end.record()
+    # clocks and power at steady state: the same step loop for >= 1 s before the timed region
+    est_ms, _ = wl.timed(K, fence)
+    est_ms = max(max_over_ranks(est_ms) / K, 1e-3)
+    t_a = time.perf_counter()
+    wl.timed(max(K, int(args.presteady_s * 1e3 / est_ms)), fence)
+    # ---- the timed region: exactly K steps, no event between the kernels
+    ms_total, host_enqueue_ms = wl.timed(K, fence)
+    ms_total = max_over_ranks(ms_total)
+    # ---- sustained: the same loop for >= 2 s
+    n_sus = max(K, int(args.sustained_s * 1e3 / max(ms_total / K, 1e-3)))
+    sus_ms, _ = wl.timed(n_sus, fence)
+    sus_ms = max_over_ranks(sus_ms)
+    t_b = time.perf_counter()
+    if sampler:
+        sampler.mark(t_a, t_b)
+    # ---- per-kernel durations: K further steps with an event between the kernels
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(K)]
+    for e in evs:
+        wl.step(events=e)
     fence()
-    ms_total = t_begin.elapsed_time(t_end)
-    for s in range(W + K, W + 2 * K):
-        device_step(s, instrument=True)
-    fence()
-    k_ms = [statistics.fmean(evs[s][i].elapsed_time(evs[s][i + 1]) for s in range(W + K, W + 2 * K)) for i in range(3)]
-    if world > 1:
-        tmax = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        ms_total = float(tmax.item())
+    k_ms = [statistics.fmean(e[i].elapsed_time(e[i + 1]) for e in evs) for i in range(3)]
+    exchange_kind = ("none (one GPU)" if world == 1 else
+                     ("staged: all-gather of the records" if wl.exchange.staged else "peer memory over NVLink") +
+                     (", send(k) behind log-mel(k) and scan(k-1) a step later" if wl.split else ", fused send + scan"))
+    launches_per_step = wl.launches_per_step
+    lookahead_on = wl.look
+    wl.close()
+    del wl
+    torch.cuda.empty_cache()
 
-    # ---- end to end through the C ABI with HOST buffers (H2D + kernels + D2H inside the timed region)
-    ws_bytes = lib.assl_pipeline_workspace_bytes(plan.handle, B, L, cap)
+    # ---- BASELINE configs 3, 4 and three points of config 5: GLOBAL batch sharded by clip over the ranks
+    configs = {}
+    if not args.no_configs:
+        table = [("C3", 4096, 0.95, "DeLoRes-S upstream input pipeline (length_wave 0.95 s), global batch 4096"),
+                 ("C4", 2048, 10.0, "DeCAR / DeLoRes-M 10 s clips, global batch 2048, running-norm exchange"),
+                 ("C5_256x30s", 256, 30.0, "sweep point: 30 s clips, global batch 256"),
+                 ("C5_4096x1s", 4096, 1.0, "sweep point: 1 s clips, global batch 4096"),
+                 ("C5_16384x1s", 16384, 1.0, "sweep point: 1 s clips, global batch 16384")]
+        for name, gb, secs, what in table:
+            if gb % world:
+                continue
+            b, n = gb // world, int(secs * 16000)
+            w2 = Workload(A, lib, dev, rank, world, b, n, open_exchange, lookahead=True, rotate_min=2, seed=1234 + len(configs))
+            w2.warm(3)
+            ms, _ = w2.timed(K, fence)
+            ms = max_over_ranks(ms)
+            cps = gb * K / (ms * 1e-3)
+            bpc = algorithmic_bytes(n)
+            configs[name] = {"what": what, "global_batch": gb, "per_gpu_batch": b, "clip_seconds": secs,
+                             "value": cps, "unit": UNIT, "ms_per_step": ms / K, "steps": K,
+                             "pipeline_roofline": {"achieved": cps / world * bpc / 1e9, "peak": peak, "unit": "GB/s",
+                                                   "frac": cps / world * bpc / 1e9 / peak, "bytes_per_clip": bpc}}
+            w2.close()
+            del w2
+            torch.cuda.empty_cache()
+
+    # ---- end to end through the C ABI with HOST buffers (H2D + kernels + D2H inside the timed region); across GPUs
+    #      with the statistics exchange, i.e. the sharded path
+    plan = A.Plan()
+    cap = 1024 + B
+    max_update = 2 * 10 ** 7 * 10
+    ex = StatsExchange.open(B, dev) if world > 1 else None
+    if ex is not None and ex.staged:
+        ex.close(); ex = None
+    pipe = A.HostPipeline(plan, ex)
+    ws_bytes = pipe.workspace_bytes(B, L, cap)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     ws[:64].zero_()
+    gen = torch.Generator(device="cpu").manual_seed(1234 + 2 + rank)
+    host_waves = [(torch.randn(B, L, generator=gen) * 0.1).to(torch.float32).pin_memory() for _ in range(args.rotate)]
     hv1 = torch.empty((B, N_MELS, T), dtype=torch.float32).pin_memory()
     hv2 = torch.empty((B, N_MELS, T), dtype=torch.float32).pin_memory()
     fast = A.FastSampler(seed=99 + rank)
+    vcfg = _native.ViewCfg(N_MELS, T, int(N_MELS * 1.0), int(T * 1.5), 0, 1)
     keep = []
 
     def host_step(s):
@@ -325,71 +549,69 @@ def run_ours(args):
         mix = np.where(p.src_clip >= 0, p.src_clip % cap, -1).astype(np.int32)
         alpha, crop = np.ascontiguousarray(p.alpha), np.ascontiguousarray(p.crop)
         keep.append((mix, alpha, crop))                       # the async copies read these until the sync
-        _native.check(lib.assl_pipeline_host_f32(
-            plan.handle, C.byref(vcfg), P(ws), ws_bytes, C.c_void_p(host_waves[s % args.rotate].data_ptr()), B, L,
-            (s * B) % cap, cap, max_update, mix.ctypes.data_as(C.c_void_p), alpha.ctypes.data_as(C.c_void_p),
-            crop.ctypes.data_as(C.c_void_p), C.c_void_p(hv1.data_ptr()), C.c_void_p(hv2.data_ptr()), None, None, stream()),
-            "assl_pipeline_host_f32")
-
-    def host_fence():
-        _native.check(lib.assl_pipeline_host_sync(plan.handle))
-        fence()
+        pipe.run(vcfg, ws, host_waves[s % args.rotate], B, L, (s * B) % cap, cap, max_update, mix, alpha, crop, hv1, hv2)
 
     for s in range(W):
         host_step(s)
-    host_fence()
+    pipe.sync()
+    fence()
+    n_e2e = K
     t0 = time.perf_counter()
-    for s in range(W, W + K):
+    for s in range(W, W + n_e2e):
         host_step(s)
-    _native.check(lib.assl_pipeline_host_sync(plan.handle))      # every download has landed in host memory
+    pipe.sync()                                                # every download has landed in host memory
     torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        tmax = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        e2e_s = float(tmax.item())
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
     clocks = sampler.stop() if sampler else None
     checksum = float(hv1[0, 0, :4].sum())
+    if ex is not None:
+        ex.check()
+    pipe.close()
 
     if rank != 0:
         if world > 1:
             dist.barrier(); dist.destroy_process_group()
+        if shard_ok is False:
+            sys.exit(3)
         return
-    peak, peak_src = measured_peak_gbs()
     clips_per_s = world * B * K / (ms_total * 1e-3)
-    a_fe, a_all = algorithmic_bytes(L, True), algorithmic_bytes(L)
     ach = B * a_fe / (k_ms[0] * 1e-3) / 1e9
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
-            traffic = json.load(fh).get("logmel_kernel_bytes_per_launch")
-    except Exception:
-        pass
+    traffic, traffic_note = recorded_traffic()
     out = {
         "metric": METRIC, "value": clips_per_s, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-        "ms_per_step": ms_total / K, "host_enqueue_ms_per_step": host_enqueue_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": dict(workload_config(args, B), stats_exchange=("none (one GPU)" if world == 1 else
-                                                                 "peer memory over NVLink, fused into the statistics kernel"
-                                                                 if exchange is not None else "NCCL all-gather"),
-                    step_order=("log-mel(k), statistics(k), views(k-1): the views of the previous batch are launched "
-                                "deferred (assl_two_views_deferred_f32, UpstreamInputPipeline(lookahead=True)); every step "
-                                "runs all three kernels" if look else "log-mel(k), statistics(k), views(k)"),
-                    mixup_bank=("global FIFO, bank entries read from the peers' rings over NVLink (optional mode)" if gbank
-                                else "rank-local FIFO (as each reference worker's)")),
+        "ms_per_step": ms_total / K, "host_enqueue_ms_per_step": host_enqueue_ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, B),
+        "path": {"stats_exchange": exchange_kind,
+                 "step_order": ("scan(k-1), log-mel(k), send(k), views(k-1)" if (lookahead_on and world > 1) else
+                                "log-mel(k), statistics(k), views(k-1): the views of the previous batch are launched deferred "
+                                "(assl_two_views_deferred_f32, UpstreamInputPipeline(lookahead=True)); every step runs all the "
+                                "kernels" if lookahead_on else "log-mel(k), statistics(k), views(k)"),
+                 "mixup_bank": ("global FIFO, bank entries read from the peers' rings over NVLink (optional mode)" if gbank
+                                else "rank-local FIFO (as each reference worker's)")},
+        "sustained": {"value": world * B * n_sus / (sus_ms * 1e-3), "unit": UNIT, "steps": n_sus, "seconds": sus_ms * 1e-3,
+                      "note": "the same step loop run for >= 2 s right after the timed region (steady-state clocks and power)"},
         "roofline": {"bound": "hbm", "kernel": "logmel_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
-                     "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
+                     "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_note, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": B * a_fe, "kernel_ms": k_ms[0],
                      "kernel_timing": f"CUDA events around each launch over {K} further steps of the same loop, right after the "
                                       f"timed region (events between the kernels would serialise their dependent launches)"},
         "pipeline_roofline": {"achieved": clips_per_s / world * a_all / 1e9, "peak": peak, "unit": "GB/s",
                               "frac": clips_per_s / world * a_all / 1e9 / peak, "bytes_per_clip": a_all},
-        "kernel_ms": {"logmel": k_ms[0], "running_stats(+gather)": k_ms[1], "two_views": k_ms[2]},
-        "e2e": {"value": world * B * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * L * 4 + B * 40,
-                "d2h_bytes_per_step": 2 * B * N_MELS * T * 4, "ms_per_step": 1e3 * e2e_s / K, "checksum": checksum,
-                "api": "assl_pipeline_host_f32 + assl_pipeline_host_sync (pinned host waveforms in, both views back to pinned host memory; uploads/kernels/downloads of consecutive calls overlap)"},
-        "gpu_launches": K * (3 if (world == 1 or exchange is not None) else 4), "clocks": clocks,
+        "kernel_ms": {"logmel(+scan of the previous batch across GPUs)": k_ms[0], "running_stats | send": k_ms[1],
+                      "two_views": k_ms[2]},
+        "e2e": {"value": world * B * n_e2e / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * L * 4 + B * 40,
+                "d2h_bytes_per_step": 2 * B * N_MELS * T * 4, "ms_per_step": 1e3 * e2e_s / n_e2e, "checksum": checksum,
+                "api": "assl_pipeline_host_f32 + assl_pipeline_host_sync (pinned host waveforms in, both views back to pinned "
+                       "host memory; uploads/kernels/downloads of consecutive calls overlap"
+                       + ("; statistics exchanged between the ranks inside every call)" if ex is not None else ")")},
+        "gpu_launches": K * launches_per_step, "clocks": clocks,
     }
+    if configs:
+        out["configs"] = configs
+    if shard_ok is not None:
+        out["sharded_equals_unsharded"] = shard_ok
+        out["sharded_check"] = {"max_abs_diff": shard_diff, "what": shard_note}
     if world == 1 and not args.no_cpu:
         arm = CpuArm(L)
         val, n_done, dt = arm.run(args.cpu_seconds)
@@ -401,6 +623,8 @@ def run_ours(args):
     _emit(json.dumps(out))
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
+    if shard_ok is False:
+        sys.exit(3)
 
 
 _REAL_STDOUT = None
@@ -430,6 +654,10 @@ def main():
     ap.add_argument("--rotate", type=int, default=4, help="distinct input batches cycled through (L2 hygiene)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="wall seconds of one CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip BASELINE configs 3-5 behind the headline")
+    ap.add_argument("--no-check", action="store_true", help="skip the sharded == unsharded check (N > 1)")
+    ap.add_argument("--presteady-s", type=float, default=1.0, help="seconds of the step loop before the timed region")
+    ap.add_argument("--sustained-s", type=float, default=2.0, help="seconds of the sustained loop")
     ap.add_argument("--lookahead", type=int, default=1,
                     help="1: software-pipelined step order log-mel(k), statistics(k), views(k-1)")
     ap.add_argument("--global-bank", action="store_true",

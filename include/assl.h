@@ -12,7 +12,8 @@
  *     pointer unless its name starts with ``host_``; the caller owns every data buffer, the
  *     library owns only the plan-lifetime constants (window, twiddles, sparse filterbank);
  *   - every call is asynchronous on ``stream`` (a ``cudaStream_t`` passed as ``void*``), never
- *     synchronises, keeps no global mutable state; a plan is immutable after creation;
+ *     synchronises, keeps no global mutable state; a plan is immutable after creation and may be shared
+ *     between threads (per-call state lives in assl_pipeline / assl_exchange objects, one caller each);
  *   - return value: 0 = ASSL_OK, otherwise an ``assl_status``; nothing throws, aborts or prints;
  *   - fp32 data, CUDA sm_100a only; there is no CPU fallback.
  *
@@ -36,7 +37,8 @@ typedef enum assl_status {
   ASSL_ERR_INVALID_ARG = 1,   /* null pointer, negative size, crop outside the canvas ...      */
   ASSL_ERR_UNSUPPORTED = 2,   /* shape/config outside what the kernels are built for           */
   ASSL_ERR_CUDA = 3,          /* allocation / copy / launch failure reported by the runtime    */
-  ASSL_ERR_NO_DEVICE = 4      /* no sm_100 device visible                                      */
+  ASSL_ERR_NO_DEVICE = 4,     /* no sm_100 device visible                                      */
+  ASSL_ERR_PEER_TIMEOUT = 5   /* a peer's statistics records did not arrive (assl_exchange_error) */
 } assl_status;
 
 /* Front-end constants: MelSpectrogramLibrosa.__init__ defaults, src/utils/utils.py:22. */
@@ -169,34 +171,59 @@ int assl_two_views_global_f32(const assl_view_cfg* cfg, const float* lms, const 
                               const int32_t* order, int64_t B, float* view1, float* view2, void* stream);
 
 /* -- running pre-normalisation across the GPUs of one node, over peer memory ----------------
- * With the batch sharded by clip (rank r owns clips [r*B, (r+1)*B) of the global order), the
- * running statistics of the reference's single stream need every rank's per-clip sums.  Instead
- * of reduce -> NCCL all-gather -> scan (three launches and a collective's latency), ONE kernel per
- * rank reduces its own clips, stores the per-clip sums straight into every peer's buffer over
- * NVLink (P2P stores of 8-byte words that each carry the call number as their own flag, like NCCL's
- * LL protocol), polls its own buffer until every rank's records show this call's number and runs
- * the scan over the global batch.  No host synchronisation, nothing but that
- * kernel on the stream.
+ * With the batch sharded by clip (rank r owns a contiguous block of the global clip order), the running
+ * statistics of the reference's single stream need every rank's per-clip sums.  Instead of reduce -> NCCL
+ * all-gather -> scan (three launches and a collective's latency) every rank stores its per-clip sums straight
+ * into every peer's buffer over NVLink (P2P stores of 8-byte words that each carry the call number as their own
+ * flag, like NCCL's LL protocol) and scans the records in its own buffer.  Ranks may bring different numbers of
+ * clips to a call (an uneven block split, a ragged last batch): a header record per sender says how many, and the
+ * scan runs over their concatenation, sender after sender.  No host synchronisation.
  *
- * assl_exchange_create   allocates this rank's buffer (room for world * max_clips per-clip sums, two
- *                        parities, 32-byte flagged records) and writes its 64-byte CUDA IPC handle to handle_out
- * assl_exchange_connect  all_handles = world * 64 bytes, rank-major (all-gather them with any host
- *                        or device collective); maps the peers' buffers.  ASSL_ERR_CUDA when the
- *                        devices cannot reach each other -- fall back to assl_clip_sums + all-gather
- * assl_running_stats_exchange  arguments as assl_running_stats, except: pair_sums [B, n_parts, 2]
- *                        are THIS rank's clips, every rank must call it with the same B, the scan
- *                        runs over world * B clips and (mean, std) of the local slice is written
- *                        (write_all != 0: of ALL world * B clips, clip g -> slot (slot0 + g) % cap -- the
- *                        global statistics ring of the global-bank mode).
- *                        A peer that does not show up within ~2 s sets state[7] = 1 (checked by
- *                        assl_exchange_error) instead of hanging the GPU.                        */
+ * assl_exchange_create   allocates this rank's buffer (world segments of max_clips + 1 flagged 32-byte records, two
+ *                        parities) and writes its 64-byte CUDA IPC handle to handle_out
+ * assl_exchange_connect  all_handles = world * 64 bytes, rank-major (all-gather them with any host or device
+ *                        collective); maps the peers' buffers.  ASSL_ERR_CUDA when the devices cannot reach each
+ *                        other: call assl_exchange_use_staging instead
+ * assl_exchange_use_staging  no peer mapping: assl_exchange_send writes this rank's segment into its OWN buffer only
+ *                        and the caller moves the segments with any collective before the scan -- all-gather
+ *                        ``segment_bytes`` from buffer + rank * segment_bytes into buffer (assl_exchange_staging
+ *                        returns both for the call sent last, back = 0, or the one before, back = 1).  Same kernels,
+ *                        same results; the fused assl_running_stats_exchange is not available
+ * assl_exchange_send     this rank's clips of one call: pair_sums [B, n_parts, 2] (0 <= B <= max_clips) -> per-clip
+ *                        totals -> its segment of every rank's buffer.  One small kernel behind the log-mel kernel;
+ *                        nobody waits in it
+ * assl_running_stats_exchange_scan   the scan of the call sent last: waits until every sender's records of that call
+ *                        are in this rank's buffer, then as assl_running_stats over their concatenation; (mean, std) of
+ *                        the local slice is written to mean_std slot (slot0 + b) % cap (write_all != 0: of ALL clips,
+ *                        global clip g -> slot (slot0 + g) % cap -- the statistics ring of the global-bank mode, which
+ *                        needs the same B on every rank).  deferred != 0: the launch does not wait for the kernel
+ *                        launched before it on the stream at its start but at its end, like assl_two_views_deferred_f32
+ *                        -- everything it depends on travels in the flagged records and in ``state`` (written by the
+ *                        previous scan, which a log-mel launch in between has already waited for).  Issued one step
+ *                        AFTER the send -- scan(k-1) . log-mel(k) . send(k) . views(k-1) -- the records have long
+ *                        landed and no rank waits for the slowest one inside a step.  A call has to be scanned before
+ *                        the next one is sent (two parities)
+ * assl_running_stats_exchange  send + scan of one call in ONE kernel (peer transport), for the ordinary step order:
+ *                        arguments as assl_running_stats, except pair_sums [B, n_parts, 2] are THIS rank's clips
+ * assl_exchange_error    ASSL_ERR_PEER_TIMEOUT once a scan gave up waiting for a peer (assl_exchange_set_timeout,
+ *                        30 s by default): that scan left the running statistics UNTOUCHED (its clips got the last
+ *                        published mean/std, state[7] = 1) and the ranks' statistics no longer agree -- treat it as
+ *                        fatal.  Reads a mapped host word the kernel sets: no synchronisation, callable every step */
 typedef struct assl_exchange assl_exchange;
 #define ASSL_EXCHANGE_HANDLE_BYTES 64
 #define ASSL_EXCHANGE_MAX_WORLD 16
 int assl_exchange_create(assl_exchange** out, int32_t rank, int32_t world, int64_t max_clips,
                          void* handle_out);
 int assl_exchange_connect(assl_exchange* x, const void* all_handles);
+int assl_exchange_use_staging(assl_exchange* x);
+int assl_exchange_staging(const assl_exchange* x, int64_t back, void** buffer, int64_t* segment_bytes);
+int assl_exchange_set_timeout(assl_exchange* x, double seconds);
+int assl_exchange_error(const assl_exchange* x);
 int assl_exchange_destroy(assl_exchange* x);
+int assl_exchange_send(assl_exchange* x, const double* pair_sums, int64_t B, int64_t n_parts, void* stream);
+int assl_running_stats_exchange_scan(assl_exchange* x, double* state, int64_t elems, int64_t max_update,
+                                     float* mean_std, int64_t slot0, int64_t cap, int32_t write_all,
+                                     int32_t deferred, void* stream);
 int assl_running_stats_exchange(assl_exchange* x, double* state, const double* pair_sums, int64_t B,
                                 int64_t n_parts, int64_t elems, int64_t max_update, float* mean_std,
                                 int64_t slot0, int64_t cap, int32_t write_all, void* stream);
@@ -274,19 +301,27 @@ int assl_affine_norm_f32(const float* x, float* y, int64_t n, float mean, float 
  * to the ring inside ``ws``).  ``ws`` is a caller-owned DEVICE workspace of at least
  * assl_pipeline_workspace_bytes(), zero-filled before first use; the ring (cap slots) and the norm state
  * live at its start and persist between calls.  Kernels run in order on ``stream``; uploads and downloads
- * run on two internal copy streams, chunked and double-buffered so that consecutive calls overlap upload,
- * kernels and download.  Every host buffer passed in must stay untouched, and host_view* is complete, only
- * after assl_pipeline_host_sync(plan) returns.  host_view* may be NULL to leave the views on the device:
+ * run on two copy streams of the pipeline object, chunked and double-buffered so that consecutive calls overlap
+ * upload, kernels and download.  Every host buffer passed in must stay untouched, and host_view* is complete, only
+ * after assl_pipeline_host_sync() returns.  host_view* may be NULL to leave the views on the device:
  * their device addresses are returned through dev_view1/2 and are valid in ``stream`` order until the call
- * after next.  One caller at a time per plan for these two entry points.                               */
+ * after next.
+ * assl_pipeline_create: the pipeline object holds the copy streams, events and the call parity (the plan stays
+ * immutable and shareable); one caller at a time per PIPELINE.  ``exchange`` (may be NULL) is the connected
+ * peer-transport statistics exchange of a clip-sharded multi-GPU run: every call then runs the fused send + scan
+ * (assl_running_stats_exchange) over all ranks' clips instead of the local scan, and every rank must make the
+ * same sequence of calls.                                                                                 */
+typedef struct assl_pipeline assl_pipeline;
+int assl_pipeline_create(assl_pipeline** out, const assl_plan* plan, assl_exchange* exchange);
+int assl_pipeline_destroy(assl_pipeline* pipe);
 int64_t assl_pipeline_workspace_bytes(const assl_plan* plan, int64_t B, int64_t L, int64_t cap);
-int assl_pipeline_host_f32(const assl_plan* plan, const assl_view_cfg* vcfg, void* ws,
+int assl_pipeline_host_f32(assl_pipeline* pipe, const assl_view_cfg* vcfg, void* ws,
                            int64_t ws_bytes, const float* host_wave, int64_t B, int64_t L,
                            int64_t slot0, int64_t cap, int64_t max_update,
                            const int32_t* host_mix_slot, const float* host_alpha,
                            const int32_t* host_crop, float* host_view1, float* host_view2,
                            float** dev_view1, float** dev_view2, void* stream);
-int assl_pipeline_host_sync(const assl_plan* plan);
+int assl_pipeline_host_sync(assl_pipeline* pipe);
 
 #ifdef __cplusplus
 }

@@ -1,18 +1,25 @@
-"""Multi-GPU check of the statistics exchange (not collected by pytest; needs >= 2 GPUs):
+"""Multi-GPU check of the statistics exchange (not collected by pytest; needs >= 2 GPUs on one node):
 
-    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29531 \
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29531 \
         tests/multigpu_check.py
 
-1. the peer-memory path (assl_running_stats_exchange) == the NCCL path (assl_clip_sums + all-gather +
-   assl_running_stats) == one process scanning the whole batch, bit for bit, over several steps (both parities,
-   carries, a smaller last batch);
+1. the fused peer-memory exchange (assl_running_stats_exchange) == the split form (assl_exchange_send, then
+   assl_running_stats_exchange_scan) == the staged transport (same kernels, records moved by an all-gather) == a
+   hand-made NCCL path (assl_clip_sums + all-gather + assl_running_stats) == one process scanning the whole batch,
+   bit for bit, over several steps (both parities, carries, a smaller last batch);
+1b. ranks that bring DIFFERENT numbers of clips to a call (uneven block split) == one process on the concatenation;
 2. the sharded front end + views (mixup off, explicit crops) == one process on the unsharded batch;
 3. global-bank mode (mixup ON, bank entries read from the peers' rings over NVLink) == one process on the
-   unsharded batch, bit for bit, over 9 steps.
+   unsharded batch, bit for bit, over 9 steps;
+4. lookahead order across GPUs (scan(k-1) . log-mel(k) . send(k) . views(k-1)) == the ordinary order;
+5. NormalizeBatch(sync=True) over the ranks == one process on the concatenated batch;
+6. a rank that shows up 2.5 s late is waited for (no error, same result); with the timeout set to 0.5 s the waiting
+   ranks leave their statistics untouched and ``check()`` raises.
 """
 import ctypes as C
 import os
 import sys
+import time
 
 import numpy as np
 import torch
@@ -34,34 +41,62 @@ def main():
     st = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)   # noqa: E731
 
     ex = StatsExchange.open(300, dev)
-    assert ex is not None, "peer-memory exchange unavailable on this box"
+    assert ex is not None and not ex.staged, "peer-memory exchange unavailable on this box"
+    ex_split = StatsExchange.open(300, dev)
+    os.environ["ASSL_STATS_EXCHANGE"] = "nccl"
+    ex_staged = StatsExchange.open(300, dev)
+    del os.environ["ASSL_STATS_EXCHANGE"]
+    assert ex_staged.staged
     parts, elems, cap, max_update = 7, 640, 4096, 1500
-    state = {k: torch.zeros(8, dtype=torch.float64, device=dev) for k in "abc"}
-    stats = {k: torch.zeros((cap, 2), dtype=torch.float32, device=dev) for k in "abc"}
+    names = "abcde"
+    state = {k: torch.zeros(8, dtype=torch.float64, device=dev) for k in names}
+    stats = {k: torch.zeros((cap, 2), dtype=torch.float32, device=dev) for k in names}
     g = torch.Generator(device="cpu").manual_seed(7)
     done = 0
     for step, b in enumerate([300, 300, 300, 129, 300, 1]):
         allsums = torch.rand((world, b, parts, 2), generator=g, dtype=torch.float64) * 50 + 1   # same on every rank
         mine = allsums[rank].to(dev)
         slot0 = done % cap
-        ex.run(state["a"], mine, b, parts, elems, max_update, stats["a"], slot0, cap)
-        local = torch.empty((b, 2), dtype=torch.float64, device=dev)
+        ex.run(state["a"], mine, b, parts, elems, max_update, stats["a"], slot0, cap)                       # fused
+        local = torch.empty((b, 2), dtype=torch.float64, device=dev)                                        # hand-made NCCL
         _native.check(lib.assl_clip_sums(P(mine), b, parts, P(local), st()))
         gathered = gather_clip_sums(local)
         _native.check(lib.assl_running_stats(P(state["b"]), P(gathered), world * b, 1, elems, max_update, rank * b, b,
                                              P(stats["b"]), slot0, cap, st()))
-        whole = allsums.reshape(world * b, parts, 2).to(dev)
+        whole = allsums.reshape(world * b, parts, 2).to(dev)                                                # one process
         _native.check(lib.assl_running_stats(P(state["c"]), P(whole), world * b, parts, elems, max_update, rank * b, b,
                                              P(stats["c"]), slot0, cap, st()))
+        ex_split.send(mine, b, parts)                                                                      # split
+        ex_split.scan(state["d"], elems, max_update, stats["d"], slot0, cap, deferred=bool(step & 1))
+        ex_staged.run(state["e"], mine, b, parts, elems, max_update, stats["e"], slot0, cap)               # staged transport
         torch.cuda.synchronize()
-        for k in "bc":
+        for k in names[1:]:
             assert torch.equal(state["a"], state[k]), (step, k, state["a"], state[k])
             assert torch.equal(stats["a"], stats[k]), (step, k)
         assert float(state["a"][7]) == 0.0
         done += b
     assert float(state["a"][0]) == min(done * world, max_update)
+    for e in (ex, ex_split, ex_staged):
+        e.check()
 
-    # ---- sharded pipeline vs one process
+    # ---- 1b. uneven block split: rank r brings 40 + 3 r clips (and nothing at all in one step)
+    sa, sb = (torch.zeros(8, dtype=torch.float64, device=dev) for _ in range(2))
+    ta, tb = (torch.zeros((cap, 2), dtype=torch.float32, device=dev) for _ in range(2))
+    for step in range(4):
+        counts = [40 + 3 * r if (step != 2 or r != world - 1) else 0 for r in range(world)]
+        every = [torch.rand((c, parts, 2), generator=g, dtype=torch.float64) * 50 + 1 for c in counts]
+        mine = every[rank].to(dev) if counts[rank] else torch.zeros((1, parts, 2), dtype=torch.float64, device=dev)
+        ex_split.send(mine, counts[rank], parts)
+        ex_split.scan(sa, elems, max_update, ta, 100 * step, cap)
+        whole = torch.cat(every).to(dev)
+        first = sum(counts[:rank])
+        _native.check(lib.assl_running_stats(P(sb), P(whole), sum(counts), parts, elems, max_update, first, counts[rank],
+                                             P(tb), 100 * step, cap, st()))
+        torch.cuda.synchronize()
+        assert torch.equal(sa, sb) and torch.equal(ta, tb), ("uneven", step)
+    ex_split.check()
+
+    # ---- 2. sharded pipeline vs one process
     cfg = {"pretrain": {"normalization": "mean_var", "input": {"length_wave": 0.5},
                         "augmentations": {"RandomResizeCrop": {"virtual_crop_scale": [1.0, 1.5], "freq_crop_scale": [0.6, 1.5],
                                                                "time_crop_scale": [0.6, 1.5]}}}}
@@ -77,7 +112,7 @@ def main():
     w1, w2 = single(wave, params=params)
     torch.cuda.synchronize()
     assert torch.equal(v1, w1[rank * b:(rank + 1) * b]) and torch.equal(v2, w2[rank * b:(rank + 1) * b])
-    # ---- global bank: mixup picks over the GLOBAL clip order, bank entries read from the peers' rings over NVLink.
+    # ---- 3. global bank: mixup picks over the GLOBAL clip order, bank entries read from the peers' rings over NVLink.
     #      9 steps: the ring (steps_back + 2 steps deep) wraps, picks reach back several steps and across ranks.
     cfg_mix = {"pretrain": {"normalization": "mean_var", "input": {"length_wave": 0.5},
                             "augmentations": {"MixupBYOLA": {"ratio": 0.4, "log_mixup_exp": True},
@@ -95,8 +130,9 @@ def main():
         src = sharded.tfms.last_params.src_clip
         remote += int(np.sum((src >= 0) & ((src % (world * b)) // b != rank)))
     assert remote > 0                                             # bank entries really came from other GPUs
-    # ---- lookahead step order across GPUs: the deferred views of batch k-1 run beside the statistics EXCHANGE of batch k.
-    #      Sharded lookahead pipeline (rank-local banks, global statistics) == the same pipeline in the ordinary order.
+    # ---- 4. lookahead step order across GPUs: scan(k-1) . log-mel(k) . send(k) . views(k-1), the deferred views of batch
+    #      k-1 beside the log-mel tail of batch k.  Sharded lookahead pipeline (rank-local banks, global statistics) == the
+    #      same pipeline in the ordinary order (fused exchange).
     import random
     rng_state = (np.random.get_state(), random.getstate())
     batches = [(torch.randn(b, 8000, generator=g) * 0.1).to(dev) for _ in range(14)]          # > 1024 clips: the bank wraps
@@ -105,18 +141,63 @@ def main():
     want = [plain(w) for w in batches]
     np.random.seed(31 + rank); random.seed(31 + rank)
     look = A.UpstreamInputPipeline(cfg_mix, 10 ** 6, max_batch=b, lookahead=True)
+    assert look.tfms.engine.split_stats
     got = [look(w) for w in batches][1:] + [look.flush()]
     torch.cuda.synchronize()
     assert look.tfms.engine._exchange is not None
     for (a1, a2), (b1, b2) in zip(got, want):
         assert torch.equal(a1, b1) and torch.equal(a2, b2)
+    assert torch.equal(look.tfms.engine.state, plain.tfms.engine.state)
     np.random.set_state(rng_state[0]); random.setstate(rng_state[1])
     assert float(sharded.tfms.engine.state[7]) == 0.0
+    look.tfms.engine.check_exchange()
+
+    # ---- 5. NormalizeBatch(sync=True): global batch statistics (optional mode)
+    x = torch.randn(world * 24, 1, 64, 51, generator=g).to(dev) * 3 + 1
+    y = A.NormalizeBatch(sync=True)(x[rank * 24:(rank + 1) * 24])
+    want_y = (x - x.mean()) / x.std().clamp(torch.finfo().eps, torch.finfo().max)
+    torch.cuda.synchronize()
+    assert torch.allclose(y, want_y[rank * 24:(rank + 1) * 24], rtol=1e-5, atol=1e-5)
+
+    # ---- 6. a late rank.  (a) 2.5 s late with the default timeout: waited for, same statistics as everyone.
     dist.barrier()
-    ex.close()
+    sl, tl = torch.zeros(8, dtype=torch.float64, device=dev), torch.zeros((cap, 2), dtype=torch.float32, device=dev)
+    allsums = torch.rand((world, 50, parts, 2), generator=g, dtype=torch.float64) * 50 + 1
+    if rank == world - 1:
+        time.sleep(2.5)
+    ex.run(sl, allsums[rank].to(dev), 50, parts, elems, max_update, tl, 0, cap)
+    torch.cuda.synchronize()
+    ex.check()
+    ref_s, ref_t = torch.zeros_like(sl), torch.zeros_like(tl)
+    _native.check(lib.assl_running_stats(P(ref_s), P(allsums.reshape(world * 50, parts, 2).to(dev)), world * 50, parts, elems,
+                                         max_update, rank * 50, 50, P(ref_t), 0, cap, st()))
+    torch.cuda.synchronize()
+    assert torch.equal(sl, ref_s) and torch.equal(tl, ref_t)
+    #      (b) timeout 0.5 s, last rank 2 s late: the waiting ranks give up, leave their statistics untouched, raise.
+    dist.barrier()
+    ex.set_timeout(0.5)
+    before = sl.clone()
+    if rank == world - 1:
+        time.sleep(2.0)
+    ex.run(sl, allsums[rank].to(dev), 50, parts, elems, max_update, tl, 0, cap)
+    torch.cuda.synchronize()
+    raised = False
+    try:
+        ex.check()
+    except RuntimeError:
+        raised = True
+    if rank == world - 1:
+        assert not raised and float(sl[7]) == 0.0            # everyone else's records were there long before
+    else:
+        assert raised and float(sl[7]) == 1.0
+        assert torch.equal(sl[:5], before[:5])               # n_put, carries, mean, std: untouched
+    dist.barrier()
+    for e in (ex, ex_split, ex_staged):
+        e.close()
     if rank == 0:
-        print(f"multigpu_check: OK on {world} GPUs (peer exchange == NCCL path == single stream, bit for bit; "
-              f"global bank == unsharded run, {remote} remote bank entries on rank 0; lookahead order == ordinary order)")
+        print(f"multigpu_check: OK on {world} GPUs (fused == split == staged == NCCL path == single stream, bit for bit; "
+              f"uneven shards; global bank == unsharded run, {remote} remote bank entries on rank 0; lookahead order == "
+              f"ordinary order; NormalizeBatch(sync); late rank waited for / timeout raised)")
     dist.destroy_process_group()
 
 

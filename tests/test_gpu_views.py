@@ -186,7 +186,8 @@ def test_c_abi_host_pipeline_matches_device_pipeline():
     plan = pipe.plan
     T = plan.num_frames(L)
     cap = pipe.tfms.engine.cap
-    ws_bytes = lib.assl_pipeline_workspace_bytes(plan.handle, B, L, cap)
+    host = A.HostPipeline(plan)
+    ws_bytes = host.workspace_bytes(B, L, cap)
     assert ws_bytes > 0
     ws = torch.zeros(ws_bytes, dtype=torch.uint8, device="cuda")
     vcfg = _native.ViewCfg(64, T, 64, int(T * 1.5), 0, 1)
@@ -200,12 +201,8 @@ def test_c_abi_host_pipeline_matches_device_pipeline():
         mix = np.where(p.src_clip >= 0, p.src_clip % cap, -1).astype(np.int32)
         alpha, crop = np.ascontiguousarray(p.alpha), np.ascontiguousarray(p.crop)
         keep.append((mix, alpha, crop))
-        _native.check(lib.assl_pipeline_host_f32(
-            plan.handle, C.byref(vcfg), C.c_void_p(ws.data_ptr()), ws_bytes, C.c_void_p(waves[k].data_ptr()), B, L,
-            (k * B) % cap, cap, 2 * 5 * 10, mix.ctypes.data_as(C.c_void_p), alpha.ctypes.data_as(C.c_void_p),
-            crop.ctypes.data_as(C.c_void_p), C.c_void_p(hv[k][0].data_ptr()), C.c_void_p(hv[k][1].data_ptr()),
-            None, None, st))
-    _native.check(lib.assl_pipeline_host_sync(plan.handle))
+        host.run(vcfg, ws, waves[k], B, L, (k * B) % cap, cap, 2 * 5 * 10, mix, alpha, crop, hv[k][0], hv[k][1], stream=st)
+    host.sync()
     torch.cuda.synchronize()
     for k in range(calls):
         # chunked statistics scans may round the running mean/std differently in the last bit

@@ -18,7 +18,8 @@ plan = A.Plan()
 T = plan.num_frames(L)
 cap = 2048
 vcfg = _native.ViewCfg(64, T, 64, int(T * 1.5), 0, 1)
-ws_bytes = lib.assl_pipeline_workspace_bytes(plan.handle, B, L, cap)
+pipe = A.HostPipeline(plan)
+ws_bytes = pipe.workspace_bytes(B, L, cap)
 ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
 ws[:64].zero_()
 g = torch.Generator().manual_seed(1)
@@ -45,20 +46,17 @@ def loop(download=True, ahead=False):
         t = time.perf_counter()
         mix, alpha, crop = pre[s] if ahead else params(s)
         keep.append((mix, alpha, crop))
-        _native.check(lib.assl_pipeline_host_f32(
-            plan.handle, C.byref(vcfg), C.c_void_p(ws.data_ptr()), ws_bytes, C.c_void_p(waves[s % 4].data_ptr()), B, L,
-            (s * B) % cap, cap, 10 ** 9, mix.ctypes.data_as(C.c_void_p), alpha.ctypes.data_as(C.c_void_p),
-            crop.ctypes.data_as(C.c_void_p), C.c_void_p(hv1.data_ptr()) if download else None,
-            C.c_void_p(hv2.data_ptr()) if download else None, None, None, st()))
+        pipe.run(vcfg, ws, waves[s % 4], B, L, (s * B) % cap, cap, 10 ** 9, mix, alpha, crop,
+                 hv1 if download else None, hv2 if download else None, stream=st())
         host_ms += time.perf_counter() - t
     for s in range(W):
         step(s)
-    lib.assl_pipeline_host_sync(plan.handle); torch.cuda.synchronize()
+    pipe.sync(); torch.cuda.synchronize()
     host_ms = 0.0
     t0 = time.perf_counter()
     for s in range(W, W + K):
         step(s)
-    lib.assl_pipeline_host_sync(plan.handle); torch.cuda.synchronize()
+    pipe.sync(); torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     print(f"download={download!s:5} ahead={ahead!s:5}  {1e3 * dt / K:6.3f} ms/step  {B * K / dt / 1e3:7.1f} k clips/s  "
           f"H2D {B * L * 4 * K / dt / 1e9:5.1f} GB/s  host enqueue {1e3 * host_ms / K:5.3f} ms/step")

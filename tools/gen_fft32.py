@@ -1,21 +1,17 @@
 #!/usr/bin/env python3
-"""Generator for ``audio-ssl_b200/csrc/fft32_gen.cuh``: a fully unrolled, register-resident
-32-point complex FFT (forward, e^{-2 pi i jk/32}) written as straight-line FFMA/FADD code.
+"""Generator for ``audio-ssl_b200/csrc/fft32p_gen.cuh``: a fully unrolled, register-resident 32-point complex FFT
+(forward, e^{-2 pi i jk/32}) on {re, im} register pairs, written as straight-line two-wide FP32 code.
 
 The op list is built once and has two back ends:
-  * ``emit_cuda``  -- prints the CUDA device function;
-  * ``run_numpy``  -- executes the very same ops on float32 numpy arrays (FMA modelled as
-    float64 multiply-add rounded once), so the emitted arithmetic can be checked against
-    numpy's FFT in this GPU-less container (tests/test_fft32_codegen.py).
+  * ``emit_cuda_packed`` -- prints the CUDA device function;
+  * ``run_numpy_packed`` -- executes the very same ops on float32 numpy arrays (FMA modelled as float64
+    multiply-add rounded once), so the emitted arithmetic can be checked against numpy's FFT in this GPU-less
+    container (tests/test_fft32_codegen.py).
 
-Algorithm: radix-2 decimation in time, natural-order in, natural-order out (the bit-reversal is
-a renaming of registers).  Butterflies use the 6-instruction form
-    o1 = a + W*b   (2 FFMA per component)
-    o2 = 2a - o1   (1 FFMA per component)
-and the trivial twiddles (1, -i, (+-1-i)/sqrt2) are specialised.  Per 32-point transform:
-46 trivial butterflies x 4 FADD + 34 twiddled butterflies x 6 = 388 instructions.
+Algorithm: radix-2 decimation in time, natural-order in, natural-order out (the bit-reversal is a renaming of
+registers); the trivial twiddles (1, -i, (+-1-i)/sqrt2) are specialised.
 
-Usage:  python tools/gen_fft32.py > audio-ssl_b200/csrc/fft32_gen.cuh
+Usage:  python tools/gen_fft32.py > audio-ssl_b200/csrc/fft32p_gen.cuh
 """
 import math
 import sys
@@ -33,132 +29,14 @@ def bitrev(i, bits):
     return r
 
 
-class Prog:
-    """SSA op list.  Values are names (str); constants are python floats."""
-
-    def __init__(self):
-        self.ops = []          # (dst, kind, args)
-        self.n = 0
-
-    def _new(self):
-        self.n += 1
-        return f"t{self.n}"
-
-    def add(self, a, b):
-        d = self._new(); self.ops.append((d, "add", (a, b))); return d
-
-    def sub(self, a, b):
-        d = self._new(); self.ops.append((d, "sub", (a, b))); return d
-
-    def fma(self, a, b, c, neg_c=False):
-        """a may be a float constant or a name; computes a*b + (-c if neg_c else c)."""
-        d = self._new(); self.ops.append((d, "fma", (a, b, c, neg_c))); return d
-
-
-def build_fft32():
-    p = Prog()
-    bits = 5
-    re = [f"re[{bitrev(i, bits)}]" for i in range(N)]
-    im = [f"im[{bitrev(i, bits)}]" for i in range(N)]
-    m = 2
-    while m <= N:
-        half = m // 2
-        for s in range(0, N, m):
-            for j in range(half):
-                ia, ib = s + j, s + j + half
-                ar, ai, br, bi = re[ia], im[ia], re[ib], im[ib]
-                # W = exp(-2 pi i j / m)
-                if j == 0:
-                    o1r, o1i = p.add(ar, br), p.add(ai, bi)
-                    o2r, o2i = p.sub(ar, br), p.sub(ai, bi)
-                elif 4 * j == m:            # W = -i : t = (bi, -br)
-                    o1r, o1i = p.add(ar, bi), p.sub(ai, br)
-                    o2r, o2i = p.sub(ar, bi), p.add(ai, br)
-                elif 8 * j == m:            # W = (1 - i)/sqrt2 : t = c*(br+bi, bi-br)
-                    c = math.sqrt(0.5)
-                    s1, s2 = p.add(br, bi), p.sub(bi, br)
-                    o1r, o1i = p.fma(c, s1, ar), p.fma(c, s2, ai)
-                    o2r, o2i = p.fma(-c, s1, ar), p.fma(-c, s2, ai)
-                elif 8 * j == 3 * m:        # W = (-1 - i)/sqrt2 : t = c*(bi-br, -(br+bi))
-                    c = math.sqrt(0.5)
-                    s1, s2 = p.add(br, bi), p.sub(bi, br)
-                    o1r, o1i = p.fma(c, s2, ar), p.fma(-c, s1, ai)
-                    o2r, o2i = p.fma(-c, s2, ar), p.fma(c, s1, ai)
-                else:
-                    ang = -2.0 * math.pi * j / m
-                    wr, wi = math.cos(ang), math.sin(ang)
-                    x = p.fma(-wi, bi, ar)
-                    o1r = p.fma(wr, br, x)
-                    y = p.fma(wi, br, ai)
-                    o1i = p.fma(wr, bi, y)
-                    o2r = p.fma(2.0, ar, o1r, neg_c=True)
-                    o2i = p.fma(2.0, ai, o1i, neg_c=True)
-                re[ia], im[ia], re[ib], im[ib] = o1r, o1i, o2r, o2i
-        m *= 2
-    return p, re, im
-
-
-def f32(x):
-    return np.float32(x)
-
-
-def run_numpy(re_in, im_in):
-    """Execute the op list on float32 arrays of shape [32, ...]; returns (re, im) [32, ...]."""
-    p, ore, oim = build_fft32()
-    env = {}
-    for i in range(N):
-        env[f"re[{i}]"] = np.asarray(re_in[i], np.float32)
-        env[f"im[{i}]"] = np.asarray(im_in[i], np.float32)
-
-    def val(a):
-        return env[a] if isinstance(a, str) else np.float32(a)
-
-    for d, kind, args in p.ops:
-        if kind == "add":
-            env[d] = (val(args[0]) + val(args[1])).astype(np.float32)
-        elif kind == "sub":
-            env[d] = (val(args[0]) - val(args[1])).astype(np.float32)
-        else:
-            a, b, c, neg = args
-            cc = val(c).astype(np.float64)
-            r = val(a).astype(np.float64) * val(b).astype(np.float64) + (-cc if neg else cc)
-            env[d] = r.astype(np.float32)
-    return np.stack([env[n] for n in ore]), np.stack([env[n] for n in oim])
-
-
 def lit(c):
     return f"{np.float32(c)!r}".replace("np.float32(", "").rstrip(")") + "f"
-
-
-def emit_cuda(out=sys.stdout):
-    p, ore, oim = build_fft32()
-    w = out.write
-    w("// GENERATED by tools/gen_fft32.py -- do not edit; regenerate instead.\n")
-    w("// 32-point forward complex FFT, natural order in and out, all operands in registers.\n")
-    n_fma = sum(1 for o in p.ops if o[1] == "fma")
-    w(f"// {len(p.ops)} floating-point instructions ({n_fma} FFMA, {len(p.ops) - n_fma} FADD).\n")
-    w("#pragma once\n\nnamespace assl {\n\n")
-    w("__device__ __forceinline__ void fft32(float (&re)[32], float (&im)[32]) {\n")
-    for d, kind, args in p.ops:
-        if kind == "add":
-            w(f"  const float {d} = {args[0]} + {args[1]};\n")
-        elif kind == "sub":
-            w(f"  const float {d} = {args[0]} - {args[1]};\n")
-        else:
-            a, b, c, neg = args
-            aa = lit(a) if not isinstance(a, str) else a
-            w(f"  const float {d} = __fmaf_rn({aa}, {b}, {'-' if neg else ''}{c});\n")
-    for i in range(N):
-        w(f"  re[{i}] = {ore[i]}; im[{i}] = {oim[i]};\n")
-    w("}\n\n}  // namespace assl\n")
-
 
 
 # ---------------------------------------------------------------------------------------------------
 # Packed variant: one 64-bit register pair holds {re, im} of a point and every butterfly is written
 # with the sm_100 two-wide FP32 instructions (fma/add/sub.rn.f32x2 -> SASS FFMA2 / FADD2, whose
-# operand modifiers swap and negate halves for free).  Same radix-2 DIT network and the same roundings
-# per component as the scalar version:
+# operand modifiers swap and negate halves for free):
 #     W = 1      o1 = a + b                       o2 = a - b                        (2 instr)
 #     W = -i     o1 = a + {bi, -br}               o2 = a - {bi, -br}                (2)
 #     W = c(1-i) s  = b + {bi, -br}               o1 = a + c s      o2 = a - c s    (3)
@@ -242,7 +120,7 @@ def run_numpy_packed(re_in, im_in):
 def emit_cuda_packed(out=sys.stdout):
     ops, res = build_fft32_packed()
     w = out.write
-    w("// GENERATED by tools/gen_fft32.py --packed -- do not edit; regenerate instead.\n")
+    w("// GENERATED by tools/gen_fft32.py -- do not edit; regenerate instead.\n")
     w("// 32-point forward complex FFT on {re, im} register pairs, natural order in and out.\n")
     w(f"// {len(ops)} two-wide FP32 instructions (FFMA2 / FADD2); helpers in f32x2.cuh.\n")
     w("#pragma once\n\n#include \"f32x2.cuh\"\n\nnamespace assl {\n\n")
@@ -262,7 +140,4 @@ def emit_cuda_packed(out=sys.stdout):
 
 
 if __name__ == "__main__":
-    if "--packed" in sys.argv:
-        emit_cuda_packed()
-    else:
-        emit_cuda()
+    emit_cuda_packed()
