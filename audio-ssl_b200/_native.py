@@ -50,7 +50,7 @@ class Cfg(C.Structure):
 
 class ViewCfg(C.Structure):
     _fields_ = [("n_freq", C.c_int32), ("n_time", C.c_int32), ("canvas_h", C.c_int32),
-                ("canvas_w", C.c_int32), ("interp", C.c_int32), ("log_mixup", C.c_int32)]
+                ("canvas_w", C.c_int32), ("interp", C.c_int32), ("log_mixup", C.c_int32), ("ring_pitch", C.c_int32)]
 
 
 _P, _I64, _F = C.c_void_p, C.c_int64, C.c_float
@@ -63,6 +63,7 @@ SIGNATURES = {
     "assl_plan_num_tiles": (_I64, [_P, _I64]),
     "assl_plan_filterbank": (C.c_int, [_P, _P]),
     "assl_logmel_f32": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _P, _I64, _I64, _P, C.c_int32, _P]),
+    "assl_logmel_pitched_f32": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _P, _I64, _I64, _I64, _P, C.c_int32, _P]),
     "assl_clip_moments_f32": (C.c_int, [_P, _I64, _I64, _P, _P]),
     "assl_clip_normalize_f32": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _I64, _P]),
     "assl_wave_l2_gain_f32": (C.c_int, [_P, _I64, _I64, _I64, _P, _P]),

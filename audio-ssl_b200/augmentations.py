@@ -176,9 +176,9 @@ class RandomResizeCrop(nn.Module):
         eng = ViewEngine(n_memory=0, pushes_per_clip=1, virtual_crop_scale=self.virtual_crop_scale,
                          interp=self.interpolation, normalize=False, max_batch=max(b, 1))
         with torch.cuda.device(x.device):
-            eng.f, eng.t = f, t
+            eng.f, eng.t, eng.pitch = f, t, t
             eng.cap = b
-            eng.ring, eng.stats = x.contiguous(), None           # the input itself is the "ring"
+            eng.ring, eng.stats = x.contiguous(), None           # the input itself is the "ring" (dense rows)
             v1, _ = eng.launch_views(params, b, x.device)
         return v1[:, 0] if single else v1
 

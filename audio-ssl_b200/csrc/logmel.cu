@@ -62,6 +62,7 @@ struct LogmelArgs {
   double* pair_sums;  // [B, ppc, 2] (sum, sum^2) of what each frame pair wrote, or null
   long long L, ld, slot0, cap;
   int B, T, hop, n_mels, out_kind, bulk_ok;
+  int pitch;          // floats per output row ([n_mels, pitch] slots; T for dense rows)
   int ppc;            // frame pairs per clip = ceil(T / 2)
   unsigned ppc_mul;   // n / ppc == (t + ((n - t) >> ppc_sh1)) >> ppc_sh2 with t = umulhi(ppc_mul, n)
   int ppc_sh1, ppc_sh2;
@@ -403,8 +404,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
     long long slot = a.slot0 + clip;
     if (a.cap > 0 && slot >= a.cap) slot -= a.cap;
     const bool power = a.out_kind & 1, tmajor = a.out_kind & 2;      // [n_mels, T] rows, or time-major [T, n_mels]
-    const int band_stride = tmajor ? 1 : a.T, frame_stride = tmajor ? a.n_mels : 1;
-    float* dst = a.lms + slot * (static_cast<long long>(a.n_mels) * a.T) + (tmajor ? ta * a.n_mels : ta) + lane * band_stride;
+    const int band_stride = tmajor ? 1 : a.pitch, frame_stride = tmajor ? a.n_mels : 1;
+    float* dst = a.lms + slot * (static_cast<long long>(a.n_mels) * a.pitch) + (tmajor ? ta * a.n_mels : ta) + lane * band_stride;
     float g2 = 1.f;
     if (a.gain) { const float g = a.gain[clip]; g2 = g * g; }   // |g x|^2 = g^2 |x|^2: per-clip gain applied here
     float s1 = 0.f, s2 = 0.f;
@@ -478,6 +479,12 @@ extern "C" int64_t assl_plan_num_tiles(const assl_plan* p, int64_t n_samples) {
 extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const float* wave_gain, int64_t B,
                                int64_t L, int64_t ld, float* lms, int64_t slot0, int64_t cap,
                                double* tile_sums, int32_t out_kind, void* stream) {
+  return assl_logmel_pitched_f32(p, wave, wave_gain, B, L, ld, lms, slot0, cap, 0, tile_sums, out_kind, stream);
+}
+
+extern "C" int assl_logmel_pitched_f32(const assl_plan* p, const float* wave, const float* wave_gain, int64_t B,
+                                       int64_t L, int64_t ld, float* lms, int64_t slot0, int64_t cap, int64_t pitch,
+                                       double* tile_sums, int32_t out_kind, void* stream) {
   using namespace assl;
   if (out_kind < 0 || out_kind > 3) return ASSL_ERR_INVALID_ARG;
   if (!p || !wave || !lms || B < 0 || ld < L || slot0 < 0 || cap < 0) return ASSL_ERR_INVALID_ARG;
@@ -486,7 +493,10 @@ extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const floa
   if (tile_sums && reinterpret_cast<uintptr_t>(tile_sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;
   if (B == 0) return ASSL_OK;
   const int64_t T = 1 + L / p->cfg.hop;
+  if (pitch == 0) pitch = T;
+  if (pitch < T || pitch > (1ll << 30) || ((out_kind & 2) && pitch != T)) return ASSL_ERR_INVALID_ARG;   // time-major slots are dense
   LogmelArgs a;
+  a.pitch = static_cast<int>(pitch);
   a.ppc = static_cast<int>((T + 1) / 2);
   const int64_t total_pairs = B * a.ppc;
   if (T > (1ll << 24) || total_pairs > (1ll << 30) || L > (1ll << 31) - 4096) return ASSL_ERR_UNSUPPORTED;

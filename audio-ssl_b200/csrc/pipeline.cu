@@ -17,6 +17,8 @@ namespace {
 
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
+inline int64_t ring_pitch(int64_t T) { return (T + 3) & ~static_cast<int64_t>(3); }   // 16-byte aligned ring rows
+
 struct WsLayout {
   size_t state, stats_ring, lms_ring, tile_sums, clip_slot, mix_slot, alpha, crop, wave[2], view1[2], view2[2], total;
 };
@@ -25,11 +27,12 @@ WsLayout layout(const assl_plan* p, int64_t B, int64_t L, int64_t cap) {
   const int64_t T = 1 + L / p->cfg.hop;
   const int64_t parts = assl_plan_num_tiles(p, L);
   const size_t plane = static_cast<size_t>(p->cfg.n_mels) * T * sizeof(float);
+  const size_t ring_plane = static_cast<size_t>(p->cfg.n_mels) * ring_pitch(T) * sizeof(float);
   WsLayout w;
   size_t o = 0;
   w.state = o;      o = align_up(o + 8 * sizeof(double));
   w.stats_ring = o; o = align_up(o + static_cast<size_t>(cap) * 2 * sizeof(float));
-  w.lms_ring = o;   o = align_up(o + static_cast<size_t>(cap) * plane);
+  w.lms_ring = o;   o = align_up(o + static_cast<size_t>(cap) * ring_plane);
   w.tile_sums = o;  o = align_up(o + static_cast<size_t>(B) * parts * 2 * sizeof(double));
   w.clip_slot = o;  o = align_up(o + static_cast<size_t>(B) * sizeof(int32_t));
   w.mix_slot = o;   o = align_up(o + 2 * static_cast<size_t>(B) * 2 * sizeof(int32_t));   // x2: double-buffered
@@ -118,6 +121,8 @@ extern "C" int assl_pipeline_host_f32(assl_pipeline* pipe, const assl_view_cfg* 
   if (vc->n_freq != p->cfg.n_mels || vc->n_time != T) return ASSL_ERR_INVALID_ARG;
   const WsLayout w = layout(p, B, L, cap);
   if (static_cast<size_t>(ws_bytes) < w.total) return ASSL_ERR_INVALID_ARG;
+  assl_view_cfg vcr = *vc;
+  vcr.ring_pitch = static_cast<int32_t>(ring_pitch(T));            // the ring lives in the workspace: its layout is ours
   int rc = ASSL_OK;
   cudaStream_t st = as_stream(stream);
   const int par = static_cast<int>(pipe->calls & 1);
@@ -171,13 +176,14 @@ extern "C" int assl_pipeline_host_f32(assl_pipeline* pipe, const assl_view_cfg* 
     ok = ok && cudaEventRecord(pipe->ev_in[c], pipe->s_in) == cudaSuccess;
     ok = ok && cudaStreamWaitEvent(st, pipe->ev_in[c], 0) == cudaSuccess;
     const int64_t s0 = (slot0 + b0) % cap;
-    rc = assl_logmel_f32(p, wave + b0 * L, nullptr, nb, L, L, lms, s0, cap, tsums + b0 * n_parts * 2, 0, stream);
+    rc = assl_logmel_pitched_f32(p, wave + b0 * L, nullptr, nb, L, L, lms, s0, cap, ring_pitch(T), tsums + b0 * n_parts * 2, 0,
+                                 stream);
     if (rc == ASSL_OK && pipe->exchange)   // sharded run: this rank's clips + every peer's, in global clip order
       rc = assl_running_stats_exchange(pipe->exchange, state, tsums, nb, n_parts, elems, max_update, stats, s0, cap, 0, stream);
     else if (rc == ASSL_OK)
       rc = assl_running_stats(state, tsums + b0 * n_parts * 2, nb, n_parts, elems, max_update, 0, nb, stats, s0, cap, stream);
     if (rc == ASSL_OK)
-      rc = assl_two_views_f32(vc, lms, stats, cap, clip_slot + b0, mix_slot + b0 * 2, alpha + b0 * 2, crop + b0 * 8, nb,
+      rc = assl_two_views_f32(&vcr, lms, stats, cap, clip_slot + b0, mix_slot + b0 * 2, alpha + b0 * 2, crop + b0 * 8, nb,
                               v1 + b0 * elems, v2 + b0 * elems, stream);
     if (rc == ASSL_OK && (host_view1 || host_view2)) {
       ok = ok && cudaEventRecord(pipe->ev_out[c], st) == cudaSuccess;

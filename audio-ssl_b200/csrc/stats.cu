@@ -237,7 +237,7 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
         state[7] = 1.0;
         if (x.host_err) { *reinterpret_cast<volatile int*>(x.host_err) = 1; __threadfence_system(); }
       }
-      if (x.deferred) pdl_wait();
+      if (x.deferred && rank == 0) pdl_wait();
       return;
     }
     n_parts = 1;
@@ -334,8 +334,8 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
     state[2] = carry_v;
   }
   // deferred launch: this grid ran beside the one launched before it; whoever waits for THIS grid to complete (the
-  // next kernel's pdl_wait) must also get that one's completion
-  if (x.deferred) pdl_wait();
+  // next kernel's pdl_wait) must also get that one's completion (one CTA holds the grid open, the others free their SMs)
+  if (x.deferred && rank == 0) pdl_wait();
 }
 
 __global__ void __launch_bounds__(256) clip_sums_kernel(const double* tile_sums, long long B, long long n_parts, double* clip_sums) {

@@ -11,13 +11,13 @@
 // (what F.interpolate reaches at augmentations.py:53-54): source coordinate dst * (in-1)/(out-1)
 // in fp32, A = -0.75 cubic convolution weights, taps clamped to the CROP, rows nested over columns.
 // It is evaluated separably: stage A mixes the needed crop span once into shared memory (3 MUFU
-// per source pixel instead of per tap), stage B resamples along time, stage C along frequency.
+// per source pixel instead of per tap; 128-bit loads from the ring), stage B resamples along time, stage C along frequency.
 #include "common.cuh"
 
 namespace assl {
 
 constexpr int kViewThreads = 256;
-constexpr int kSrcPad = 8;
+constexpr int kViewWarps = kViewThreads / 32;
 
 struct ViewArgs {
   assl_view_cfg c;
@@ -38,7 +38,8 @@ struct ViewArgs {
   float* view1;
   float* view2;
   int tiles_t;     // output-time tiles per view
-  int src_w;       // staged source columns per tile (row stride of the source tile)
+  int src_w;       // floats per staged row (a multiple of 4)
+  int pitch;       // floats per ring row (>= n_time; a multiple of 4 on the vector path)
   int y0, x0;      // where the clip sits in the canvas (augmentations.py:47)
   int deferred;    // assl_two_views_deferred_f32: may overlap the grid launched before it (waits for it at the END)
 };
@@ -87,37 +88,46 @@ __device__ __forceinline__ void source_index(int dst, int n_in, int n_out, int* 
   *lam = fminf(fmaxf(real - static_cast<float>(i), 0.f), 1.f);
 }
 
-__device__ __forceinline__ void tap_weights(float t, int bilinear, float w[4]) {
-  if (bilinear) {
-    w[0] = 0.f; w[1] = 1.f - t; w[2] = t; w[3] = 0.f;
-  } else {
-    w[0] = cubic2(t + 1.f); w[1] = cubic1(t); w[2] = cubic1(1.f - t); w[3] = cubic2(2.f - t);
-  }
+__device__ __forceinline__ float4 tap_weights(float t, int bilinear) {
+  if (bilinear) return make_float4(0.f, 1.f - t, t, 0.f);
+  return make_float4(cubic2(t + 1.f), cubic1(t), cubic1(1.f - t), cubic2(2.f - t));
 }
 
-__host__ __device__ inline size_t views_smem_bytes(int canvas_h, int src_w, int n_freq) {
-  return sizeof(float) * static_cast<size_t>(canvas_h) * src_w +
-         (sizeof(float) + sizeof(int)) * 4 * static_cast<size_t>(n_freq);
+// shared memory: frequency taps [F] (weights, row byte offsets), time taps [TW] (weights, first-tap byte offset), rows
+__host__ __device__ inline size_t views_smem_bytes(int canvas_h, int src_w, int n_freq, int tw) {
+  return sizeof(float) * static_cast<size_t>(canvas_h) * src_w + (sizeof(float4) + sizeof(int4)) * static_cast<size_t>(n_freq) +
+         (sizeof(float4) + sizeof(int)) * static_cast<size_t>(tw);
 }
 
-// ---- stage A: normalise + mix the crop span [0,h) x [xs_lo, xs_lo+nsx) into shared memory.
-//      Only the part of the span that lies inside the pasted clip is computed: lanes <-> its columns
-//      xs = xs_in0 + lane + 32 c, c < G = ceil(n_in / 32) (G chosen per CTA), i.e. clip columns lx_in0 + lane + 32 c --
-//      one 64-bit row pointer per lane and row, every load at an immediate offset, no per-element predicate or
-//      select (only the last group is clamped / guarded).  The zero canvas around the clip (augmentations.py:45-47)
-//      is two guarded stores per row.  exp(xn) = ex2(x*a + b) with a = log2e/std, b = -mean*log2e/std: one FFMA +
-//      one MUFU per operand.  LOGMIX (log-mixup-exp against a bank entry, the path's normal case) is a separate
-//      instantiation; the other modes (no bank entry yet, plain mixup) share the generic one.
-template <int G, bool GB, bool LOGMIX>
-__device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, long long b, int v, int h, int ci,
-                                              int lx_in0, int xs_in0, int n_in, int nsx, int lane, int warp) {
+// What a CTA knows about its view, tile and staged rows.  A staged row holds the crop columns xs_lo .. xs_hi of one crop
+// row, xs_lo = (first tap of the tile's first output column) = ix_lo - 1 and xs_hi = ix_hi + 2 UNCLAMPED, so that the four
+// taps of an output column are four consecutive floats; the (at most one + two) slots that fall outside the crop hold
+// copies of its first / last column (ATen clamps the taps to the crop).  Slot u of a row = crop column xs_lo + u - xo =
+// clip column (d4 + u), where the shift xo in 0..3 makes d4 a multiple of 4: 16-byte groups of slots are 16-byte groups
+// of the ring row, and one LDG.128 -> math -> STS.128 moves four columns.
+struct Geo {
+  int h, w, ci, cj;      // the crop box, clamped into the canvas
+  int ox0, ncol;         // this tile's output columns
+  int xs_lo, xo, nslots; // staged span
+  int d4;                // clip column of slot 0 (multiple of 4, may be negative)
+  int j_in0, j_in1;      // float4 groups of a row that overlap the clip's columns [0, T)
+  int n4;                // float4 groups per staged row in use
+};
+
+// ---- stage A for one warp's rows: normalise + mix into shared memory.
+//      exp(xn) = ex2(x*a + b) with a = log2e/std, b = -mean*log2e/std: one FFMA + one MUFU per operand.
+//      LOGMIX (log-mixup-exp against a bank entry, the path's normal case) is a separate instantiation; the other
+//      modes (no bank entry yet, plain mixup) share the generic one.  G = 32-lane groups of float4 the in-clip part of a
+//      row needs (1 for clips up to 125 frames per tile span, else 2).  VEC: ring rows are 16-byte aligned (pitch % 4 == 0).
+template <int G, bool GB, bool LOGMIX, bool VEC>
+__device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, float* s_src, long long b, int v, int lane, int warp) {
   const int F = a.c.n_freq, T = a.c.n_time;
-  const int plane = F * T;
+  const long long plane = static_cast<long long>(F) * a.pitch;
   // GB (global bank, a separate instantiation so the default kernel keeps its register budget): the bank entry may
   // sit in a peer's ring (loads over NVLink) and the (mean, std) pairs live in a ring over global clips
   const int xslot = a.clip_slot[b];
   const int xstat = (GB && a.clip_stat) ? a.clip_stat[b] : xslot;
-  const float* xp = a.lms + static_cast<long long>(xslot) * plane;
+  const float* xp = a.lms + xslot * plane;
   float mu = 0.f, inv = 1.f;
   if (a.mean_std) { mu = a.mean_std[2 * xstat]; inv = 1.f / a.mean_std[2 * xstat + 1]; }
   const int zslot = a.mix_slot[b * 2 + v];
@@ -125,7 +135,7 @@ __device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, l
   const int zstat = (GB && a.mix_stat) ? a.mix_stat[b * 2 + v] : zslot;
   const float* zbase = a.lms;
   if (GB) { if (a.mix_rank && mix) zbase = a.peer_lms[a.mix_rank[b * 2 + v]]; }
-  const float* zp = zbase + static_cast<long long>(mix ? zslot : 0) * plane;
+  const float* zp = zbase + (mix ? zslot : 0) * plane;
   float zmu = 0.f, zinv = 1.f;
   if (mix && a.mean_std) { zmu = a.mean_std[2 * zstat]; zinv = 1.f / a.mean_std[2 * zstat + 1]; }
   const float al = a.alpha[b * 2 + v];
@@ -133,308 +143,295 @@ __device__ __forceinline__ void mix_crop_span(const ViewArgs& a, float* s_src, l
   const float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
   const float xa = LOGMIX ? inv * kLog2e : inv, xb = -mu * xa;
   const float za = LOGMIX ? zinv * kLog2e : zinv, zb = -zmu * za;
-  constexpr int kColGroups = G;                               // 32 * G >= n_in, 32 * (G - 1) < n_in
-  const int col0 = lx_in0 + lane;                             // this lane's clip column of group 0
-  const int col_last = lx_in0 + min(lane + 32 * (kColGroups - 1), n_in - 1);   // last group: clamped into the clip
-  const bool last_ok = lane + 32 * (kColGroups - 1) < n_in;
-  const int ml = xs_in0, mr = nsx - (xs_in0 + n_in);          // canvas columns of the span left / right of the clip
-  // (pointers opaque to the compiler, which otherwise rebuilds every address as ring base + 64-bit offset)
-  asm volatile("" : "+l"(xp));
-  asm volatile("" : "+l"(zp));
-  // Rows are taken kRowBatch at a time per warp and ALL their global loads are issued before any
-  // arithmetic, so a warp keeps 2 * kRowBatch * G loads in flight instead of 2.
-  constexpr int kRowBatch = 2;                               // (3 or 4 rows for the narrow instances: no gain measured)
-  for (int yb = warp * kRowBatch; yb < h; yb += (kViewThreads / 32) * kRowBatch) {
-    float xv[kRowBatch][kColGroups], zv[kRowBatch][kColGroups];
+
+  // this lane's float4 groups: j = j_in0 + lane + 32 q; their clip columns col .. col + 3.  Everything that does not
+  // depend on the row is worked out here, once: the row loop below only advances pointers.
+  int col[G];
+  bool on[G];
 #pragma unroll
-    for (int r = 0; r < kRowBatch; ++r) {
-      const int lyc = min(max(ci + yb + r - a.y0, 0), F - 1);  // warp-uniform; rows outside the clip are zero-filled below
-      const float* xr = xp + (lyc * T + col0);
-      const float* zr = zp + (lyc * T + col0);
-#pragma unroll
-      for (int c = 0; c < kColGroups - 1; ++c) {
-        xv[r][c] = __ldg(xr + 32 * c);
-        zv[r][c] = 0.f;
-        if (mix) zv[r][c] = __ldg(zr + 32 * c);                // CTA-uniform (compile-time true for LOGMIX)
-      }
-      xv[r][kColGroups - 1] = __ldg(xp + (lyc * T + col_last));
-      zv[r][kColGroups - 1] = 0.f;
-      if (mix) zv[r][kColGroups - 1] = __ldg(zp + (lyc * T + col_last));
+  for (int q = 0; q < G; ++q) {
+    const int j = g.j_in0 + lane + 32 * q;
+    on[q] = j < g.j_in1;
+    col[q] = min(max(g.d4 + 4 * (on[q] ? j : g.j_in0), 0), VEC ? a.pitch - 4 : T - 1);   // (idle lanes: any address inside the row)
+  }
+  // zero canvas: the groups left and right of the clip's columns (all groups, in a canvas row above / below the clip)
+  const bool row_a = lane < g.n4, row_b = lane + 32 < g.n4;                   // groups lane and lane + 32 exist
+  const bool zero_a = row_a && (lane < g.j_in0 || lane >= g.j_in1);
+  const bool zero_b = row_b && (lane + 32 < g.j_in0 || lane + 32 >= g.j_in1);
+  // the crop's edge columns are copied into the slots just outside it (taps clamp to the crop): which slots, if any
+  const int u_first = g.xo + (0 - g.xs_lo);                    // slot of crop column 0
+  const int u_last = g.xo + (g.w - 1 - g.xs_lo);               // slot of crop column w - 1
+  const int u_end = g.xo + g.nslots;                           // one past the last slot in use
+  int fix_dst = -1, fix_src = 0;
+  if (lane == 0 && g.xs_lo < 0) { fix_dst = u_first - 1; fix_src = u_first; }
+  if (lane >= 1 && lane <= 2 && u_last + lane < u_end) { fix_dst = u_last + lane; fix_src = u_last; }
+  const int fix_col = g.d4 + fix_src;                          // clip column of the copied slot: outside [0, T) it is canvas
+  const bool fix_zero = fix_col < 0 || fix_col >= T;
+
+  auto load4 = [&](const float* p, int c) -> float4 {          // (dense rows: c = the group's first column)
+    if (VEC) return __ldg(reinterpret_cast<const float4*>(p));
+    float4 r;
+    r.x = __ldg(p);
+    r.y = c + 1 < T ? __ldg(p + 1) : 0.f;
+    r.z = c + 2 < T ? __ldg(p + 2) : 0.f;
+    r.w = c + 3 < T ? __ldg(p + 3) : 0.f;
+    return r;
+  };
+  auto mix1 = [&](float x, float z) -> float {
+    const float xn = fmaf(x, xa, xb);
+    if (LOGMIX) {
+      const float zn = fmaf(z, za, zb);
+      return kLn2 * lg2_approx(fmaf(wx, ex2_approx(xn), fmaf(wz, ex2_approx(zn), kLogEps)));
     }
+    if (mix) return fmaf(wz, fmaf(z, za, zb), wx * xn);
+    return xn;
+  };
+
+  // Rows y = warp, warp + 8, ...: the same warp resamples them along time afterwards, so stage A -> stage B needs no
+  // CTA-wide barrier.  The loads run kDepth - 1 rows ahead of the arithmetic (kDepth register sets): a warp waits for
+  // global memory once, not once per row.
+  constexpr int kDepth = G == 1 ? 3 : 1;                       // (two groups per lane: no room for a second register set)
+  const float* xq[G];
+  const float* zq[G];
+  int ly = g.ci + warp - a.y0;                                  // clip row of this warp's first crop row
 #pragma unroll
-    for (int r = 0; r < kRowBatch; ++r) {
-      const int y = yb + r;
-      const int ly = ci + y - a.y0;
-      float* row = s_src + y * a.src_w;
-      if (y < h) {
-        if (ly >= 0 && ly < F) {                               // warp-uniform
-          float* drow = row + xs_in0 + lane;
+  for (int q = 0; q < G; ++q) {
+    xq[q] = xp + (static_cast<long long>(ly) * a.pitch + col[q]);
+    zq[q] = zp + (static_cast<long long>(ly) * a.pitch + col[q]);
+  }
+  const long long row_step = static_cast<long long>(kViewWarps) * a.pitch;
+  float* srow = s_src + warp * a.src_w;
+  const int srow_step = kViewWarps * a.src_w;
+  float4 xv[kDepth][G], zv[kDepth][G];
+  bool in_clip[kDepth];
+  auto fetch = [&](int set, int y) {                            // (no-op past the last row)
+    in_clip[set] = ly >= 0 && ly < F && y < g.h;                // warp-uniform
 #pragma unroll
-          for (int c = 0; c < kColGroups; ++c) {
-            const float xn = fmaf(xv[r][c], xa, xb);
-            float val;
-            if (LOGMIX) {
-              const float zn = fmaf(zv[r][c], za, zb);
-              val = kLn2 * lg2_approx(fmaf(wx, ex2_approx(xn), fmaf(wz, ex2_approx(zn), kLogEps)));
-            } else if (mix) {
-              val = fmaf(wz, fmaf(zv[r][c], za, zb), wx * xn);
-            } else {
-              val = xn;
-            }
-            if (c < kColGroups - 1 || last_ok) drow[32 * c] = val;
-          }
-          if (lane < ml) row[lane] = 0.f;                      // zero canvas left and right of the pasted clip
-          if (lane < mr) row[xs_in0 + n_in + lane] = 0.f;
-          if (ml > 32 || mr > 32) {                            // (long clips: a tile that mostly misses the clip)
-#pragma unroll 1
-            for (int x = 32 + lane; x < ml; x += 32) row[x] = 0.f;
-#pragma unroll 1
-            for (int x = 32 + lane; x < mr; x += 32) row[xs_in0 + n_in + x] = 0.f;
-          }
-        } else {
-#pragma unroll 1
-          for (int x = lane; x < nsx; x += 32) row[x] = 0.f;   // canvas row above / below the clip
-        }
+    for (int q = 0; q < G; ++q) {
+      xv[set][q] = zv[set][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (in_clip[set]) {
+        xv[set][q] = load4(xq[q], col[q]);
+        if (mix) zv[set][q] = load4(zq[q], col[q]);             // CTA-uniform (compile-time true for LOGMIX)
+      }
+      xq[q] += row_step; zq[q] += row_step;
+    }
+    ly += kViewWarps;
+  };
+  auto emit = [&](int set) {
+    float4* row4 = reinterpret_cast<float4*>(srow);
+    if (in_clip[set]) {
+#pragma unroll
+      for (int q = 0; q < G; ++q) {
+        const float4 x = xv[set][q], z = zv[set][q];
+        float4 o;
+        o.x = mix1(x.x, z.x);
+        o.y = col[q] + 1 < T ? mix1(x.y, z.y) : 0.f;            // (the last group may reach past the clip's last column:
+        o.z = col[q] + 2 < T ? mix1(x.z, z.z) : 0.f;            //  canvas)
+        o.w = col[q] + 3 < T ? mix1(x.w, z.w) : 0.f;
+        if (on[q]) row4[g.j_in0 + lane + 32 * q] = o;
+      }
+      if (zero_a) row4[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (zero_b) row4[lane + 32] = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+      if (row_a) row4[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (row_b) row4[lane + 32] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncwarp();
+    if (fix_dst >= 0) srow[fix_dst] = (fix_zero || !in_clip[set]) ? 0.f : srow[fix_src];
+    srow += srow_step;
+  };
+#pragma unroll
+  for (int d = 0; d < kDepth - 1; ++d) fetch(d, warp + kViewWarps * d);
+  for (int y = warp; y < g.h; y += kViewWarps * kDepth) {       // (unrolled by kDepth so that the register sets are static)
+#pragma unroll
+    for (int d = 0; d < kDepth; ++d) {
+      if (y + kViewWarps * d < g.h) {                           // warp-uniform
+        fetch((d + kDepth - 1) % kDepth, y + kViewWarps * (d + kDepth - 1));
+        emit(d);
       }
     }
   }
+  __syncwarp();
 }
 
-template <int G, bool GB>
-__device__ __forceinline__ void mix_crop_span_any(const ViewArgs& a, float* s_src, long long b, int v, int h, int ci,
-                                                  int lx_in0, int xs_in0, int n_in, int nsx, int lane, int warp) {
+template <int G, bool GB, bool VEC>
+__device__ __forceinline__ void stage_rows_any(const ViewArgs& a, const Geo& g, float* s_src, long long b, int v, int lane, int warp) {
   const bool logmix = a.mix_slot[b * 2 + v] >= 0 && a.c.log_mixup;          // CTA-uniform
-  if (logmix) mix_crop_span<G, GB, true>(a, s_src, b, v, h, ci, lx_in0, xs_in0, n_in, nsx, lane, warp);
-  else mix_crop_span<G, GB, false>(a, s_src, b, v, h, ci, lx_in0, xs_in0, n_in, nsx, lane, warp);
+  if (logmix) stage_rows<G, GB, true, VEC>(a, g, s_src, b, v, lane, warp);
+  else stage_rows<G, GB, false, VEC>(a, g, s_src, b, v, lane, warp);
 }
 
-// ---- stage B (along time: lanes <-> output columns, taps and weights in registers, warps <-> crop rows, each row
-//      overwritten in place by the warp that owns it) and stage C (along frequency, coalesced stores: lanes <->
-//      columns, warps <-> output rows).  NCM groups of 32 columns go through that mapping; with LEFT the tile has
-//      32 * NCM + n_left columns, 1 <= n_left <= kLeftMax, and the left-over columns are handled 32 / n_left rows
-//      at a time (lane -> (row, column)), so no lane idles on a mostly empty column group.
-constexpr int kLeftMax = 8;
-
-template <int NCM, bool LEFT>
-__device__ __forceinline__ void resample_tile(const ViewArgs& a, float* s_src, const float4* s_wy, const int4* s_ya,
-                                              float* outp, int h, int w, int ncol, int ox0, int xs_lo, int nsx, int bil,
-                                              int lane, int warp) {
-  const int F = a.c.n_freq, T = a.c.n_time;
-  constexpr int kWarps = kViewThreads / 32;
-  // left-over columns: lane -> (row rr of the iteration, column cc)
-  const int n_left = LEFT ? ncol - 32 * NCM : 1;
-  const int rpi = 32 / n_left;                                 // rows per iteration
-  const int rr = lane / n_left, cc = lane - rr * n_left;
-  const bool lv = LEFT && rr < rpi;
-  {
-    int xi[NCM][4];
-    float wt[NCM][4];
-#pragma unroll
-    for (int c = 0; c < NCM; ++c) {
-      const int col = LEFT ? lane + 32 * c : min(lane + 32 * c, ncol - 1);
-      int ix; float tx;
-      source_index(ox0 + col, w, T, &ix, &tx);
-      tap_weights(tx, bil, wt[c]);
-#pragma unroll
-      for (int q = 0; q < 4; ++q) xi[c][q] = min(max(min(max(ix - 1 + q, 0), w - 1) - xs_lo, 0), nsx - 1);
-    }
-    float accl[2] = {0.f, 0.f};
-    if (LEFT) {                                                // every left-over output of this warp's rows, before
-      int ix; float tx;                                        // any of those rows is overwritten
-      float wl[4];
-      int xl[4];
-      source_index(ox0 + 32 * NCM + cc, w, T, &ix, &tx);
-      tap_weights(tx, bil, wl);
-#pragma unroll
-      for (int q = 0; q < 4; ++q) xl[q] = min(max(min(max(ix - 1 + q, 0), w - 1) - xs_lo, 0), nsx - 1);
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        const int y = warp + kWarps * (j * rpi + rr);
-        const float* row = s_src + ((lv && y < h) ? y : 0) * a.src_w;
-        float acc = row[xl[0]] * wl[0];
-        acc = fmaf(row[xl[1]], wl[1], acc);
-        acc = fmaf(row[xl[2]], wl[2], acc);
-        accl[j] = fmaf(row[xl[3]], wl[3], acc);
-      }
-      __syncwarp();
-    }
-    for (int y = warp; y < h; y += kWarps) {                   // a warp owns the row: read every tap, then overwrite
-      float* row = s_src + y * a.src_w;
-      float acc[NCM];
-#pragma unroll
-      for (int c = 0; c < NCM; ++c) {
-        acc[c] = row[xi[c][0]] * wt[c][0];
-        acc[c] = fmaf(row[xi[c][1]], wt[c][1], acc[c]);
-        acc[c] = fmaf(row[xi[c][2]], wt[c][2], acc[c]);
-        acc[c] = fmaf(row[xi[c][3]], wt[c][3], acc[c]);
-      }
-      __syncwarp();
-#pragma unroll
-      for (int c = 0; c < NCM; ++c)
-        if (LEFT || lane + 32 * c < ncol) row[lane + 32 * c] = acc[c];
-    }
-    if (LEFT) {
-      __syncwarp();
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        const int y = warp + kWarps * (j * rpi + rr);
-        if (lv && y < h) s_src[y * a.src_w + 32 * NCM + cc] = accl[j];
-      }
-    }
-  }
-  __syncthreads();
-
-  {
-    for (int oy = warp; oy < F; oy += kWarps) {
-      const float4 wy = s_wy[oy];
-      const int4 ya = s_ya[oy];
-      const float* r0 = s_src + ya.x * a.src_w + lane;
-      const float* r1 = s_src + ya.y * a.src_w + lane;
-      const float* r2 = s_src + ya.z * a.src_w + lane;
-      const float* r3 = s_src + ya.w * a.src_w + lane;
-      float* orow = outp + static_cast<long long>(oy) * T + lane;
-#pragma unroll
-      for (int c = 0; c < NCM; ++c) {
-        if (LEFT || lane + 32 * c < ncol) {
-          float acc = r0[32 * c] * wy.x;
-          acc = fmaf(r1[32 * c], wy.y, acc);
-          acc = fmaf(r2[32 * c], wy.z, acc);
-          acc = fmaf(r3[32 * c], wy.w, acc);
-          store_view(orow + 32 * c, acc);
-        }
-      }
-    }
-    if (LEFT) {
-      const int col = 32 * NCM + cc;
-      for (int k0 = 0; warp + kWarps * k0 < F; k0 += rpi) {
-        const int oy = warp + kWarps * (k0 + rr);
-        if (lv && oy < F) {
-          const float4 wy = s_wy[oy];
-          const int4 ya = s_ya[oy];
-          float acc = s_src[ya.x * a.src_w + col] * wy.x;
-          acc = fmaf(s_src[ya.y * a.src_w + col], wy.y, acc);
-          acc = fmaf(s_src[ya.z * a.src_w + col], wy.z, acc);
-          acc = fmaf(s_src[ya.w * a.src_w + col], wy.w, acc);
-          store_view(outp + static_cast<long long>(oy) * T + col, acc);
-        }
-      }
-    }
-  }
-}
-
-// TW = output frames per tile; CG = 32-column groups of the staged crop span a warp loads per row
-template <int TW, int CG, bool GB>
+// TW = output frames per tile (32 / 64 / 128)
+template <int TW, bool GB, bool VEC>
 __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int F = a.c.n_freq, T = a.c.n_time;
-  float4* s_wy = reinterpret_cast<float4*>(smem_raw);                // [F]         frequency tap weights
-  int4* s_ya = reinterpret_cast<int4*>(s_wy + F);                    // [F]         frequency tap rows
-  float* s_src = reinterpret_cast<float*>(s_ya + F);                 // [h][src_w]  mixed crop span, then (in place,
+  float4* s_wy = reinterpret_cast<float4*>(smem_raw);                // [F]   frequency tap weights
+  int4* s_ya = reinterpret_cast<int4*>(s_wy + F);                    // [F]   frequency tap rows, as byte offsets into s_src
+  float4* s_wx = reinterpret_cast<float4*>(s_ya + F);                // [TW]  time tap weights of the tile's output columns
+  int* s_xu = reinterpret_cast<int*>(s_wx + TW);                     // [TW]  byte offset of a column's first tap in a row
+  float* s_src = reinterpret_cast<float*>(s_xu + TW);                // [h][src_w]  mixed crop span, then (in place,
                                                                      //             row by row) the time-resampled rows
-
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  long long blk = blockIdx.x;
-  const int tile = static_cast<int>(blk % a.tiles_t); blk /= a.tiles_t;
+  unsigned blk = blockIdx.x;
+  int tile = 0;
+  if (a.tiles_t > 1) { tile = static_cast<int>(blk % static_cast<unsigned>(a.tiles_t)); blk /= static_cast<unsigned>(a.tiles_t); }
   pdl_launch_dependents();                     // the next kernel may take SMs as this grid's last wave drains
   if (!a.deferred) pdl_wait();                 // nothing global is read before the previous grid has completed
-  if (a.order) blk = a.order[blk];             // CTAs start in launch order: the host puts the big crops first
-  const int v = static_cast<int>(blk & 1);
+  if (a.order) blk = static_cast<unsigned>(a.order[blk]);   // CTAs start in launch order: the host puts the big crops first
+  const int v = static_cast<int>(blk & 1u);
   const long long b = blk >> 1;
 
-  const int* cr = a.crop + (b * 2 + v) * 4;
-  // the host mirror validates crops; the clamps only keep a bad box from leaving shared memory
-  const int h = min(max(cr[2], 1), a.c.canvas_h), w = min(max(cr[3], 1), a.c.canvas_w);
-  const int ci = min(max(cr[0], 0), a.c.canvas_h - h), cj = min(max(cr[1], 0), a.c.canvas_w - w);
+  Geo g;
+  {
+    const int4 cr = *reinterpret_cast<const int4*>(a.crop + (b * 2 + v) * 4);
+    // the host mirror validates crops; the clamps only keep a bad box from leaving shared memory
+    g.h = min(max(cr.z, 1), a.c.canvas_h); g.w = min(max(cr.w, 1), a.c.canvas_w);
+    g.ci = min(max(cr.x, 0), a.c.canvas_h - g.h); g.cj = min(max(cr.y, 0), a.c.canvas_w - g.w);
+  }
   const int bil = a.c.interp;
-
-  const int ox0 = tile * TW;
-  const int ncol = min(TW, T - ox0);
-  // crop columns this tile's taps can touch
-  int ix_lo, ix_hi; float lam;
-  source_index(ox0, w, T, &ix_lo, &lam);
-  source_index(ox0 + ncol - 1, w, T, &ix_hi, &lam);
-  const int xs_lo = max(ix_lo - 1, 0);
-  const int xs_hi = min(ix_hi + 2, w - 1);
-  const int nsx = min(xs_hi - xs_lo + 1, a.src_w);
-
-  // ---- frequency-axis taps, shared by every column of the tile
-  for (int oy = tid; oy < F; oy += kViewThreads) {
-    int iy; float ty;
-    source_index(oy, h, F, &iy, &ty);
-    float wt[4];
-    tap_weights(ty, bil, wt);
-    s_wy[oy] = make_float4(wt[0], wt[1], wt[2], wt[3]);
-    s_ya[oy] = make_int4(min(max(iy - 1, 0), h - 1), min(max(iy, 0), h - 1),
-                         min(max(iy + 1, 0), h - 1), min(max(iy + 2, 0), h - 1));
+  g.ox0 = tile * TW;
+  g.ncol = min(TW, T - g.ox0);
+  {
+    int ix_lo, ix_hi; float lam;
+    source_index(g.ox0, g.w, T, &ix_lo, &lam);
+    source_index(g.ox0 + g.ncol - 1, g.w, T, &ix_hi, &lam);
+    g.xs_lo = ix_lo - 1;
+    g.nslots = min(ix_hi + 2 - g.xs_lo + 1, a.src_w - 3);
+    const int d0 = g.cj + g.xs_lo - a.x0;                            // clip column of the first slot
+    g.xo = d0 & 3;
+    g.d4 = d0 - g.xo;
+    g.n4 = (g.xo + g.nslots + 3) >> 2;
+    const int lo = g.d4 < 0 ? (-g.d4) >> 2 : 0;                      // first group at or right of clip column 0
+    const int hi = g.d4 < T ? (T - g.d4 + 3) >> 2 : 0;               // one past the last group left of clip column T
+    g.j_in0 = min(lo, g.n4);
+    g.j_in1 = max(min(hi, g.n4), g.j_in0);
   }
 
-  // ---- stage A, with as many 32-column groups as the part of THIS crop span inside the clip needs
+  // ---- taps, once per CTA: frequency (shared by every column of the tile), time (shared by every row)
+  for (int oy = tid; oy < F; oy += kViewThreads) {
+    int iy; float ty;
+    source_index(oy, g.h, F, &iy, &ty);
+    s_wy[oy] = tap_weights(ty, bil);
+    const int rb = a.src_w * 4;
+    s_ya[oy] = make_int4(min(max(iy - 1, 0), g.h - 1) * rb, min(max(iy, 0), g.h - 1) * rb,
+                         min(max(iy + 1, 0), g.h - 1) * rb, min(max(iy + 2, 0), g.h - 1) * rb);
+  }
+  for (int c = tid; c < TW; c += kViewThreads) {
+    int ix; float tx;
+    source_index(g.ox0 + min(c, g.ncol - 1), g.w, T, &ix, &tx);
+    s_wx[c] = tap_weights(tx, bil);
+    s_xu[c] = 4 * min(max(ix - 1 - g.xs_lo + g.xo, 0), a.src_w - 4);
+  }
+
+  // ---- stage A (this warp's rows), with as many 32-lane groups of float4 as the in-clip part of THIS span needs
+  if (g.j_in1 - g.j_in0 <= 32) stage_rows_any<1, GB, VEC>(a, g, s_src, b, v, lane, warp);
+  else stage_rows_any<2, GB, VEC>(a, g, s_src, b, v, lane, warp);
+  __syncthreads();                             // (the tap tables; the rows themselves stay with their warp until stage C)
+
+  // ---- stage B, along time: lanes <-> output columns, the four taps of a column are four consecutive floats of the row
+  //      (1 address add + 4 LDS + 4 FMA per column), each row overwritten in place by the warp that owns it
+  constexpr int NC = TW / 32;
   {
-    // columns of the span that fall inside the pasted clip: lx = cj + xs_lo + xs - x0 in [0, T)
-    const int lx0 = cj + xs_lo - a.x0;
-    const int xs_in0 = min(max(0, -lx0), nsx), xs_in1 = max(min(nsx, T - lx0), xs_in0);
-    const int n_in = xs_in1 - xs_in0, lx_in0 = lx0 + xs_in0;
-#define ASSL_STAGE_A(G) mix_crop_span_any<G, GB>(a, s_src, b, v, h, ci, lx_in0, xs_in0, n_in, nsx, lane, warp)
-    const int g = min((n_in + 31) >> 5, CG);                     // (the launcher guarantees CG >= ceil(n_in / 32))
-    if (g == 0) {                                                // the tile's span misses the clip: all canvas
-      for (int y = warp; y < h; y += kViewThreads / 32) {
-#pragma unroll 1
-        for (int x = lane; x < nsx; x += 32) s_src[y * a.src_w + x] = 0.f;
+    float4 wt[NC];
+    int xu[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) { wt[c] = s_wx[lane + 32 * c]; xu[c] = s_xu[lane + 32 * c]; }
+    const unsigned src0 = static_cast<unsigned>(__cvta_generic_to_shared(s_src));
+    for (int y = warp; y < g.h; y += kViewWarps) {
+      const unsigned rowb = src0 + static_cast<unsigned>(y * a.src_w) * 4u;
+      float acc[NC];
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        const unsigned p = rowb + static_cast<unsigned>(xu[c]);
+        float t0, t1, t2, t3;
+        asm volatile("ld.shared.f32 %0, [%4];\n\tld.shared.f32 %1, [%4+4];\n\tld.shared.f32 %2, [%4+8];\n\tld.shared.f32 %3, [%4+12];"
+                     : "=f"(t0), "=f"(t1), "=f"(t2), "=f"(t3) : "r"(p) : "memory");
+        acc[c] = t0 * wt[c].x;
+        acc[c] = fmaf(t1, wt[c].y, acc[c]);
+        acc[c] = fmaf(t2, wt[c].z, acc[c]);
+        acc[c] = fmaf(t3, wt[c].w, acc[c]);
       }
-    } else if (g == 1) { ASSL_STAGE_A(1); }
-    else if (CG >= 2 && g == 2) { ASSL_STAGE_A((CG >= 2 ? 2 : 1)); }
-    else if (CG >= 3 && g == 3) { ASSL_STAGE_A((CG >= 3 ? 3 : 1)); }
-    else if (CG >= 4 && g == 4) { ASSL_STAGE_A((CG >= 4 ? 4 : 1)); }
-    else if (CG >= 5 && g == 5) { ASSL_STAGE_A((CG >= 5 ? 5 : 1)); }
-    else if (CG >= 6 && g == 6) { ASSL_STAGE_A((CG >= 6 ? 6 : 1)); }
-    else if (CG >= 7) { ASSL_STAGE_A((CG >= 7 ? 7 : 1)); }
-#undef ASSL_STAGE_A
+      __syncwarp();
+      float* row = s_src + y * a.src_w;
+#pragma unroll
+      for (int c = 0; c < NC; ++c)
+        if (lane + 32 * c < g.ncol) row[lane + 32 * c] = acc[c];
+    }
   }
   __syncthreads();
 
-  // ---- stages B and C.  T = 101 is three full groups of 32 output columns and 5 left over: those are resampled
-  //      with lanes <-> (row, column) instead of wasting 27 lanes of a fourth group on every row
-  constexpr int NC = TW / 32;                                  // output columns per lane: lane + 32*c
-  float* outp = (v == 0 ? a.view1 : a.view2) + b * (static_cast<long long>(F) * T) + ox0;
-  const int n_left = ncol - 32 * (NC - 1);
-  if (NC > 1 && n_left >= 1 && n_left <= kLeftMax && (a.c.canvas_h + 7) / 8 <= 2 * (32 / n_left))
-    resample_tile<(NC > 1 ? NC - 1 : 1), true>(a, s_src, s_wy, s_ya, outp, h, w, ncol, ox0, xs_lo, nsx, bil, lane, warp);
-  else
-    resample_tile<NC, false>(a, s_src, s_wy, s_ya, outp, h, w, ncol, ox0, xs_lo, nsx, bil, lane, warp);
+  // ---- stage C, along frequency: lanes <-> columns, a warp takes a block of consecutive output rows, coalesced streaming
+  //      stores.  The frequency scale (h - 1) / (F - 1) is at most 1 (the crop is not taller than the canvas of F rows
+  //      unless virtual_crop_scale[0] > 1), so the four tap rows of consecutive output rows are the same or move down by
+  //      one: a lane keeps them in registers and loads ONE new value per column when they move (a quarter of the
+  //      shared-memory reads of four loads per output; the pipe that carries them is the busiest one in this kernel).
+  {
+    float* outp = (v == 0 ? a.view1 : a.view2) + b * (static_cast<long long>(F) * T) + g.ox0 + lane;
+    const char* col0 = reinterpret_cast<const char*>(s_src + lane);
+    bool live[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) live[c] = lane + 32 * c < g.ncol;
+    const int rows_per_warp = (F + kViewWarps - 1) / kViewWarps;
+    const int oy0 = warp * rows_per_warp, oy1 = min(F, oy0 + rows_per_warp);
+    const int rb = a.src_w * 4;
+    float* orow = outp + oy0 * T;
+    float t0[NC], t1[NC], t2[NC], t3[NC];
+    int prev = -1 - rb;                                         // second tap row of the previous output row (byte offset)
+    for (int oy = oy0; oy < oy1; ++oy, orow += T) {
+      const float4 wy = s_wy[oy];
+      const int4 ya = s_ya[oy];
+      const int moved = ya.y - prev;                            // the same for every lane
+      prev = ya.y;
+      if (moved == rb) {                                        // one row down: (t0, t1, t2, t3) <- (t1, t2, t3, new)
+        const float* r3 = reinterpret_cast<const float*>(col0 + ya.w);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) { t0[c] = t1[c]; t1[c] = t2[c]; t2[c] = t3[c]; t3[c] = r3[32 * c]; }
+      } else if (moved != 0) {                                  // the block's first row (or a scale above 1): all four
+        const float* r0 = reinterpret_cast<const float*>(col0 + ya.x);
+        const float* r1 = reinterpret_cast<const float*>(col0 + ya.y);
+        const float* r2 = reinterpret_cast<const float*>(col0 + ya.z);
+        const float* r3 = reinterpret_cast<const float*>(col0 + ya.w);
+#pragma unroll
+        for (int c = 0; c < NC; ++c) { t0[c] = r0[32 * c]; t1[c] = r1[32 * c]; t2[c] = r2[32 * c]; t3[c] = r3[32 * c]; }
+      }
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {                            // (every load stays inside the staged rows: no guard)
+        float acc = t0[c] * wy.x;
+        acc = fmaf(t1[c], wy.y, acc);
+        acc = fmaf(t2[c], wy.z, acc);
+        acc = fmaf(t3[c], wy.w, acc);
+        if (live[c]) store_view(orow + 32 * c, acc);
+      }
+    }
+  }
   // deferred launch: this grid ran beside the one launched before it; whoever waits for THIS grid to complete
-  // (the next kernel's pdl_wait) must also get that one's completion
-  if (a.deferred) pdl_wait();
+  // (the next kernel's pdl_wait) must also get that one's completion.  ONE CTA holds the grid open for that: if every
+  // CTA waited here, the first wave would sit on its SM slots until the kernel before has finished (the statistics
+  // scan + send take longer than a view) and nothing else of this grid could start.
+  if (a.deferred && blockIdx.x == 0) pdl_wait();
 }
 
-template <int TW, int CG, bool GB>
+template <int TW, bool GB, bool VEC>
 int launch_views_kernel(ViewArgs& a, size_t smem, unsigned grid, cudaStream_t st) {
-  if (cudaFuncSetAttribute(two_views_kernel<TW, CG, GB>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
+  if (cudaFuncSetAttribute(two_views_kernel<TW, GB, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
     return ASSL_ERR_CUDA;
-  if (launch_pdl(two_views_kernel<TW, CG, GB>, dim3(grid), dim3(kViewThreads), smem, st, a) != cudaSuccess) return ASSL_ERR_CUDA;
+  if (launch_pdl(two_views_kernel<TW, GB, VEC>, dim3(grid), dim3(kViewThreads), smem, st, a) != cudaSuccess) return ASSL_ERR_CUDA;
   return launch_status();
 }
 
-template <int TW, int CG>
-int launch_views_cg(ViewArgs& a, cudaStream_t st) {
-  const size_t smem = views_smem_bytes(a.c.canvas_h, a.src_w, a.c.n_freq);
-  if (smem > 227 * 1024) return ASSL_ERR_UNSUPPORTED;
+template <int TW>
+int launch_views(ViewArgs& a, bool vec, cudaStream_t st) {
+  a.tiles_t = (a.c.n_time + TW - 1) / TW;
+  const size_t smem = views_smem_bytes(a.c.canvas_h, a.src_w, a.c.n_freq, TW);
+  if (smem > 227 * 1024 / 2) return ASSL_ERR_UNSUPPORTED;        // (at least two CTAs per SM; a smaller tile is tried next)
+  if ((a.src_w + 3) / 4 > 64 + 32) return ASSL_ERR_UNSUPPORTED;  // stage A covers the in-clip part with at most 2 x 32 groups
   const long long grid = a.B * 2 * a.tiles_t;
   if (grid > 0x7fffffffll) return ASSL_ERR_UNSUPPORTED;
   const bool global_bank = a.mix_rank || a.clip_stat;
-  return global_bank ? launch_views_kernel<TW, CG, true>(a, smem, static_cast<unsigned>(grid), st)
-                     : launch_views_kernel<TW, CG, false>(a, smem, static_cast<unsigned>(grid), st);
-}
-
-template <int TW>
-int launch_views(ViewArgs& a, cudaStream_t st) {
-  a.tiles_t = (a.c.n_time + TW - 1) / TW;
-  if (a.src_w < (a.c.n_time < TW ? a.c.n_time : TW)) return ASSL_ERR_UNSUPPORTED;   // rows are reused for the outputs
-  constexpr int kMaxCG = (TW * 3 / 2 + 16 + 31) / 32;            // covers span() for virtual_crop_scale <= 1.5
-  const int need = (a.src_w - 1 + 31) / 32;                      // stage A loads 32 columns per group
-  if (need > kMaxCG) return ASSL_ERR_UNSUPPORTED;                 // virtual_crop_scale[1] well above 1.5
-  if (need <= kMaxCG - 2) return launch_views_cg<TW, (kMaxCG - 2 > 0 ? kMaxCG - 2 : 1)>(a, st);
-  if (need <= kMaxCG - 1) return launch_views_cg<TW, kMaxCG - 1>(a, st);
-  return launch_views_cg<TW, kMaxCG>(a, st);
+  const unsigned gr = static_cast<unsigned>(grid);
+  if (global_bank) return vec ? launch_views_kernel<TW, true, true>(a, smem, gr, st) : launch_views_kernel<TW, true, false>(a, smem, gr, st);
+  return vec ? launch_views_kernel<TW, false, true>(a, smem, gr, st) : launch_views_kernel<TW, false, false>(a, smem, gr, st);
 }
 
 }  // namespace assl
@@ -475,19 +472,26 @@ static int two_views_impl(const assl_view_cfg* vc, const float* lms, const float
   a.deferred = deferred;
   a.y0 = (vc->canvas_h - vc->n_freq) / 2;
   a.x0 = (vc->canvas_w - vc->n_time) / 2;
-  // widest crop span a TW-column tile can touch: (TW-1) * max scale + 4 taps, never more than the canvas
   const int T = vc->n_time;
+  a.pitch = vc->ring_pitch > 0 ? vc->ring_pitch : T;
+  if (a.pitch < T) return ASSL_ERR_INVALID_ARG;
+  // 16-byte groups of a ring row are loaded as one word when every row starts on a 16-byte boundary, in every ring read
+  bool vec = a.pitch % 4 == 0 && reinterpret_cast<uintptr_t>(lms) % 16 == 0;
+  for (int r = 0; r < world; ++r) vec = vec && reinterpret_cast<uintptr_t>(peer_lms[r]) % 16 == 0;
+  // floats per staged row: the widest span a TW-column tile can touch -- (TW-1) * max scale + 4 taps, never more than the
+  // crop can be wide + the two taps outside it on either side -- + 3 (alignment shift), rounded up to whole 16-byte groups
   const double smax = T > 1 ? static_cast<double>(vc->canvas_w - 1) / (T - 1) : 0.0;
   auto span = [&](int tw) {
     const int cols = tw < T ? tw : T;
     long long s = static_cast<long long>((cols - 1) * smax) + 5;
-    if (s > vc->canvas_w) s = vc->canvas_w;
-    return static_cast<int>((s + kSrcPad - 1) / kSrcPad * kSrcPad) + 1;     // odd-ish stride spreads banks
+    if (s > vc->canvas_w + 3) s = vc->canvas_w + 3;
+    if (s + 3 < tw) s = tw - 3;                                  // (stages B and C read column lane + 32 c of a row unguarded)
+    return static_cast<int>((s + 3 + 3) / 4 * 4);
   };
   int rc = ASSL_ERR_UNSUPPORTED;
-  if (T > 64) { a.src_w = span(128); rc = launch_views<128>(a, as_stream(stream)); }
-  if (rc == ASSL_ERR_UNSUPPORTED && T > 32) { a.src_w = span(64); rc = launch_views<64>(a, as_stream(stream)); }
-  if (rc == ASSL_ERR_UNSUPPORTED) { a.src_w = span(32); rc = launch_views<32>(a, as_stream(stream)); }
+  if (T > 64) { a.src_w = span(128); rc = launch_views<128>(a, vec, as_stream(stream)); }
+  if (rc == ASSL_ERR_UNSUPPORTED && T > 32) { a.src_w = span(64); rc = launch_views<64>(a, vec, as_stream(stream)); }
+  if (rc == ASSL_ERR_UNSUPPORTED) { a.src_w = span(32); rc = launch_views<32>(a, vec, as_stream(stream)); }
   return rc;
 }
 

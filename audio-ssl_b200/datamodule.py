@@ -157,10 +157,12 @@ class DeviceBatchLoader:
                 released[k % n_slots].set()
                 packed.raw.record_stream(torch.cuda.current_stream(device))
                 out = self.pipeline(packed)
-                if out is not None:                                  # (a lookahead pipeline returns batch k-1 at call k)
+                if out is not None:                                  # (a lookahead pipeline returns an earlier batch at call k)
                     yield out
-            last = self.pipeline.flush() if getattr(self.pipeline, "flush", None) else None
-            if last is not None:
+            while getattr(self.pipeline, "flush", None):             # whatever is still pending at the end of the epoch
+                last = self.pipeline.flush()
+                if last is None:
+                    break
                 yield last
         finally:
             for e in released:

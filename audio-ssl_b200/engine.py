@@ -219,7 +219,10 @@ class ViewEngine:
         # so the ring holds one more batch and the write head runs ``ahead`` clips in front of ``clips_done``
         self.lookahead = bool(lookahead)
         self.ahead = 0
-        self.cap = self.history + (2 if self.lookahead else 1) * self.max_batch
+        # how many batches the views run behind the front end: 1 with lookahead; 2 when the statistics are exchanged
+        # between GPUs as well (the scan of batch k-1 then runs BESIDE the views of batch k-2, off the critical path)
+        self.depth = 0 if not self.lookahead else (2 if (self.normalize and sync_stats and _dist_world()[1] > 1) else 1)
+        self.cap = self.history + (1 + self.depth) * self.max_batch
         # global bank (optional): the FIFO runs over the GLOBAL clip order; bank entries are read from the
         # peers' rings over NVLink.  Every step must bring exactly max_batch clips per rank.  The ring is
         # steps_back + 2 steps deep: a step's clips can be picked for steps_back more steps, and a rank is never
@@ -238,19 +241,22 @@ class ViewEngine:
             self.peer_ring = None
         self.clips_done = 0
         self.ring = self.stats = self.state = None
-        self.f = self.t = None
+        self.f = self.t = self.pitch = None
         self._exchange = False               # False: not tried yet; None: unavailable; else a StatsExchange
 
     # ------------------------------------------------------------------ buffers
     def ensure(self, f, t, device):
         if self.ring is None:
             self.f, self.t = int(f), int(t)
+            # ring rows are padded to a multiple of 4 floats: 16-byte aligned rows, read with 128-bit loads by the two-view
+            # kernel (assl_view_cfg.ring_pitch); the pad columns are never read as data
+            self.pitch = (self.t + 3) & ~3
             if self.global_bank:
-                self.peer_ring = PeerRing((self.cap, self.f, self.t), device)
+                self.peer_ring = PeerRing((self.cap, self.f, self.pitch), device)
                 self.ring = self.peer_ring.tensor
                 self.stats = torch.zeros((self.gcap, 2), dtype=torch.float32, device=device)   # over GLOBAL clips
             else:
-                self.ring = torch.empty((self.cap, self.f, self.t), dtype=torch.float32, device=device)
+                self.ring = torch.zeros((self.cap, self.f, self.pitch), dtype=torch.float32, device=device)
                 self.stats = torch.zeros((self.cap, 2), dtype=torch.float32, device=device)
             self.stats[:, 1] = 1.0
             self.state = torch.zeros(8, dtype=torch.float64, device=device)
@@ -270,9 +276,9 @@ class ViewEngine:
         """Copy a [B, F, T] batch into the ring at the current head (at most two slice copies)."""
         b, s0 = x.shape[0], self.slot0
         first = min(b, self.cap - s0)
-        self.ring[s0:s0 + first].copy_(x[:first])
+        self.ring[s0:s0 + first, :, :self.t].copy_(x[:first])
         if first < b:
-            self.ring[:b - first].copy_(x[first:])
+            self.ring[:b - first, :, :self.t].copy_(x[first:])
 
     # ------------------------------------------------------------------ statistics
     def exchange(self, device):
@@ -284,9 +290,10 @@ class ViewEngine:
 
     @property
     def split_stats(self):
-        """Lookahead order across GPUs: the sums of batch k are SENT right behind its log-mel kernel and SCANNED one step
-        later (just before the views that need them), so no rank waits for the slowest one inside a step."""
-        return self.lookahead and self.normalize and self.sync_stats and _dist_world()[1] > 1
+        """Lookahead order across GPUs -- log-mel(k) . scan(k-1) . send(k) . views(k-2): the sums of batch k are SENT right
+        behind its log-mel kernel and SCANNED one step later, beside the views of the batch before (launched deferred),
+        so neither the wait for the slowest rank nor the scan itself sits between two log-mel kernels."""
+        return self.depth == 2
 
     def update_stats(self, sums, n_parts):
         """sums: [B, n_parts, 2] fp64 on device for this rank's clips, in order: statistics of the batch at the ring head."""
@@ -317,15 +324,16 @@ class ViewEngine:
             raise ValueError(f"{b} clips in one call, the statistics exchange was opened for max_batch = {ex.max_clips}")
         ex.send(sums, b, n_parts)
         self._sent = (self.slot0, b)
-        self._keep = sums
+        self._keep2, self._keep = getattr(self, "_keep", None), sums
 
-    def scan_pending_stats(self, deferred=True):
+    def scan_pending_stats(self, deferred=False):
         """split_stats: the scan of the batch sent last (no-op when none is pending)."""
         if getattr(self, "_sent", None) is None:
-            return
+            return False
         slot0, _ = self._sent
         self._exchange.scan(self.state, self.f * self.t, self.max_update, self.stats, slot0, self.cap, deferred=deferred)
         self._sent = None
+        return True
 
     def check_exchange(self):
         if self._exchange not in (False, None):
@@ -371,7 +379,8 @@ class ViewEngine:
         batch, device = prep["batch"], prep["device"]
         v1 = torch.empty((batch, 1, self.f, self.t), dtype=torch.float32, device=device)
         v2 = torch.empty_like(v1)
-        vcfg = _native.ViewCfg(self.f, self.t, prep["ch"], prep["cw"], INTERP[self.interp], 1 if self.log_mixup else 0)
+        vcfg = _native.ViewCfg(self.f, self.t, prep["ch"], prep["cw"], INTERP[self.interp], 1 if self.log_mixup else 0,
+                               self.pitch)
         name = "assl_two_views_deferred_f32" if deferred else "assl_two_views_ordered_f32"
         _native.check(getattr(_native.lib(), name)(
             C.byref(vcfg), _ptr(self.ring), _ptr(self.stats if self.normalize else None), self.cap,
@@ -413,7 +422,7 @@ class ViewEngine:
         d_order = to_dev(heavy_first(params.crop, self.t, cw))
         v1 = torch.empty((batch, 1, self.f, self.t), dtype=torch.float32, device=device)
         v2 = torch.empty_like(v1)
-        vcfg = _native.ViewCfg(self.f, self.t, ch, cw, INTERP[self.interp], 1 if self.log_mixup else 0)
+        vcfg = _native.ViewCfg(self.f, self.t, ch, cw, INTERP[self.interp], 1 if self.log_mixup else 0, self.pitch)
         _native.check(_native.lib().assl_two_views_global_f32(
             C.byref(vcfg), _ptr(self.ring), self.peer_ring.ptrs, w, _ptr(self.stats), _ptr(d_clip), _ptr(d_cstat),
             _ptr(d_mix), _ptr(d_rank), _ptr(d_mstat), _ptr(d_alpha), _ptr(d_crop), _ptr(d_order), batch, _ptr(v1), _ptr(v2),
@@ -427,7 +436,7 @@ class ViewEngine:
             raise RuntimeError("a batch is still waiting for its views: call flush() before state_dict()")
         self.check_exchange()
         return {"clips_done": self.clips_done, "cap": self.cap,
-                "ring": None if self.ring is None else self.ring.cpu(),
+                "ring": None if self.ring is None else self.ring[:, :, :self.t].cpu(),
                 "stats": None if self.stats is None else self.stats.cpu(),
                 "state": None if self.state is None else self.state.cpu()}
 
@@ -437,5 +446,5 @@ class ViewEngine:
                 raise ValueError("ring capacity differs (n_memory / max_batch changed)")
             device = device or torch.device("cuda", torch.cuda.current_device())
             self.ensure(sd["ring"].shape[1], sd["ring"].shape[2], device)
-            self.ring.copy_(sd["ring"]); self.stats.copy_(sd["stats"]); self.state.copy_(sd["state"])
+            self.ring[:, :, :self.t].copy_(sd["ring"]); self.stats.copy_(sd["stats"]); self.state.copy_(sd["state"])
         self.clips_done = int(sd["clips_done"])

@@ -60,13 +60,13 @@ class Plan:
         _native.check(_native.lib().assl_plan_filterbank(self.handle, out.ctypes.data_as(C.c_void_p)))
         return out
 
-    def logmel_into(self, wave, out, slot0=0, cap=0, tile_sums=None, gain=None, power=False, time_major=False):
+    def logmel_into(self, wave, out, slot0=0, cap=0, tile_sums=None, gain=None, power=False, time_major=False, pitch=0):
         """wave [B, L] cuda fp32 -> out (ring or [B, n_mels, T]; [B, T, n_mels] with time_major); all on the
-        current stream."""
+        current stream.  ``pitch``: floats per output row (0 = T; the engines' rings pad their rows to a multiple of 4)."""
         b, n = wave.shape
-        _native.check(_native.lib().assl_logmel_f32(
-            self.handle, _ptr(wave), _ptr(gain), b, n, wave.stride(0), _ptr(out), int(slot0), int(cap),
-            _ptr(tile_sums), (1 if power else 0) | (2 if time_major else 0), _stream_ptr()), "assl_logmel_f32")
+        _native.check(_native.lib().assl_logmel_pitched_f32(
+            self.handle, _ptr(wave), _ptr(gain), b, n, wave.stride(0), _ptr(out), int(slot0), int(cap), int(pitch),
+            _ptr(tile_sums), (1 if power else 0) | (2 if time_major else 0), _stream_ptr()), "assl_logmel_pitched_f32")
 
     def __del__(self):
         try:

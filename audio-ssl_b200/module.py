@@ -147,7 +147,7 @@ class UpstreamInputPipeline:
         self.unit_length = int(unit_length) if unit_length is not None else \
             (int(length_wave * 16000) if length_wave else None)          # utils.py:168-169
         self.last_lms = None
-        self._pending = None                 # lookahead: the batch whose front end has run, waiting for its views
+        self._queue = []                     # lookahead: batches whose front end has run, waiting for their views
 
     def __call__(self, waveforms, params: ViewParams = None):
         if isinstance(waveforms, PackedClips):
@@ -179,7 +179,7 @@ class UpstreamInputPipeline:
         return self.tfms._post(v1, v2)
 
     # -- lookahead=True: software-pipelined step order  log-mel(k) . statistics(k) . views(k-1)
-    #    (across GPUs: scan(k-1) . log-mel(k) . send(k) . views(k-1), see ViewEngine.split_stats)
+    #    (across GPUs: log-mel(k) . scan(k-1) . send(k) . views(k-2), see ViewEngine.split_stats)
     def _call_lookahead(self, waveforms, params):
         """Run the front end and the statistics of THIS batch and return the two views of the PREVIOUS one (``None`` on
         the first call; ``flush()`` returns the last batch's).  The views of batch k-1 are launched right behind the
@@ -205,45 +205,55 @@ class UpstreamInputPipeline:
             return self._front_then_previous_views(wave, gain, tf._params(params, 0, b, g0=eng.head))
 
     def _front_then_previous_views(self, part, gain, p):
-        """[b, L] windows of THIS batch -> log-mel into the ring -> statistics; then the views of the pending batch."""
+        """[b, L] windows of THIS batch -> log-mel into the ring -> statistics; then the views of the oldest pending batch
+        (one batch back; two across GPUs, see ViewEngine.split_stats)."""
         eng, tf = self.tfms.engine, self.tfms
         b = part.shape[0]
-        # parameters of this batch: uploaded before its kernels, used one call later
+        # parameters of this batch: uploaded before its kernels, used one or two calls later
         prep = eng.prepare_views(p, b, part.device, eng.head)
         tiles = self.plan.num_tiles(part.shape[1])
         sums = torch.empty((b, tiles, 2), dtype=torch.float64, device=part.device) if tf.pre_norm else None
         split = tf.pre_norm and eng.split_stats
+        self.plan.logmel_into(part, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain, pitch=eng.pitch)
         if split:
-            # sharded run: the statistics of the PENDING batch are scanned now (every rank sent its sums a step ago, right
-            # behind its log-mel kernel, so nobody waits for the slowest rank here), this batch's sums go out below
-            eng.scan_pending_stats(deferred=True)
-        self.plan.logmel_into(part, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain)
-        if split:
+            # sharded run: the statistics of the batch before are scanned now -- every rank sent its sums a step ago, so
+            # nobody waits for the slowest rank -- then this batch's sums go out; both run beside the deferred views below
+            eng.scan_pending_stats(deferred=True)   # (may start under the log-mel kernel's tail: it reads records and state only)
             eng.send_stats(sums, tiles)
         elif tf.pre_norm:
             eng.update_stats(sums, tiles)
         eng.ahead += b
         out = None
-        if self._pending is not None:
-            # (deferred: right behind the statistics kernel -- or, without pre-norm, the log-mel kernel -- of THIS batch,
-            #  which the launch may overlap; everything it reads was complete before that log-mel kernel started)
-            v1, v2 = eng.launch_prepared(self._pending, deferred=True)
-            eng.ahead -= self._pending["batch"]
+        if len(self._queue) >= eng.depth:
+            # (deferred: behind the statistics kernels -- or, without pre-norm, the log-mel kernel -- of THIS step, which
+            #  the launch may overlap; everything it reads was complete before this step's log-mel kernel started)
+            oldest = self._queue.pop(0)
+            v1, v2 = eng.launch_prepared(oldest, deferred=True)
+            eng.ahead -= oldest["batch"]
             out = tf._post(v1, v2)
-        self._pending = prep
+        self._queue.append(prep)
         return out
 
     def flush(self):
-        """Views of the last batch given to a ``lookahead`` pipeline (``None`` if nothing is pending)."""
-        if self._pending is None:
+        """Views of the oldest batch still waiting in a ``lookahead`` pipeline (``None`` when nothing is pending); call it
+        until it returns None (one batch is pending on one GPU, up to two across GPUs) -- or use ``drain()``."""
+        if not self._queue:
             return None
         eng = self.tfms.engine
-        with torch.cuda.device(self._pending["device"]):
-            eng.scan_pending_stats(deferred=False)          # (sharded lookahead run: the last batch's statistics)
-            v1, v2 = eng.launch_prepared(self._pending, deferred=False)
-        eng.ahead -= self._pending["batch"]
-        self._pending = None
+        oldest = self._queue.pop(0)
+        with torch.cuda.device(oldest["device"]):
+            if not self._queue:
+                eng.scan_pending_stats()                        # (sharded run: the last batch's statistics)
+            v1, v2 = eng.launch_prepared(oldest, deferred=False)
+        eng.ahead -= oldest["batch"]
         return self.tfms._post(v1, v2)
+
+    def drain(self):
+        """Every batch still pending, oldest first: a list of (view1, view2)."""
+        out = []
+        while self._queue:
+            out.append(self.flush())
+        return out
 
     def _windows_to_views(self, part, gain, draw):
         """[b, L] windows on the GPU -> log-mel into the ring -> statistics -> two views."""
@@ -251,7 +261,7 @@ class UpstreamInputPipeline:
         b = part.shape[0]
         tiles = self.plan.num_tiles(part.shape[1])
         sums = torch.empty((b, tiles, 2), dtype=torch.float64, device=part.device) if tf.pre_norm else None
-        self.plan.logmel_into(part, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain)
+        self.plan.logmel_into(part, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain, pitch=eng.pitch)
         if tf.pre_norm:
             eng.update_stats(sums, tiles)
         return eng.launch_views(draw(), b, part.device)

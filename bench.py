@@ -209,7 +209,7 @@ class ClockSampler(threading.Thread):
 class Workload:
     """Device-resident step loop for one (per-GPU batch, clip length): the C ABI driven through ctypes with raw pointers
     taken once (~5 us per call, so the host stays ahead of the GPU).  Step order with lookahead, one GPU:
-    log-mel(k) . statistics(k) . views(k-1); across GPUs: scan(k-1) . log-mel(k) . send(k) . views(k-1)."""
+    log-mel(k) . statistics(k) . views(k-1); across GPUs: log-mel(k) . scan(k-1) . send(k) . views(k-2)."""
 
     def __init__(self, A, lib, dev, rank, world, batch, n_samples, exchange_factory, lookahead=True, gbank=False,
                  rotate_bytes=256 << 20, rotate_min=2, seed=1234):
@@ -235,10 +235,12 @@ class Workload:
         self.v2 = torch.empty_like(self.v1)
         self.sums = [torch.empty((B, self.tiles, 2), dtype=torch.float64, device=dev) for _ in range(2)]
         ch, cw = int(N_MELS * 1.0), int(T * 1.5)
-        self.vcfg = _native.ViewCfg(N_MELS, T, ch, cw, 0, 1)
+        self.vcfg = _native.ViewCfg(N_MELS, T, ch, cw, 0, 1, eng.pitch)     # ring rows padded to 16 bytes
+        self.pitch = eng.pitch
         self.max_update = int(eng.max_update)
         self.exchange = exchange_factory(B) if world > 1 else None
         self.split = self.look and self.exchange is not None
+        self.scan_deferred = int(os.environ.get("ASSL_BENCH_SCAN_DEFERRED", "1"))
         # parameter sets: the ring position of step s repeats with period cap / gcd(B, cap); the draws are those of steps far
         # into a run (bank full: every view mixes), so a set fits every step with the same ring position
         gsz = B * world if gbank else B
@@ -287,13 +289,13 @@ class Workload:
         sums = self.p_sums[s & 1]
         rec = (lambda i: events[i].record()) if events is not None else (lambda i: None)
         rec(0)
-        if self.split and s > 0:       # statistics of the PREVIOUS batch: every rank sent its sums a step ago
-            chk(lib.assl_running_stats_exchange_scan(self.exchange.handle, self.p_state, self.elems, self.max_update,
-                                                     self.p_stats, ((s - 1) * B) % cap, cap, 0, 1, st))
-        chk(lib.assl_logmel_f32(self.plan.handle, self.p_waves[s % self.rotate], None, B, L, L, self.p_ring, slot0, cap,
-                                sums, 0, st))
+        chk(lib.assl_logmel_pitched_f32(self.plan.handle, self.p_waves[s % self.rotate], None, B, L, L, self.p_ring, slot0, cap,
+                                        self.pitch, sums, 0, st))
         rec(1)
         if self.split:
+            if s > 0:                  # statistics of the PREVIOUS batch: every rank sent its sums a step ago
+                chk(lib.assl_running_stats_exchange_scan(self.exchange.handle, self.p_state, self.elems, self.max_update,
+                                                         self.p_stats, ((s - 1) * B) % cap, cap, 0, self.scan_deferred, st))
             chk(lib.assl_exchange_send(self.exchange.handle, sums, B, self.tiles, st))
             if self.exchange.staged:
                 self.exchange._gather()
@@ -307,9 +309,10 @@ class Workload:
             chk(lib.assl_running_stats(self.p_state, sums, B, self.tiles, self.elems, self.max_update, 0, B, self.p_stats,
                                        slot0, cap, st))
         rec(2)
-        if self.look:                                # views of the PREVIOUS batch, beside this batch's statistics
-            if s > 0:
-                clip, mix, alpha, crop, order = self.p_sets[(s - 1) % self.n_sets]
+        if self.look:                  # views of an EARLIER batch (one back; two across GPUs), beside this batch's statistics
+            back = 2 if self.split else 1
+            if s >= back:
+                clip, mix, alpha, crop, order = self.p_sets[(s - back) % self.n_sets]
                 chk(lib.assl_two_views_deferred_f32(self.vref, self.p_ring, self.p_stats, cap, clip, mix, alpha, crop, order,
                                                     B, self.p_v1, self.p_v2, st))
         elif self.gbank:
@@ -380,7 +383,7 @@ def sharded_check(A, dev, rank, world):
         p = draws.draw(s * world * b, world * b, N_MELS, T)
         got.append(sharded(wave[rank * b:(rank + 1) * b], params=take(p, rank * b, (rank + 1) * b)))
         want.append(single(wave, params=p))
-    got = got[1:] + [sharded.flush()]
+    got = [o for o in got if o is not None] + sharded.drain()
     torch.cuda.synchronize()
     for a, w in zip(got, want):
         compare(a, w)
@@ -491,7 +494,8 @@ def run_ours(args):
     k_ms = [statistics.fmean(e[i].elapsed_time(e[i + 1]) for e in evs) for i in range(3)]
     exchange_kind = ("none (one GPU)" if world == 1 else
                      ("staged: all-gather of the records" if wl.exchange.staged else "peer memory over NVLink") +
-                     (", send(k) behind log-mel(k) and scan(k-1) a step later" if wl.split else ", fused send + scan"))
+                     (", send(k) behind log-mel(k); scan(k-1) one step later, beside the views of batch k-2" if wl.split
+                      else ", fused send + scan"))
     launches_per_step = wl.launches_per_step
     lookahead_on = wl.look
     wl.close()
@@ -583,7 +587,7 @@ def run_ours(args):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, B),
         "path": {"stats_exchange": exchange_kind,
-                 "step_order": ("scan(k-1), log-mel(k), send(k), views(k-1)" if (lookahead_on and world > 1) else
+                 "step_order": ("log-mel(k), scan(k-1), send(k), views(k-2) (deferred launch)" if (lookahead_on and world > 1) else
                                 "log-mel(k), statistics(k), views(k-1): the views of the previous batch are launched deferred "
                                 "(assl_two_views_deferred_f32, UpstreamInputPipeline(lookahead=True)); every step runs all the "
                                 "kernels" if lookahead_on else "log-mel(k), statistics(k), views(k)"),
@@ -598,7 +602,7 @@ def run_ours(args):
                                       f"timed region (events between the kernels would serialise their dependent launches)"},
         "pipeline_roofline": {"achieved": clips_per_s / world * a_all / 1e9, "peak": peak, "unit": "GB/s",
                               "frac": clips_per_s / world * a_all / 1e9 / peak, "bytes_per_clip": a_all},
-        "kernel_ms": {"logmel(+scan of the previous batch across GPUs)": k_ms[0], "running_stats | send": k_ms[1],
+        "kernel_ms": {"logmel": k_ms[0], "running_stats (across GPUs: scan of the previous batch + send)": k_ms[1],
                       "two_views": k_ms[2]},
         "e2e": {"value": world * B * n_e2e / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * L * 4 + B * 40,
                 "d2h_bytes_per_step": 2 * B * N_MELS * T * 4, "ms_per_step": 1e3 * e2e_s / n_e2e, "checksum": checksum,

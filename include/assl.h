@@ -61,6 +61,8 @@ typedef struct assl_view_cfg {
   int32_t canvas_w;    /* int(T * virtual_crop_scale[1])                                       */
   int32_t interp;      /* 0 = bicubic (reference, augmentations.py:27), 1 = bilinear           */
   int32_t log_mixup;   /* 1 = log-mixup-exp (augmentations.py:8-12), 0 = linear mix (:104)     */
+  int32_t ring_pitch;  /* floats per row of the log-mel ring / array: 0 = n_time (dense rows); a multiple of 4
+                          (with a 16-byte aligned base) lets the kernel read the rows with 128-bit loads   */
 } assl_view_cfg;
 
 int assl_version(void);
@@ -96,6 +98,12 @@ int assl_plan_filterbank(const assl_plan* plan, float* host_out);
 int assl_logmel_f32(const assl_plan* plan, const float* wave, const float* wave_gain, int64_t B,
                     int64_t L, int64_t ld, float* lms, int64_t slot0, int64_t cap,
                     double* tile_sums, int32_t out_kind, void* stream);
+/* The same into slots of [n_mels, pitch] floats, pitch >= T (0 = T): the rings of the two-view path pad their rows to a
+ * multiple of 4 floats so that the two-view kernel reads them with 128-bit loads (assl_view_cfg.ring_pitch).  The
+ * pad columns are never written.  Time-major slots (out_kind | 2) are dense: pitch must be 0 or T. */
+int assl_logmel_pitched_f32(const assl_plan* plan, const float* wave, const float* wave_gain, int64_t B,
+                            int64_t L, int64_t ld, float* lms, int64_t slot0, int64_t cap, int64_t pitch,
+                            double* tile_sums, int32_t out_kind, void* stream);
 
 /* Per-clip sum of squares of the waveform -> gain[b] = 1 / max(||wave_b||_2, 1e-12)
  * (F.normalize(p=2), src/dataset/upstream_dataset.py:62-63). */

@@ -276,3 +276,36 @@ def test_launch_order_does_not_change_the_views():
         outs.append((v1, v2))
     for v1, v2 in outs[1:]:
         assert torch.equal(v1, outs[0][0]) and torch.equal(v2, outs[0][1])
+
+
+@pytest.mark.parametrize("t", [33, 96, 101, 330, 1001])
+def test_padded_ring_rows_give_the_same_bits_as_dense_rows(t):
+    """The two-view kernel reads 16-byte aligned ring rows (assl_view_cfg.ring_pitch, a multiple of 4) with 128-bit loads
+    and dense rows with scalar loads: same arithmetic, same bits, for every tile size and the T that is not a multiple
+    of 4.  Garbage in the pad columns must not leak into a view."""
+    import ctypes as C
+    import audiossl_b200 as A
+    from audiossl_b200 import _native
+    lib = _native.lib()
+    b, f = 24, 64
+    g = torch.Generator(device="cpu").manual_seed(t)
+    dense = torch.randn(b, f, t, generator=g).cuda()
+    pitch = (t + 3) & ~3
+    padded = torch.full((b, f, pitch), float("nan"), device="cuda")      # NaN pads: any use of them would show
+    padded[:, :, :t] = dense
+    stats = torch.stack((torch.randn(b, generator=g) * 0.1, torch.rand(b, generator=g) + 0.5), 1).contiguous().cuda()
+    p = A.FastSampler(seed=5 + t).draw(b, b, f, t)
+    mix = torch.from_numpy(np.where(p.src_clip >= 0, p.src_clip % b, -1).astype(np.int32)).cuda()
+    clip = torch.arange(b, dtype=torch.int32).cuda()
+    alpha, crop = torch.from_numpy(p.alpha).cuda(), torch.from_numpy(p.crop).cuda()
+    P = lambda x: C.c_void_p(x.data_ptr()) if x is not None else None   # noqa: E731
+    outs = []
+    for ring, pt in ((dense, 0), (padded, pitch)):
+        vcfg = _native.ViewCfg(f, t, f, int(t * 1.5), 0, 1, pt)
+        v1, v2 = torch.empty(b, f, t, device="cuda"), torch.empty(b, f, t, device="cuda")
+        _native.check(lib.assl_two_views_f32(C.byref(vcfg), P(ring), P(stats), b, P(clip), P(mix), P(alpha), P(crop), b,
+                                             P(v1), P(v2), None))
+        outs.append((v1, v2))
+    torch.cuda.synchronize()
+    assert torch.isfinite(outs[1][0]).all() and torch.isfinite(outs[1][1]).all()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
