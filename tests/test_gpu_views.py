@@ -166,10 +166,10 @@ def test_fused_pipeline_waveform_to_views():
     pipe = A.UpstreamInputPipeline(CFG, 6)
     v1a, v2a = pipe(waves[:10].cuda())
     v1b, v2b = pipe(waves[10:].cuda())
-    # the log-mel differs from the fp64-FFT oracle within tolerance, so compare the views a bit looser:
-    # the normalised values are O(1) and inherit the absolute log-mel error scaled by 1/std
-    _close(torch.cat([v1a, v1b]), w1, rtol=1e-4, atol=5e-5, what="view1")
-    _close(torch.cat([v2a, v2b]), w2, rtol=1e-4, atol=5e-5, what="view2")
+    # per-family gates of the fused path (noise-like 2e-5, tonal 1e-4): measured in test_gpu_tolerance.py
+    from test_gpu_tolerance import assert_fused_close
+    assert_fused_close(torch.cat([v1a, v1b]), w1, what="view1")
+    assert_fused_close(torch.cat([v2a, v2b]), w2, what="view2")
 
 
 def test_c_abi_host_pipeline_matches_device_pipeline():
@@ -309,3 +309,40 @@ def test_padded_ring_rows_give_the_same_bits_as_dense_rows(t):
     torch.cuda.synchronize()
     assert torch.isfinite(outs[1][0]).all() and torch.isfinite(outs[1][1]).all()
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+def test_delores_s_shard_512_clips_of_15200_samples():
+    """BASELINE config 3's per-GPU shard as one full batch (512 x 0.95 s, /root/reference/src/upstream/delores_s/config.yaml:18)
+    through UpstreamInputPipeline: crop boxes and bank picks bit-exact, views inside the fused-path gates."""
+    import audiossl_b200 as A
+    from test_gpu_frontend import families
+    from test_gpu_tolerance import assert_fused_close
+    waves = families(512, 15200, 512)
+    lms = torch.from_numpy(ofe.log_mel_batch(waves.numpy()))
+    _seed()
+    w1, w2, recs = ov.TwoViewOracle(2000).run_batch(lms)
+    _seed()
+    pipe = A.UpstreamInputPipeline(CFG, 2000, max_batch=512)
+    v1, v2 = pipe(waves.cuda())
+    arrs = ov.records_to_arrays(recs)
+    p = pipe.tfms.last_params
+    assert np.array_equal(p.crop, arrs["crop"]) and np.array_equal(p.src_clip.astype(np.int32), arrs["src_clip"])
+    assert_fused_close(v1, w1, what="view1")
+    assert_fused_close(v2, w2, what="view2")
+
+
+def test_two_views_with_128_mel_bands():
+    """The MAST variant's 128 bands (extras/mast_new/mast/utils.py:251-259) through the two-view kernel: a canvas of 128
+    rows (twice the shared memory per CTA)."""
+    import audiossl_b200 as A
+    g = torch.Generator(device="cpu").manual_seed(128)
+    x = torch.randn(20, 128, 101, generator=g) * 2.0 - 4.0
+    _seed(5)
+    w1, w2, recs = ov.TwoViewOracle(50).run_batch(x)
+    _seed(5)
+    tf = A.AugmentationModule(CFG, 50, max_batch=32)
+    v1, v2 = tf(x.unsqueeze(1).cuda())
+    arrs = ov.records_to_arrays(recs)
+    assert np.array_equal(tf.last_params.crop, arrs["crop"])
+    _close(v1, w1, what="view1")
+    _close(v2, w2, what="view2")

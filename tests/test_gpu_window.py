@@ -99,7 +99,7 @@ def test_raw_clip_pipeline_replays_reference_order():
     assert np.array_equal(p.crop, arrs["crop"]) and np.array_equal(p.src_clip.astype(np.int32), arrs["src_clip"])
     for got, ref in ((v1, torch.stack(want1)), (v2, torch.stack(want2))):
         d = np.abs(got.cpu().numpy() - ref.numpy())
-        assert (d <= 5e-5 + 1e-4 * np.abs(ref.numpy())).all(), d.max()
+        assert (d <= 2e-5 + 1e-4 * np.abs(ref.numpy())).all(), d.max()
 
 
 def test_empty_and_invalid():
@@ -136,7 +136,7 @@ def test_device_batch_loader_matches_reference_epoch():
             a, b = oracle(torch.from_numpy(ofe.log_mel(w)).unsqueeze(0))
             for have, ref in ((got[k][0][r], a), (got[k][1][r], b)):
                 d = np.abs(have.numpy() - ref.numpy())
-                assert (d <= 5e-5 + 1e-4 * np.abs(ref.numpy())).all(), (k, r, d.max())
+                assert (d <= 2e-5 + 1e-4 * np.abs(ref.numpy())).all(), (k, r, d.max())
 
 
 def test_device_batch_loader_with_a_lookahead_pipeline_yields_the_same_epoch():
