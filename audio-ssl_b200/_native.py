@@ -69,6 +69,7 @@ SIGNATURES = {
     "assl_wave_l2_gain_f32": (C.c_int, [_P, _I64, _I64, _I64, _P, _P]),
     "assl_extract_windows_f32": (C.c_int, [_P, _P, _P, _P, _I64, _I64, _P, _I64, _P, _P]),
     "assl_running_stats": (C.c_int, [_P, _P, _I64, _I64, _I64, _I64, _I64, _I64, _P, _I64, _I64, _P]),
+    "assl_running_norm_stats_static_f32": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _I64, _I64, _P]),
     "assl_clip_sums": (C.c_int, [_P, _I64, _I64, _P, _P]),
     "assl_exchange_create": (C.c_int, [C.POINTER(_P), C.c_int32, C.c_int32, _I64, _P]),
     "assl_exchange_connect": (C.c_int, [_P, _P]),

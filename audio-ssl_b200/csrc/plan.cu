@@ -51,6 +51,7 @@ extern "C" const char* assl_status_string(int status) {
     case ASSL_ERR_CUDA: return "CUDA runtime error";
     case ASSL_ERR_NO_DEVICE: return "no CUDA device";
     case ASSL_ERR_PEER_TIMEOUT: return "a peer's statistics records did not arrive in time";
+    case ASSL_ERR_TOO_LARGE: return "more clips than the static scratch holds (ASSL_STATIC_MAX_CLIPS)";
     default: return "unknown status";
   }
 }

@@ -680,3 +680,58 @@ extern "C" int assl_peer_open(const void* handle, void** ptr) {
   return ASSL_OK;
 }
 extern "C" int assl_peer_close(void* ptr) { return cudaIpcCloseMemHandle(ptr) == cudaSuccess ? ASSL_OK : ASSL_ERR_CUDA; }
+
+// ---- running-norm statistics with NO allocation anywhere (assl_running_norm_stats_static_f32) ----------------------
+// No counterpart in the reference: added for callers that cannot allocate (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  assl_clip_moments_f32 followed by
+// assl_running_stats needs a caller-owned [B, 2] fp64 array between the two kernels; here that scratch is a file-scope
+// device array of ASSL_STATIC_MAX_CLIPS entries (64 KB, held by every GPU that loads the library until exit).
+// Every call on a device shares it and it keeps the last call's contents: the first kernel overwrites all B entries
+// the second one reads, so nothing has to start at zero, but two calls that overlap on the GPU (different streams)
+// race on it.
+namespace assl {
+static __device__ __align__(256) double g_static_clip_sums[2 * ASSL_STATIC_MAX_CLIPS];
+}
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+// In host code ``g_static_clip_sums`` is only a stand-in for the symbol, not a device address: the address a kernel can
+// use comes from cudaGetSymbolAddress, asked once per device with that device current.
+int static_clip_sums(double** out) {
+  static std::atomic<double*> addr[kStaticMaxDevices];
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return ASSL_ERR_NO_DEVICE; }
+  if (dev < 0 || dev >= kStaticMaxDevices) return ASSL_ERR_UNSUPPORTED;
+  double* p = addr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    void* sym = nullptr;
+    if (cudaGetSymbolAddress(&sym, assl::g_static_clip_sums) != cudaSuccess || !sym) { cudaGetLastError(); return ASSL_ERR_CUDA; }
+    p = static_cast<double*>(sym);
+    addr[dev].store(p, std::memory_order_release);       // (two threads racing here store the same address)
+  }
+  *out = p;
+  return ASSL_OK;
+}
+}  // namespace
+
+extern "C" int assl_running_norm_stats_static_f32(double* state, const float* x, int64_t B, int64_t elems,
+                                                  int64_t max_update, float* mean_std, int64_t slot0, int64_t cap,
+                                                  void* stream) {
+  using namespace assl;
+  if (!state || !x || !mean_std || B < 0 || elems < 1 || max_update < 1 || slot0 < 0 || cap < 0) return ASSL_ERR_INVALID_ARG;
+  if (B > ASSL_STATIC_MAX_CLIPS) return ASSL_ERR_TOO_LARGE;       // the static scratch holds ASSL_STATIC_MAX_CLIPS clips
+  if (cap > 0 && (B > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
+  if (B == 0) return ASSL_OK;
+  double* sums = nullptr;
+  const int rc = static_clip_sums(&sums);
+  if (rc != ASSL_OK) return rc;
+  cudaStream_t st = as_stream(stream);
+  clip_moments_kernel<<<static_cast<unsigned>(B), 256, 0, st>>>(x, elems, sums);
+  if (launch_status() != ASSL_OK) return ASSL_ERR_CUDA;
+  if (launch_pdl(running_stats_kernel, dim3(kStatCtas), dim3(kScanThreads), 0, st, state, static_cast<const double*>(sums),
+                 static_cast<long long>(B), 1ll, 1.0 / static_cast<double>(elems), static_cast<long long>(max_update), 0ll,
+                 static_cast<long long>(B), mean_std, static_cast<long long>(slot0), static_cast<long long>(cap), ExArgs(),
+                 static_cast<const double*>(nullptr), 0ll, 0ll) != cudaSuccess)
+    return ASSL_ERR_CUDA;
+  return launch_status();
+}

@@ -38,7 +38,8 @@ typedef enum assl_status {
   ASSL_ERR_UNSUPPORTED = 2,   /* shape/config outside what the kernels are built for           */
   ASSL_ERR_CUDA = 3,          /* allocation / copy / launch failure reported by the runtime    */
   ASSL_ERR_NO_DEVICE = 4,     /* no sm_100 device visible                                      */
-  ASSL_ERR_PEER_TIMEOUT = 5   /* a peer's statistics records did not arrive (assl_exchange_error) */
+  ASSL_ERR_PEER_TIMEOUT = 5,  /* a peer's statistics records did not arrive (assl_exchange_error) */
+  ASSL_ERR_TOO_LARGE = 6      /* more clips than the static scratch of a no-allocation entry point holds */
 } assl_status;
 
 /* Front-end constants: MelSpectrogramLibrosa.__init__ defaults, src/utils/utils.py:22. */
@@ -145,6 +146,24 @@ int assl_clip_moments_f32(const float* x, int64_t B, int64_t elems, double* sums
  * RunningNorm.forward (augmentations.py:282) on its own. */
 int assl_clip_normalize_f32(const float* x, float* y, int64_t B, int64_t elems, const float* mean_std,
                             int64_t slot0, int64_t cap, void* stream);
+
+/* -- running pre-normalisation statistics, no allocation anywhere ---------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same result as assl_clip_moments_f32(x, B, elems, sums) followed by assl_running_stats(state, sums, B, 1, elems,
+ * max_update, 0, B, mean_std, slot0, cap) -- the same two kernels -- but the [B, 2] fp64 array between them is a
+ * file-scope device array inside the library instead of a caller buffer: the call (and everything under it) makes no
+ * cudaMalloc / cudaFree and calls no allocating library routine.  The caller still owns x, state and mean_std.
+ *   - B <= ASSL_STATIC_MAX_CLIPS (4096 clips = 64 KB, held by every GPU that loads the library until the process
+ *     exits); a larger B returns ASSL_ERR_TOO_LARGE and launches nothing;
+ *   - every call on a device shares that array and it keeps the last call's contents.  Nothing has to start at zero
+ *     (the first kernel overwrites every entry the second one reads), but two calls that overlap on the GPU --
+ *     different streams, no ordering between them -- race on it: keep calls on one device in stream order;
+ *   - the array's device address is looked up once per device, on the first call made with that device current.   */
+#define ASSL_STATIC_MAX_CLIPS 4096
+int assl_running_norm_stats_static_f32(double* state, const float* x, int64_t B, int64_t elems,
+                                       int64_t max_update, float* mean_std, int64_t slot0, int64_t cap,
+                                       void* stream);
 
 /* Reduce tile_sums [B, n_parts, 2] -> clip_sums [B, 2] (what ranks all-gather). */
 int assl_clip_sums(const double* tile_sums, int64_t B, int64_t n_parts, double* clip_sums,
