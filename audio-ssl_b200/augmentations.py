@@ -269,6 +269,15 @@ class Kmix(nn.Module):
     def memory_bank_size(self):
         return int(self._bank_cluster.shape[0])
 
+    def state_dict(self):
+        """Bank (the engine's ring) + the cluster of every bank entry; the np.random / random generator states are the
+        caller's to save, as in the reference."""
+        return {"engine": self._engine.state_dict(), "bank_cluster": self._bank_cluster.copy()}
+
+    def load_state_dict(self, sd):
+        self._engine.load_state_dict(sd["engine"])
+        self._bank_cluster = np.asarray(sd["bank_cluster"], np.int32).copy()
+
     def _clusters(self, xb):
         lib = _native.lib()
         b, f, t = xb.shape

@@ -119,10 +119,15 @@ class AugmentationModule:
         return p
 
     def state_dict(self):
-        return self.engine.state_dict()
+        sd = self.engine.state_dict()
+        if self.kmix is not None:
+            sd["kmix"] = self.kmix.state_dict()
+        return sd
 
     def load_state_dict(self, sd):
         self.engine.load_state_dict(sd)
+        if self.kmix is not None and "kmix" in sd:
+            self.kmix.load_state_dict(sd["kmix"])
 
 
 class UpstreamInputPipeline:

@@ -3,7 +3,8 @@
 ``ReferenceSampler`` replays the reference's exact draw order on the SAME generators the reference
 uses -- numpy's global ``np.random`` and python's ``random`` module -- so that a training script that
 seeds them (``np.random.seed(31); random.seed(31)``, /root/reference/extras/delores-s/main.py:64) gets
-bit-identical crop boxes and mixup selections:
+bit-identical crop boxes and mixup selections (with a ``Kmix`` stage configured its data-dependent draws come after the
+batch's draws instead of interleaved per view, so the replay is bit-exact only WITHOUT Kmix; see module.py):
 
     per view:  np.random.random()            -> alpha      (MixupBYOLA.forward, augmentations.py:99)
                np.random.randint(len(bank))  -> bank entry (:102, only when the bank is not empty)
