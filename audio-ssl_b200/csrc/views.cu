@@ -114,35 +114,31 @@ struct Geo {
   int n4;                // float4 groups per staged row in use
 };
 
+// The per-view parameters, all loaded in ONE hop right after the view id is known (they were four dependent hops:
+// order -> slots -> statistics -> rows); the (mean, std) pairs follow while the geometry is worked out.
+struct Sel {
+  const float* xp;       // the clip's log-mel in the ring
+  const float* zp;       // the bank entry's (this ring or a peer's)
+  float mu, sd, zmu, zsd, al;
+  bool mix;              // there is a bank entry
+};
+
 // ---- stage A for one warp's rows: normalise + mix into shared memory.
 //      exp(xn) = ex2(x*a + b) with a = log2e/std, b = -mean*log2e/std: one FFMA + one MUFU per operand.
 //      LOGMIX (log-mixup-exp against a bank entry, the path's normal case) is a separate instantiation; the other
 //      modes (no bank entry yet, plain mixup) share the generic one.  G = 32-lane groups of float4 the in-clip part of a
 //      row needs (1 for clips up to 125 frames per tile span, else 2).  VEC: ring rows are 16-byte aligned (pitch % 4 == 0).
-template <int G, bool GB, bool LOGMIX, bool VEC>
-__device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, float* s_src, long long b, int v, int lane, int warp) {
+template <int G, bool LOGMIX, bool VEC, typename Mid>
+__device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, const Sel& sel, float* s_src, int lane, int warp, Mid mid) {
   const int F = a.c.n_freq, T = a.c.n_time;
-  const long long plane = static_cast<long long>(F) * a.pitch;
-  // GB (global bank, a separate instantiation so the default kernel keeps its register budget): the bank entry may
-  // sit in a peer's ring (loads over NVLink) and the (mean, std) pairs live in a ring over global clips
-  const int xslot = a.clip_slot[b];
-  const int xstat = (GB && a.clip_stat) ? a.clip_stat[b] : xslot;
-  const float* xp = a.lms + xslot * plane;
-  float mu = 0.f, inv = 1.f;
-  if (a.mean_std) { mu = a.mean_std[2 * xstat]; inv = 1.f / a.mean_std[2 * xstat + 1]; }
-  const int zslot = a.mix_slot[b * 2 + v];
-  const bool mix = LOGMIX || zslot >= 0;
-  const int zstat = (GB && a.mix_stat) ? a.mix_stat[b * 2 + v] : zslot;
-  const float* zbase = a.lms;
-  if (GB) { if (a.mix_rank && mix) zbase = a.peer_lms[a.mix_rank[b * 2 + v]]; }
-  const float* zp = zbase + (mix ? zslot : 0) * plane;
-  float zmu = 0.f, zinv = 1.f;
-  if (mix && a.mean_std) { zmu = a.mean_std[2 * zstat]; zinv = 1.f / a.mean_std[2 * zstat + 1]; }
-  const float al = a.alpha[b * 2 + v];
-  const float wx = 1.f - al, wz = al;
+  const float* xp = sel.xp;
+  const float* zp = sel.zp;
+  const bool mix = LOGMIX || sel.mix;
+  const float inv = 1.f / sel.sd, zinv = 1.f / sel.zsd;
+  const float wx = 1.f - sel.al, wz = sel.al;
   const float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
-  const float xa = LOGMIX ? inv * kLog2e : inv, xb = -mu * xa;
-  const float za = LOGMIX ? zinv * kLog2e : zinv, zb = -zmu * za;
+  const float xa = LOGMIX ? inv * kLog2e : inv, xb = -sel.mu * xa;
+  const float za = LOGMIX ? zinv * kLog2e : zinv, zb = -sel.zmu * za;
 
   // this lane's float4 groups: j = j_in0 + lane + 32 q; their clip columns col .. col + 3.  Everything that does not
   // depend on the row is worked out here, once: the row loop below only advances pointers.
@@ -242,6 +238,7 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, floa
   };
 #pragma unroll
   for (int d = 0; d < kDepth - 1; ++d) fetch(d, warp + kViewWarps * d);
+  mid();                                                        // (the CTA's tap tables, while the first rows are in flight)
   for (int y = warp; y < g.h; y += kViewWarps * kDepth) {       // (unrolled by kDepth so that the register sets are static)
 #pragma unroll
     for (int d = 0; d < kDepth; ++d) {
@@ -254,11 +251,12 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, floa
   __syncwarp();
 }
 
-template <int G, bool GB, bool VEC>
-__device__ __forceinline__ void stage_rows_any(const ViewArgs& a, const Geo& g, float* s_src, long long b, int v, int lane, int warp) {
-  const bool logmix = a.mix_slot[b * 2 + v] >= 0 && a.c.log_mixup;          // CTA-uniform
-  if (logmix) stage_rows<G, GB, true, VEC>(a, g, s_src, b, v, lane, warp);
-  else stage_rows<G, GB, false, VEC>(a, g, s_src, b, v, lane, warp);
+template <int G, bool VEC, typename Mid>
+__device__ __forceinline__ void stage_rows_any(const ViewArgs& a, const Geo& g, const Sel& sel, float* s_src, int lane, int warp,
+                                               Mid mid) {
+  const bool logmix = sel.mix && a.c.log_mixup;                 // CTA-uniform
+  if (logmix) stage_rows<G, true, VEC>(a, g, sel, s_src, lane, warp, mid);
+  else stage_rows<G, false, VEC>(a, g, sel, s_src, lane, warp, mid);
 }
 
 // TW = output frames per tile (32 / 64 / 128)
@@ -282,9 +280,36 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
   const int v = static_cast<int>(blk & 1u);
   const long long b = blk >> 1;
 
+  // ---- every per-view parameter in one hop ...
+  const int4 cr = __ldg(reinterpret_cast<const int4*>(a.crop) + (b * 2 + v));
+  const int xslot = __ldg(a.clip_slot + b);
+  const int zslot = __ldg(a.mix_slot + (b * 2 + v));
+  Sel sel;
+  sel.al = __ldg(a.alpha + (b * 2 + v));
+  sel.mix = zslot >= 0;
+  // GB (global bank, a separate instantiation so the default kernel keeps its register budget): the bank entry may
+  // sit in a peer's ring (loads over NVLink) and the (mean, std) pairs live in a ring over global clips
+  int xstat = xslot, zstat = zslot;
+  const float* zbase = a.lms;
+  if (GB) {
+    if (a.clip_stat) { xstat = a.clip_stat[b]; zstat = a.mix_stat[b * 2 + v]; }
+    if (a.mix_rank && sel.mix) zbase = a.peer_lms[a.mix_rank[b * 2 + v]];
+  }
+  {
+    const long long plane = static_cast<long long>(F) * a.pitch;
+    sel.xp = a.lms + xslot * plane;
+    sel.zp = zbase + (sel.mix ? zslot : 0) * plane;
+  }
+  // ... then the two (mean, std) pairs, in flight while the geometry and the first row addresses are worked out
+  sel.mu = 0.f; sel.sd = 1.f; sel.zmu = 0.f; sel.zsd = 1.f;
+  if (a.mean_std) {
+    const float2 xs = __ldg(reinterpret_cast<const float2*>(a.mean_std) + xstat);
+    sel.mu = xs.x; sel.sd = xs.y;
+    if (sel.mix) { const float2 zs = __ldg(reinterpret_cast<const float2*>(a.mean_std) + zstat); sel.zmu = zs.x; sel.zsd = zs.y; }
+  }
+
   Geo g;
   {
-    const int4 cr = *reinterpret_cast<const int4*>(a.crop + (b * 2 + v) * 4);
     // the host mirror validates crops; the clamps only keep a bad box from leaving shared memory
     g.h = min(max(cr.z, 1), a.c.canvas_h); g.w = min(max(cr.w, 1), a.c.canvas_w);
     g.ci = min(max(cr.x, 0), a.c.canvas_h - g.h); g.cj = min(max(cr.y, 0), a.c.canvas_w - g.w);
@@ -308,25 +333,28 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
     g.j_in1 = max(min(hi, g.n4), g.j_in0);
   }
 
-  // ---- taps, once per CTA: frequency (shared by every column of the tile), time (shared by every row)
-  for (int oy = tid; oy < F; oy += kViewThreads) {
-    int iy; float ty;
-    source_index(oy, g.h, F, &iy, &ty);
-    s_wy[oy] = tap_weights(ty, bil);
-    const int rb = a.src_w * 4;
-    s_ya[oy] = make_int4(min(max(iy - 1, 0), g.h - 1) * rb, min(max(iy, 0), g.h - 1) * rb,
-                         min(max(iy + 1, 0), g.h - 1) * rb, min(max(iy + 2, 0), g.h - 1) * rb);
-  }
-  for (int c = tid; c < TW; c += kViewThreads) {
-    int ix; float tx;
-    source_index(g.ox0 + min(c, g.ncol - 1), g.w, T, &ix, &tx);
-    s_wx[c] = tap_weights(tx, bil);
-    s_xu[c] = 4 * min(max(ix - 1 - g.xs_lo + g.xo, 0), a.src_w - 4);
-  }
+  // ---- taps, once per CTA: frequency (shared by every column of the tile), time (shared by every row).  Built by every
+  //      warp right after it has issued its first row loads (stage A calls this back), i.e. under their latency.
+  auto tap_tables = [&]() {
+    for (int oy = tid; oy < F; oy += kViewThreads) {
+      int iy; float ty;
+      source_index(oy, g.h, F, &iy, &ty);
+      s_wy[oy] = tap_weights(ty, bil);
+      const int rb = a.src_w * 4;
+      s_ya[oy] = make_int4(min(max(iy - 1, 0), g.h - 1) * rb, min(max(iy, 0), g.h - 1) * rb,
+                           min(max(iy + 1, 0), g.h - 1) * rb, min(max(iy + 2, 0), g.h - 1) * rb);
+    }
+    for (int c = tid; c < TW; c += kViewThreads) {
+      int ix; float tx;
+      source_index(g.ox0 + min(c, g.ncol - 1), g.w, T, &ix, &tx);
+      s_wx[c] = tap_weights(tx, bil);
+      s_xu[c] = 4 * min(max(ix - 1 - g.xs_lo + g.xo, 0), a.src_w - 4);
+    }
+  };
 
   // ---- stage A (this warp's rows), with as many 32-lane groups of float4 as the in-clip part of THIS span needs
-  if (g.j_in1 - g.j_in0 <= 32) stage_rows_any<1, GB, VEC>(a, g, s_src, b, v, lane, warp);
-  else stage_rows_any<2, GB, VEC>(a, g, s_src, b, v, lane, warp);
+  if (g.j_in1 - g.j_in0 <= 32) stage_rows_any<1, VEC>(a, g, sel, s_src, lane, warp, tap_tables);
+  else stage_rows_any<2, VEC>(a, g, sel, s_src, lane, warp, tap_tables);
   __syncthreads();                             // (the tap tables; the rows themselves stay with their warp until stage C)
 
   // ---- stage B, along time: lanes <-> output columns, the four taps of a column are four consecutive floats of the row
