@@ -33,12 +33,12 @@
 
 namespace assl {
 
-constexpr int kMaxWarps = 20;                       // per CTA: 16 at 128 registers, 20 at 96 (one CTA per SM holds the register file)
+constexpr int kMaxWarps = 16;                       // per CTA (128 registers x 512 threads = the register file)
 constexpr int kExStride = 34;                       // float2 units: lane-major rows of 32 + 2 pad (272 B: 128-bit
                                                     // row stores of a quarter warp hit 8 distinct 16-byte bank groups)
-constexpr int kExWarp = 32 * kExStride + 2;         // 1090 float2 = 8720 B per warp: the transposition's rows
-constexpr int kScratch = 520;                       // float2 offset of the interval totals inside a warp's buffer (a part
-                                                    // reads power bins up to 512 + 7; kScratchEntries x 16 B fit behind)
+constexpr int kExWarp = 32 * kExStride + 2;         // 1090 float2 = 8720 B per warp
+constexpr int kScratch = 640;                       // float2 offset of the interval totals inside a warp's buffer
+                                                    // (padded power reads stay below 640; kScratchEntries x 16 B fit behind)
 static_assert(kScratch + 2 * kScratchEntries <= 32 * kExStride, "interval totals overflow the warp buffer");
 constexpr int kTwStride = 10;                       // float2 units: per lane w^8, w^16, w^24, w^1..w^7 (w = W_1024^lane);
                                                     // 80-byte rows: an odd number of 16-byte groups, conflict-free
@@ -68,10 +68,6 @@ struct LogmelArgs {
   int ppc_sh1, ppc_sh2;
   int total_pairs;
   int wave_floats;    // per-warp staging buffer (n_fft + hop, rounded up to 4)
-  int warp_c32;       // float2 units of a warp's exchange buffer (>= kExWarp)
-  int stage_c32;      // >= 0: the staging buffer lives INSIDE the exchange buffer at this float2 offset (behind the power
-                      // spectra and the interval totals) and a pair's span is fetched once the transposed columns of the
-                      // pair before have been read; < 0: a buffer of its own, fetched as soon as the span is in registers
   int n_slots;        // rows of lane_iv in use
   const float2* tw;
   const int4* lane_iv;   // [kIvSlots][32] interval part owned by (slot, lane), see assl_plan::d_lane_iv
@@ -84,11 +80,11 @@ struct LogmelArgs {
   int span4;             // (n_fft + hop) & ~3: what one bulk copy covers for every other pair
 };
 
-__host__ __device__ inline size_t logmel_smem_bytes(int warps, int wave_floats, int warp_c32, bool stage_inside) {
+__host__ __device__ inline size_t logmel_smem_bytes(int warps, int wave_floats) {
   size_t b = 0;
-  b += sizeof(float2) * warps * warp_c32;   // exchange / power / interval-sum (/ staging) buffers
+  b += sizeof(float2) * warps * kExWarp;    // exchange / power / interval-sum buffers
   b += sizeof(float2) * 32 * kTwStride;     // twiddles
-  if (!stage_inside) b += sizeof(float) * warps * wave_floats;   // staging
+  b += sizeof(float) * warps * wave_floats; // staging
   b += sizeof(int4) * kMaxMels;             // per-band {scratch offsets of its two edges, enorm, folded eps}
   b += sizeof(int4) * kIvSlots * 32;        // interval ownership
   b += sizeof(unsigned long long) * (kMaxWarps + 32);  // one mbarrier per warp + the ticket counter's address, per lane
@@ -177,23 +173,21 @@ __device__ __forceinline__ void pair_cover(const LogmelArgs& a, int q, int span,
 }
 
 // H32 = hop / 32 when hop is a multiple of 32 (both frames of a pair share registers), else 0
-// W = most warps per CTA this instantiation is launched with (its register budget: 65536 / (32 W))
-template <int H32, int W>
-__global__ void __launch_bounds__(W * 32, 1) logmel_kernel(const LogmelArgs a) {
+template <int H32>
+__global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int n_warps = blockDim.x >> 5;
   float2* s_ex = reinterpret_cast<float2*>(smem_raw);
-  float2* s_tw = s_ex + n_warps * a.warp_c32;
+  float2* s_tw = s_ex + n_warps * kExWarp;
   float* s_wave = reinterpret_cast<float*>(s_tw + 32 * kTwStride);
-  const bool stage_inside = a.stage_c32 >= 0;
-  int4* s_band = reinterpret_cast<int4*>(s_wave + (stage_inside ? 0 : n_warps * a.wave_floats));   // [n_mels]
+  int4* s_band = reinterpret_cast<int4*>(s_wave + n_warps * a.wave_floats);   // [n_mels]
   int4* s_lane = s_band + kMaxMels;                                          // [kIvSlots][32]
   unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_lane + kIvSlots * 32);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n_threads = blockDim.x;
   void* bar = s_bar + warp;                  // this warp's span has landed (tx bytes)
-  float* buf = stage_inside ? reinterpret_cast<float*>(s_ex + warp * a.warp_c32 + a.stage_c32) : s_wave + warp * a.wave_floats;
+  float* buf = s_wave + warp * a.wave_floats;
 
   if (lane == 0) mbar_init(bar, 1);
   if (tid < 32) s_bar[kMaxWarps + tid] = reinterpret_cast<unsigned long long>(a.ticket);   // (see draw_ticket)
@@ -255,7 +249,7 @@ __global__ void __launch_bounds__(W * 32, 1) logmel_kernel(const LogmelArgs a) {
   unsigned* const ticket_ctr = reinterpret_cast<unsigned*>(s_bar[kMaxWarps + lane]);
   if (lane == 0 && a.ticket && nxt < a.total_pairs) ticket = draw_ticket(ticket_ctr);
 
-  c32* ex = reinterpret_cast<c32*>(s_ex + warp * a.warp_c32);
+  c32* ex = reinterpret_cast<c32*>(s_ex + warp * kExWarp);
   const unsigned scratch_addr = smem_u32(ex + kScratch);
   unsigned it = 0;
   while (cur < a.total_pairs) {
@@ -312,7 +306,7 @@ __global__ void __launch_bounds__(W * 32, 1) logmel_kernel(const LogmelArgs a) {
     // the span is in registers: the next pair's copy may overwrite the buffer and lands behind this pair's compute
     __syncwarp();
     const PairPos pn = pair_pos(a, nxt);
-    if (!stage_inside && a.bulk_ok && lane == 0 && nxt < a.total_pairs) issue(pn);
+    if (a.bulk_ok && lane == 0 && nxt < a.total_pairs) issue(pn);
     // the pair after that: the ticket drawn one pair ago has long arrived; draw the next one
     int nn = nxt + stride;
     if (a.ticket) {
@@ -347,10 +341,6 @@ __global__ void __launch_bounds__(W * 32, 1) logmel_kernel(const LogmelArgs a) {
     __syncwarp();
 #pragma unroll
     for (int n1 = 0; n1 < 32; ++n1) z[n1] = ex[n1 * kExStride + lane];
-    if (stage_inside) {                              // the rows have been read: the next span may land in their upper part
-      __syncwarp();
-      if (a.bulk_ok && lane == 0 && nxt < a.total_pairs) issue(pn);
-    }
     fft32p(z);                                       // over n1 -> k1, this lane is k2: Z[lane + 32*k1]
 
     // unpack: X1[k] = (Z[k] + conj Z[N-k]) / 2, X2[k] = (Z[k] - conj Z[N-k]) / 2i  (the 1/2 sits in the window)
@@ -470,11 +460,11 @@ __global__ void __launch_bounds__(256) wave_l2_gain_kernel(const float* wave, lo
   }
 }
 
-template <int H32, int W>
+template <int H32>
 int launch_logmel(const LogmelArgs& a, size_t smem, unsigned grid, int warps, cudaStream_t st) {
-  if (cudaFuncSetAttribute(logmel_kernel<H32, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
+  if (cudaFuncSetAttribute(logmel_kernel<H32>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
     return ASSL_ERR_CUDA;
-  if (launch_pdl(logmel_kernel<H32, W>, dim3(grid), dim3(warps * 32), smem, st, a) != cudaSuccess) return ASSL_ERR_CUDA;
+  if (launch_pdl(logmel_kernel<H32>, dim3(grid), dim3(warps * 32), smem, st, a) != cudaSuccess) return ASSL_ERR_CUDA;
   return launch_status();
 }
 
@@ -535,23 +525,11 @@ extern "C" int assl_logmel_pitched_f32(const assl_plan* p, const float* wave, co
     const int64_t room = L - span + kNfft / 2;                                // 2 q hop <= room: the span ends inside the clip
     a.q_edge_hi = (span % 4 != 0 || room < 0) ? 0 : static_cast<int>(room / (2 * a.hop) + 1);
   }
-  // Warps per CTA (one CTA per SM) and where the staging buffer lives.  ASSL_LOGMEL_LAYOUT=inside puts it into the
-  // exchange buffer, behind the power spectra and the interval totals (10.0 KB per warp instead of 13.4 KB: 20 warps fit,
-  // at 96 registers each); the default keeps a buffer of its own (16 warps at 128 registers).  ASSL_LOGMEL_WARPS overrides.
-  static const bool inside_env = [] { const char* e = getenv("ASSL_LOGMEL_LAYOUT"); return e && e[0] == 'i'; }();
-  const bool stage_inside = inside_env;
-  int n_pos = 0;
-  for (int v : p->h_iv_pos) n_pos = n_pos > v + 1 ? n_pos : v + 1;
-  a.stage_c32 = -1; a.warp_c32 = kExWarp;
-  if (stage_inside) {
-    a.stage_c32 = (kScratch + 2 * n_pos + 1) & ~1;                              // 16-byte aligned, behind the totals in use
-    const int need = a.stage_c32 + a.wave_floats / 2;
-    a.warp_c32 = ((need > kExWarp ? need : kExWarp) + 1) & ~1;
-  }
-  int warps = stage_inside ? kMaxWarps : 16;
+  // as many warps per CTA (one CTA per SM) as shared memory allows
+  int warps = kMaxWarps;
   if (const char* e = getenv("ASSL_LOGMEL_WARPS")) { const int w = atoi(e); if (w >= 1 && w <= kMaxWarps) warps = w; }
-  while (warps > 1 && logmel_smem_bytes(warps, a.wave_floats, a.warp_c32, stage_inside) > 227 * 1024) --warps;
-  const size_t smem = logmel_smem_bytes(warps, a.wave_floats, a.warp_c32, stage_inside);
+  while (warps > 1 && logmel_smem_bytes(warps, a.wave_floats) > 227 * 1024) --warps;
+  const size_t smem = logmel_smem_bytes(warps, a.wave_floats);
   if (smem > 227 * 1024) return ASSL_ERR_UNSUPPORTED;
   const int64_t ctas = (total_pairs + warps - 1) / warps;
   const unsigned grid = static_cast<unsigned>(ctas < p->sm_count ? ctas : p->sm_count);
@@ -562,12 +540,8 @@ extern "C" int assl_logmel_pitched_f32(const assl_plan* p, const float* wave, co
   static const bool tickets_on = [] { const char* e = getenv("ASSL_LOGMEL_TICKETS"); return !(e && e[0] == '0'); }();
   if (tickets_on && total_pairs > 2ll * grid * warps)
     a.ticket = p->d_tickets + 2 * (p->ticket_seq.fetch_add(1u, std::memory_order_relaxed) % assl_plan::kTicketSlots);
-  if (warps <= 16) {
-    if (a.hop == 160) return launch_logmel<5, 16>(a, smem, grid, warps, as_stream(stream));
-    return launch_logmel<0, 16>(a, smem, grid, warps, as_stream(stream));
-  }
-  if (a.hop == 160) return launch_logmel<5, kMaxWarps>(a, smem, grid, warps, as_stream(stream));
-  return launch_logmel<0, kMaxWarps>(a, smem, grid, warps, as_stream(stream));
+  if (a.hop == 160) return launch_logmel<5>(a, smem, grid, warps, as_stream(stream));
+  return launch_logmel<0>(a, smem, grid, warps, as_stream(stream));
 }
 
 extern "C" int assl_wave_l2_gain_f32(const float* wave, int64_t B, int64_t L, int64_t ld, float* gain, void* stream) {
