@@ -148,3 +148,41 @@ def test_global_bank_index_mapping():
     assert heavy_first(crop, 101, 151).tolist() == [1, 2, 0, 3]
     assert heavy_first(np.array([[[0, 0, 64, 60], [0, 40, 64, 60]]], np.int32), 101, 151).tolist() == [0, 1]
     assert heavy_first(np.array([[[0, 0, 64, 50], [0, 40, 64, 50]]], np.int32), 101, 151).tolist() == [1, 0]
+
+
+def _worker_depth(rank, world, port, out_q):
+    """Ring depth and mixup-source bounds of the lookahead orders on the host (no GPU)."""
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from audiossl_b200.engine import ViewEngine
+    b = 64
+    rows = []
+    for kw in (dict(), dict(lookahead=True), dict(lookahead=True, sync_stats=False), dict(lookahead=True, normalize=False)):
+        e = ViewEngine(max_batch=b, max_update=10 ** 6 if kw.get("normalize", True) else None, **kw)
+        rows.append((e.depth, e.cap, e.split_stats))
+    out_q.put((rank, rows))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_lookahead_depth_across_ranks():
+    """Across ranks with synchronised statistics the views run TWO batches behind the front end (the scan of batch k-1
+    runs beside the views of batch k-2) and the ring is two batches deeper; otherwise one, or none."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 33500 + os.getpid() % 2000
+    world, b = 2, 64
+    procs = [ctx.Process(target=_worker_depth, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, rows in res:
+        assert rows == [(0, 1024 + b, False), (2, 1024 + 3 * b, True), (1, 1024 + 2 * b, False), (1, 1024 + 2 * b, False)]
+    # one process: lookahead is one batch deep
+    from audiossl_b200.engine import ViewEngine
+    e = ViewEngine(max_batch=b, max_update=10, lookahead=True)
+    assert (e.depth, e.cap, e.split_stats) == (1, 1024 + 2 * b, False)
