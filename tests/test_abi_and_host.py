@@ -141,3 +141,30 @@ def test_lookahead_ring_bookkeeping_on_the_host():
     assert look.head == 6 * 64 and look.slot0 == (6 * 64) % look.cap
     with pytest.raises(RuntimeError):
         look.state_dict()
+
+
+def test_bank_picks_are_bounded_by_the_fifo_not_by_the_ring(A):
+    """ViewEngine.prepare_views: a mixup source must be one of the last ``history`` clips (or, for view 2, the clip itself);
+    with lookahead the ring holds more than that, and slots older than the FIFO have been overwritten by the front end."""
+    import numpy as np
+    import pytest
+    from audiossl_b200.engine import ViewEngine
+    b = 8
+    eng = ViewEngine(max_batch=b, max_update=10, lookahead=True)
+    eng.f, eng.t, eng.pitch = 64, 101, 104
+    g0 = 5000
+
+    def params(src):
+        crop = np.tile(np.array([0, 25, 64, 101], np.int32), (b, 2, 1))
+        return A.ViewParams(np.zeros((b, 2), np.float32), src, np.zeros((b, 2), np.int32), crop)
+
+    ok = np.full((b, 2), -1, np.int64)
+    ok[0] = (g0 - eng.history, g0)                         # oldest entry still in the FIFO; the clip itself
+    bad_old = ok.copy(); bad_old[0, 0] = g0 - eng.history - 1      # still inside the RING (cap = history + 2 b), not in the FIFO
+    bad_new = ok.copy(); bad_new[3, 1] = g0 + 4                    # a clip that comes later in the batch
+    for src in (bad_old, bad_new):
+        with pytest.raises(ValueError, match="mixup source outside the bank"):
+            eng.prepare_views(params(src), b, "cpu", g0)
+    assert g0 - eng.history - 1 >= g0 + b - eng.cap        # (the old ring-based check would have let bad_old through)
+    prep = eng.prepare_views(params(ok), b, "cpu", g0)     # passes the checks (tensors stay on the CPU here)
+    assert prep["mix"][0].tolist() == [(g0 - eng.history) % eng.cap, g0 % eng.cap]
