@@ -154,15 +154,11 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, cons
   const bool row_a = lane < g.n4, row_b = lane + 32 < g.n4;                   // groups lane and lane + 32 exist
   const bool zero_a = row_a && (lane < g.j_in0 || lane >= g.j_in1);
   const bool zero_b = row_b && (lane + 32 < g.j_in0 || lane + 32 >= g.j_in1);
-  // the crop's edge columns are copied into the slots just outside it (taps clamp to the crop): which slots, if any
+  // the crop's edge columns are copied into the slots just outside it (taps clamp to the crop) in one pass over the
+  // warp's rows at the end: which slots, if any
   const int u_first = g.xo + (0 - g.xs_lo);                    // slot of crop column 0
   const int u_last = g.xo + (g.w - 1 - g.xs_lo);               // slot of crop column w - 1
   const int u_end = g.xo + g.nslots;                           // one past the last slot in use
-  int fix_dst = -1, fix_src = 0;
-  if (lane == 0 && g.xs_lo < 0) { fix_dst = u_first - 1; fix_src = u_first; }
-  if (lane >= 1 && lane <= 2 && u_last + lane < u_end) { fix_dst = u_last + lane; fix_src = u_last; }
-  const int fix_col = g.d4 + fix_src;                          // clip column of the copied slot: outside [0, T) it is canvas
-  const bool fix_zero = fix_col < 0 || fix_col >= T;
 
   auto load4 = [&](const float* p, int c) -> float4 {          // (dense rows: c = the group's first column)
     if (VEC) return __ldg(reinterpret_cast<const float4*>(p));
@@ -183,69 +179,83 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, cons
     return xn;
   };
 
-  // Rows y = warp, warp + 8, ...: the same warp resamples them along time afterwards, so stage A -> stage B needs no
-  // CTA-wide barrier.  The loads run kDepth - 1 rows ahead of the arithmetic (kDepth register sets): a warp waits for
-  // global memory once, not once per row.
+  // Rows y = warp + 8 k, k < K: the same warp resamples them along time afterwards, so stage A -> stage B needs no
+  // CTA-wide barrier.  Clip rows 8 k - r0 grow with k, so the warp's rows INSIDE the clip are one range [k0, k1) -- all of
+  // them when the canvas is as high as the clip -- and the loop over it carries no per-row tests; canvas rows above /
+  // below are zero-filled apart.  The loads run kDepth - 1 rows ahead of the arithmetic (kDepth register sets): a warp
+  // waits for global memory once, not once per row.
   constexpr int kDepth = G == 1 ? 3 : 1;                       // (two groups per lane: no room for a second register set)
+  const int K = warp < g.h ? (g.h - warp + kViewWarps - 1) / kViewWarps : 0;
+  const int r0 = a.y0 - g.ci - warp;
+  const int k0 = min(r0 > 0 ? (r0 + kViewWarps - 1) / kViewWarps : 0, K);
+  const int k1 = min(max(F + r0 > 0 ? (F + r0 + kViewWarps - 1) / kViewWarps : 0, k0), K);
+  for (int k = 0; k < K; ++k) {                                 // canvas rows (none in the reference's configuration)
+    if (k >= k0 && k < k1) { k = k1 - 1; continue; }
+    float4* row4 = reinterpret_cast<float4*>(s_src + (warp + kViewWarps * k) * a.src_w);
+    if (row_a) row4[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (row_b) row4[lane + 32] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   const float* xq[G];
   const float* zq[G];
-  int ly = g.ci + warp - a.y0;                                  // clip row of this warp's first crop row
 #pragma unroll
   for (int q = 0; q < G; ++q) {
-    xq[q] = xp + (static_cast<long long>(ly) * a.pitch + col[q]);
-    zq[q] = zp + (static_cast<long long>(ly) * a.pitch + col[q]);
+    const long long off = static_cast<long long>(kViewWarps * k0 - r0) * a.pitch + col[q];
+    xq[q] = xp + off;
+    zq[q] = zp + off;
   }
   const long long row_step = static_cast<long long>(kViewWarps) * a.pitch;
-  float* srow = s_src + warp * a.src_w;
+  float* srow = s_src + (warp + kViewWarps * k0) * a.src_w;
   const int srow_step = kViewWarps * a.src_w;
   float4 xv[kDepth][G], zv[kDepth][G];
-  bool in_clip[kDepth];
-  auto fetch = [&](int set, int y) {                            // (no-op past the last row)
-    in_clip[set] = ly >= 0 && ly < F && y < g.h;                // warp-uniform
+  auto fetch = [&](int set, int k) {                            // (no-op past the last row)
 #pragma unroll
     for (int q = 0; q < G; ++q) {
       xv[set][q] = zv[set][q] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (in_clip[set]) {
+      if (k < k1) {                                             // warp-uniform
         xv[set][q] = load4(xq[q], col[q]);
         if (mix) zv[set][q] = load4(zq[q], col[q]);             // CTA-uniform (compile-time true for LOGMIX)
       }
       xq[q] += row_step; zq[q] += row_step;
     }
-    ly += kViewWarps;
   };
   auto emit = [&](int set) {
     float4* row4 = reinterpret_cast<float4*>(srow);
-    if (in_clip[set]) {
 #pragma unroll
-      for (int q = 0; q < G; ++q) {
-        const float4 x = xv[set][q], z = zv[set][q];
-        float4 o;
-        o.x = mix1(x.x, z.x);
-        o.y = col[q] + 1 < T ? mix1(x.y, z.y) : 0.f;            // (the last group may reach past the clip's last column:
-        o.z = col[q] + 2 < T ? mix1(x.z, z.z) : 0.f;            //  canvas)
-        o.w = col[q] + 3 < T ? mix1(x.w, z.w) : 0.f;
-        if (on[q]) row4[g.j_in0 + lane + 32 * q] = o;
-      }
-      if (zero_a) row4[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (zero_b) row4[lane + 32] = make_float4(0.f, 0.f, 0.f, 0.f);
-    } else {
-      if (row_a) row4[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (row_b) row4[lane + 32] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int q = 0; q < G; ++q) {
+      const float4 x = xv[set][q], z = zv[set][q];
+      float4 o;
+      o.x = mix1(x.x, z.x);
+      o.y = col[q] + 1 < T ? mix1(x.y, z.y) : 0.f;              // (the last group may reach past the clip's last column:
+      o.z = col[q] + 2 < T ? mix1(x.z, z.z) : 0.f;              //  canvas)
+      o.w = col[q] + 3 < T ? mix1(x.w, z.w) : 0.f;
+      if (on[q]) row4[g.j_in0 + lane + 32 * q] = o;
     }
-    __syncwarp();
-    if (fix_dst >= 0) srow[fix_dst] = (fix_zero || !in_clip[set]) ? 0.f : srow[fix_src];
+    if (zero_a) row4[lane] = make_float4(0.f, 0.f, 0.f, 0.f);   // canvas left and right of the clip's columns
+    if (zero_b) row4[lane + 32] = make_float4(0.f, 0.f, 0.f, 0.f);
     srow += srow_step;
   };
 #pragma unroll
-  for (int d = 0; d < kDepth - 1; ++d) fetch(d, warp + kViewWarps * d);
+  for (int d = 0; d < kDepth - 1; ++d) fetch(d, k0 + d);
   mid();                                                        // (the CTA's tap tables, while the first rows are in flight)
-  for (int y = warp; y < g.h; y += kViewWarps * kDepth) {       // (unrolled by kDepth so that the register sets are static)
+  for (int k = k0; k < k1; k += kDepth) {                       // (unrolled by kDepth so that the register sets are static)
 #pragma unroll
     for (int d = 0; d < kDepth; ++d) {
-      if (y + kViewWarps * d < g.h) {                           // warp-uniform
-        fetch((d + kDepth - 1) % kDepth, y + kViewWarps * (d + kDepth - 1));
+      if (k + d < k1) {                                         // warp-uniform
+        fetch((d + kDepth - 1) % kDepth, k + d + kDepth - 1);
         emit(d);
       }
+    }
+  }
+  __syncwarp();
+  // edge slots: lane <-> row.  A copy of the crop's first / last column; where that column is canvas (or the whole row
+  // is) it already holds the zero that belongs there.
+  for (int r = lane; r < K; r += 32) {
+    float* row = s_src + (warp + kViewWarps * r) * a.src_w;
+    if (g.xs_lo < 0) row[u_first - 1] = row[u_first];
+    if (u_last + 1 < u_end) {                                   // (a tile that ends inside the crop has no such slots)
+      const float e = row[u_last];
+      row[u_last + 1] = e;
+      if (u_last + 2 < u_end) row[u_last + 2] = e;
     }
   }
   __syncwarp();

@@ -346,3 +346,24 @@ def test_two_views_with_128_mel_bands():
     assert np.array_equal(tf.last_params.crop, arrs["crop"])
     _close(v1, w1, what="view1")
     _close(v2, w2, what="view2")
+
+
+@pytest.mark.parametrize("t", [96, 330])
+def test_canvas_taller_than_the_clip(t):
+    """virtual_crop_scale[0] > 1: canvas rows above and below the pasted clip (zero-filled apart from the clip rows in the
+    two-view kernel) and a frequency scale above 1 (tap rows that move by two per output row)."""
+    import audiossl_b200 as A
+    vs = (1.4, 1.5)
+    g = torch.Generator(device="cpu").manual_seed(14 + t)
+    x = torch.randn(24, 1, 64, t, generator=g) * 2.0 - 3.0
+    ch, cw = int(64 * vs[0]), int(t * vs[1])
+    _seed(3)
+    boxes = [ov.draw_crop((ch, cw), (64, t)) for _ in range(24)]
+    boxes[0] = (0, 0, ch, cw)                                   # the whole canvas
+    boxes[1] = (0, 5, 10, 40)                                   # canvas rows only at the top ...
+    boxes[2] = (ch - 12, 0, 12, cw)                             # ... and at the bottom
+    assert max(b[2] for b in boxes) > 64
+    for mode in ("bicubic", "bilinear"):
+        want = torch.stack([ov.resize_crop(c, bx, vs, mode) for c, bx in zip(x, boxes)])
+        got = A.RandomResizeCrop(virtual_crop_scale=vs, interpolation=mode)(x.cuda(), crop=boxes)
+        _close(got, want, what=mode)
