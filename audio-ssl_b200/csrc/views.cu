@@ -69,6 +69,29 @@ __device__ __forceinline__ void store_view(float* p, float v) {
 #endif
 }
 
+// ---- mbarrier + bulk async copy (TMA; SASS: SYNCS / UBLKCP): a warp brings the bank entry's rows into its staged rows
+__device__ __forceinline__ unsigned vsmem(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void vbar_init(void* bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(vsmem(bar)) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void vbar_expect(void* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(vsmem(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void vbar_wait(void* bar, unsigned parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "VWAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra VDONE_%=;\n\t"
+      "bra VWAIT_%=;\n\t"
+      "VDONE_%=:\n\t}" ::"r"(vsmem(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_row(void* dst, const void* src, unsigned bytes, void* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(vsmem(dst)), "l"(src), "r"(bytes), "r"(vsmem(bar)) : "memory");
+}
+
 __device__ __forceinline__ float cubic1(float x) {   // |x| <= 1
   const float A = -0.75f;
   return ((A + 2.f) * x - (A + 3.f)) * x * x + 1.f;
@@ -96,7 +119,7 @@ __device__ __forceinline__ float4 tap_weights(float t, int bilinear) {
 // shared memory: frequency taps [F] (weights, row byte offsets), time taps [TW] (weights, first-tap byte offset), rows
 __host__ __device__ inline size_t views_smem_bytes(int canvas_h, int src_w, int n_freq, int tw) {
   return sizeof(float) * static_cast<size_t>(canvas_h) * src_w + (sizeof(float4) + sizeof(int4)) * static_cast<size_t>(n_freq) +
-         (sizeof(float4) + sizeof(int)) * static_cast<size_t>(tw);
+         (sizeof(float4) + sizeof(int)) * static_cast<size_t>(tw) + sizeof(unsigned long long) * kViewWarps;   // + one mbarrier per warp
 }
 
 // What a CTA knows about its view, tile and staged rows.  A staged row holds the crop columns xs_lo .. xs_hi of one crop
@@ -128,8 +151,13 @@ struct Sel {
 //      LOGMIX (log-mixup-exp against a bank entry, the path's normal case) is a separate instantiation; the other
 //      modes (no bank entry yet, plain mixup) share the generic one.  G = 32-lane groups of float4 the in-clip part of a
 //      row needs (1 for clips up to 125 frames per tile span, else 2).  VEC: ring rows are 16-byte aligned (pitch % 4 == 0).
-template <int G, bool LOGMIX, bool VEC, typename Mid>
-__device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, const Sel& sel, float* s_src, int lane, int warp, Mid mid) {
+//      BULK (aligned rows of this GPU's ring): the bank entry's in-clip row segments are brought into the staged rows -- the
+//      very slots the results go to -- by bulk async copies, one per row, each issued by a different lane, all of a warp's
+//      rows in flight at once on the warp's mbarrier; the clip's own rows come through registers, four rows deep; the mix
+//      happens in place.
+template <int G, bool LOGMIX, bool VEC, bool BULK, typename Mid>
+__device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, const Sel& sel, float* s_src, void* bar, int lane, int warp,
+                                           Mid mid) {
   const int F = a.c.n_freq, T = a.c.n_time;
   const float* xp = sel.xp;
   const float* zp = sel.zp;
@@ -184,7 +212,8 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, cons
   // them when the canvas is as high as the clip -- and the loop over it carries no per-row tests; canvas rows above /
   // below are zero-filled apart.  The loads run kDepth - 1 rows ahead of the arithmetic (kDepth register sets): a warp
   // waits for global memory once, not once per row.
-  constexpr int kDepth = G == 1 ? 3 : 1;                       // (two groups per lane: no room for a second register set)
+  constexpr int kDepth = BULK ? (G == 1 ? 4 : 2) : (G == 1 ? 3 : 1);   // (without BULK two groups per lane leave no room
+                                                                       //  for a second register set)
   const int K = warp < g.h ? (g.h - warp + kViewWarps - 1) / kViewWarps : 0;
   const int r0 = a.y0 - g.ci - warp;
   const int k0 = min(r0 > 0 ? (r0 + kViewWarps - 1) / kViewWarps : 0, K);
@@ -194,6 +223,15 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, cons
     float4* row4 = reinterpret_cast<float4*>(s_src + (warp + kViewWarps * k) * a.src_w);
     if (row_a) row4[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (row_b) row4[lane + 32] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const bool zbulk = BULK && mix && k1 > k0 && g.j_in1 > g.j_in0;
+  if (zbulk) {
+    const unsigned nb = static_cast<unsigned>(g.j_in1 - g.j_in0) * 16u;       // the in-clip groups of a row
+    if (lane == 0) vbar_expect(bar, nb * static_cast<unsigned>(k1 - k0));
+    __syncwarp();
+    for (int r = k0 + lane; r < k1; r += 32)
+      bulk_row(s_src + (warp + kViewWarps * r) * a.src_w + 4 * g.j_in0,
+               zp + (static_cast<long long>(kViewWarps * r - r0) * a.pitch + (g.d4 + 4 * g.j_in0)), nb, bar);
   }
   const float* xq[G];
   const float* zq[G];
@@ -206,14 +244,14 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, cons
   const long long row_step = static_cast<long long>(kViewWarps) * a.pitch;
   float* srow = s_src + (warp + kViewWarps * k0) * a.src_w;
   const int srow_step = kViewWarps * a.src_w;
-  float4 xv[kDepth][G], zv[kDepth][G];
+  float4 xv[kDepth][G], zv[BULK ? 1 : kDepth][G];
   auto fetch = [&](int set, int k) {                            // (no-op past the last row)
 #pragma unroll
     for (int q = 0; q < G; ++q) {
-      xv[set][q] = zv[set][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      xv[set][q] = zv[BULK ? 0 : set][q] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (k < k1) {                                             // warp-uniform
         xv[set][q] = load4(xq[q], col[q]);
-        if (mix) zv[set][q] = load4(zq[q], col[q]);             // CTA-uniform (compile-time true for LOGMIX)
+        if (!BULK && mix) zv[set][q] = load4(zq[q], col[q]);    // CTA-uniform (compile-time true for LOGMIX)
       }
       xq[q] += row_step; zq[q] += row_step;
     }
@@ -222,7 +260,9 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, cons
     float4* row4 = reinterpret_cast<float4*>(srow);
 #pragma unroll
     for (int q = 0; q < G; ++q) {
-      const float4 x = xv[set][q], z = zv[set][q];
+      const float4 x = xv[set][q];
+      float4 z = zv[BULK ? 0 : set][q];
+      if (BULK) { z = make_float4(0.f, 0.f, 0.f, 0.f); if (zbulk && on[q]) z = row4[g.j_in0 + lane + 32 * q]; }
       float4 o;
       o.x = mix1(x.x, z.x);
       o.y = col[q] + 1 < T ? mix1(x.y, z.y) : 0.f;              // (the last group may reach past the clip's last column:
@@ -237,6 +277,7 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, cons
 #pragma unroll
   for (int d = 0; d < kDepth - 1; ++d) fetch(d, k0 + d);
   mid();                                                        // (the CTA's tap tables, while the first rows are in flight)
+  if (zbulk) vbar_wait(bar, 0);                                 // the bank entry's rows have landed in the staged rows
   for (int k = k0; k < k1; k += kDepth) {                       // (unrolled by kDepth so that the register sets are static)
 #pragma unroll
     for (int d = 0; d < kDepth; ++d) {
@@ -261,12 +302,12 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, cons
   __syncwarp();
 }
 
-template <int G, bool VEC, typename Mid>
-__device__ __forceinline__ void stage_rows_any(const ViewArgs& a, const Geo& g, const Sel& sel, float* s_src, int lane, int warp,
-                                               Mid mid) {
+template <int G, bool VEC, bool BULK, typename Mid>
+__device__ __forceinline__ void stage_rows_any(const ViewArgs& a, const Geo& g, const Sel& sel, float* s_src, void* bar, int lane,
+                                               int warp, Mid mid) {
   const bool logmix = sel.mix && a.c.log_mixup;                 // CTA-uniform
-  if (logmix) stage_rows<G, true, VEC>(a, g, sel, s_src, lane, warp, mid);
-  else stage_rows<G, false, VEC>(a, g, sel, s_src, lane, warp, mid);
+  if (logmix) stage_rows<G, true, VEC, BULK>(a, g, sel, s_src, bar, lane, warp, mid);
+  else stage_rows<G, false, VEC, BULK>(a, g, sel, s_src, bar, lane, warp, mid);
 }
 
 // TW = output frames per tile (32 / 64 / 128)
@@ -278,9 +319,14 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
   int4* s_ya = reinterpret_cast<int4*>(s_wy + F);                    // [F]   frequency tap rows, as byte offsets into s_src
   float4* s_wx = reinterpret_cast<float4*>(s_ya + F);                // [TW]  time tap weights of the tile's output columns
   int* s_xu = reinterpret_cast<int*>(s_wx + TW);                     // [TW]  byte offset of a column's first tap in a row
-  float* s_src = reinterpret_cast<float*>(s_xu + TW);                // [h][src_w]  mixed crop span, then (in place,
+  unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_xu + TW);   // [8] one mbarrier per warp (bulk copies)
+  float* s_src = reinterpret_cast<float*>(s_bar + kViewWarps);       // [h][src_w]  mixed crop span, then (in place,
                                                                      //             row by row) the time-resampled rows
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (VEC && !GB) {                                            // this warp's barrier: only this warp ever touches it
+    if (lane == 0) vbar_init(s_bar + warp);
+    __syncwarp();
+  }
   unsigned blk = blockIdx.x;
   int tile = 0;
   if (a.tiles_t > 1) { tile = static_cast<int>(blk % static_cast<unsigned>(a.tiles_t)); blk /= static_cast<unsigned>(a.tiles_t); }
@@ -363,8 +409,9 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
   };
 
   // ---- stage A (this warp's rows), with as many 32-lane groups of float4 as the in-clip part of THIS span needs
-  if (g.j_in1 - g.j_in0 <= 32) stage_rows_any<1, VEC>(a, g, sel, s_src, lane, warp, tap_tables);
-  else stage_rows_any<2, VEC>(a, g, sel, s_src, lane, warp, tap_tables);
+  constexpr bool kBulk = VEC && !GB;                            // (peer rings and dense rows: loads through registers)
+  if (g.j_in1 - g.j_in0 <= 32) stage_rows_any<1, VEC, kBulk>(a, g, sel, s_src, s_bar + warp, lane, warp, tap_tables);
+  else stage_rows_any<2, VEC, kBulk>(a, g, sel, s_src, s_bar + warp, lane, warp, tap_tables);
   __syncthreads();                             // (the tap tables; the rows themselves stay with their warp until stage C)
 
   // ---- stage B, along time: lanes <-> output columns, the four taps of a column are four consecutive floats of the row
