@@ -64,6 +64,7 @@ SIGNATURES = {
     "assl_plan_filterbank": (C.c_int, [_P, _P]),
     "assl_logmel_f32": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _P, _I64, _I64, _P, C.c_int32, _P]),
     "assl_logmel_pitched_f32": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _P, _I64, _I64, _I64, _P, C.c_int32, _P]),
+    "assl_logmel_deferred_f32": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _P, _I64, _I64, _I64, _P, C.c_int32, _P]),
     "assl_clip_moments_f32": (C.c_int, [_P, _I64, _I64, _P, _P]),
     "assl_clip_normalize_f32": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _I64, _P]),
     "assl_wave_l2_gain_f32": (C.c_int, [_P, _I64, _I64, _I64, _P, _P]),

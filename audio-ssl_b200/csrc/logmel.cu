@@ -78,6 +78,7 @@ struct LogmelArgs {
   int q_edge_lo, q_edge_hi;   // pairs q < q_edge_lo / q >= q_edge_hi of a clip touch the reflect padding (or the tail
                               // remainder of an L that is not a multiple of 4): their span is patched by the warp
   int span4;             // (n_fft + hop) & ~3: what one bulk copy covers for every other pair
+  int deferred;          // assl_logmel_deferred_f32: does not wait for the grid before it at its start, but at its end
 };
 
 __host__ __device__ inline size_t logmel_smem_bytes(int warps, int wave_floats) {
@@ -231,10 +232,13 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   for (int i = tid; i < kIvSlots * 32; i += n_threads) s_lane[i] = a.lane_iv[i];
   // (s_ex needs no clearing: every power bin a part reads is either written by this pair or selected away,
   //  never multiplied, and every interval total is started before it is read)
-  pdl_wait();
-  // (after the wait, so that a kernel launched behind this one knows every older grid has completed: that is what lets
-  //  a deferred two-view launch, assl_two_views_deferred_f32, start without waiting for this grid)
-  pdl_launch_dependents();
+  // Deferred (assl_logmel_deferred_f32): the grid launched before this one writes nothing this grid READS (the
+  // caller's promise), so a warp loads and transforms its first pair the moment its CTA has an SM -- under that grid's
+  // tail -- and waits only before its first STORE (below): the slots and sums it overwrites may still be in use there.
+  // (the trigger comes after the wait -- here, or with a warp's first store -- so that a kernel launched behind this one
+  //  knows every older grid has completed: that is what lets a deferred two-view launch, assl_two_views_deferred_f32,
+  //  start without waiting for this grid)
+  if (!a.deferred) { pdl_wait(); pdl_launch_dependents(); }
   int cur = first, nxt = first + stride;             // the pair in work; the pair whose span is being copied
   PairPos pc = pair_pos(a, cur);
   unsigned ticket = 0;                               // lane 0: the claim in flight (becomes the pair after nxt)
@@ -398,6 +402,10 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
       __syncwarp();
     }
 
+    if (a.deferred && it == 0) {                     // (warp-uniform) nothing global is written before the grid before
+      pdl_wait();                                    //  this one has completed
+      pdl_launch_dependents();                       // (the CTA's first call counts)
+    }
     // ---- bands: add the two edges, fold eps and gain, log, store, statistics
     const int ta = 2 * wpair;
     const bool two = ta + 1 < a.T;                   // the last pair of an odd-length clip has one frame
@@ -440,7 +448,9 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
   if (a.ticket && lane == 0) {
     const unsigned total_warps = static_cast<unsigned>(stride);
     if (atomicAdd(a.ticket + 1, 1u) == total_warps - 1) { a.ticket[0] = 0u; a.ticket[1] = 0u; }
-  }
+  }  // deferred launch: whoever waits for THIS grid to complete must also get the completion of the grid before it; every
+  // warp that had a pair has waited for it already, this covers a launch too small to give CTA 0 one
+  if (a.deferred && blockIdx.x == 0 && warp == 0) pdl_wait();
 }
 
 // gain[b] = 1 / max(||wave_b||_2, 1e-12): F.normalize(p=2), upstream_dataset.py:62-63
@@ -482,9 +492,25 @@ extern "C" int assl_logmel_f32(const assl_plan* p, const float* wave, const floa
   return assl_logmel_pitched_f32(p, wave, wave_gain, B, L, ld, lms, slot0, cap, 0, tile_sums, out_kind, stream);
 }
 
+namespace assl {
+static int logmel_launch(const assl_plan* p, const float* wave, const float* wave_gain, int64_t B, int64_t L, int64_t ld,
+                         float* lms, int64_t slot0, int64_t cap, int64_t pitch, double* tile_sums, int32_t out_kind,
+                         int deferred, void* stream);
+}
 extern "C" int assl_logmel_pitched_f32(const assl_plan* p, const float* wave, const float* wave_gain, int64_t B,
                                        int64_t L, int64_t ld, float* lms, int64_t slot0, int64_t cap, int64_t pitch,
                                        double* tile_sums, int32_t out_kind, void* stream) {
+  return assl::logmel_launch(p, wave, wave_gain, B, L, ld, lms, slot0, cap, pitch, tile_sums, out_kind, 0, stream);
+}
+extern "C" int assl_logmel_deferred_f32(const assl_plan* p, const float* wave, const float* wave_gain, int64_t B,
+                                        int64_t L, int64_t ld, float* lms, int64_t slot0, int64_t cap, int64_t pitch,
+                                        double* tile_sums, int32_t out_kind, void* stream) {
+  return assl::logmel_launch(p, wave, wave_gain, B, L, ld, lms, slot0, cap, pitch, tile_sums, out_kind, 1, stream);
+}
+
+static int assl::logmel_launch(const assl_plan* p, const float* wave, const float* wave_gain, int64_t B, int64_t L, int64_t ld,
+                               float* lms, int64_t slot0, int64_t cap, int64_t pitch, double* tile_sums, int32_t out_kind,
+                               int deferred, void* stream) {
   using namespace assl;
   if (out_kind < 0 || out_kind > 3) return ASSL_ERR_INVALID_ARG;
   if (!p || !wave || !lms || B < 0 || ld < L || slot0 < 0 || cap < 0) return ASSL_ERR_INVALID_ARG;
@@ -505,7 +531,7 @@ extern "C" int assl_logmel_pitched_f32(const assl_plan* p, const float* wave, co
   a.T = static_cast<int>(T); a.hop = p->cfg.hop; a.n_mels = p->cfg.n_mels;
   a.total_pairs = static_cast<int>(total_pairs);
   a.wave_floats = (kNfft + a.hop + 3) & ~3;
-  a.n_slots = p->n_slots; a.out_kind = out_kind;
+  a.n_slots = p->n_slots; a.out_kind = out_kind; a.deferred = deferred;
   {   // n / ppc by multiply-high (Granlund-Montgomery, exact for every 32-bit n)
     const unsigned d = static_cast<unsigned>(a.ppc);
     int l = 0;

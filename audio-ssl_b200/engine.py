@@ -15,6 +15,7 @@ every rank runs the identical statistics scan; the bank stays rank-local, as eac
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import numpy as np

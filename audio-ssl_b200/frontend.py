@@ -60,13 +60,17 @@ class Plan:
         _native.check(_native.lib().assl_plan_filterbank(self.handle, out.ctypes.data_as(C.c_void_p)))
         return out
 
-    def logmel_into(self, wave, out, slot0=0, cap=0, tile_sums=None, gain=None, power=False, time_major=False, pitch=0):
+    def logmel_into(self, wave, out, slot0=0, cap=0, tile_sums=None, gain=None, power=False, time_major=False, pitch=0,
+                    deferred=False):
         """wave [B, L] cuda fp32 -> out (ring or [B, n_mels, T]; [B, T, n_mels] with time_major); all on the
-        current stream.  ``pitch``: floats per output row (0 = T; the engines' rings pad their rows to a multiple of 4)."""
+        current stream.  ``pitch``: floats per output row (0 = T; the engines' rings pad their rows to a multiple of 4).
+        ``deferred``: assl_logmel_deferred_f32 -- the kernel reads ``wave`` / ``gain`` without waiting for the kernel
+        launched before it (it waits before its first store): only when that kernel did not write them."""
         b, n = wave.shape
-        _native.check(_native.lib().assl_logmel_pitched_f32(
+        name = "assl_logmel_deferred_f32" if deferred else "assl_logmel_pitched_f32"
+        _native.check(getattr(_native.lib(), name)(
             self.handle, _ptr(wave), _ptr(gain), b, n, wave.stride(0), _ptr(out), int(slot0), int(cap), int(pitch),
-            _ptr(tile_sums), (1 if power else 0) | (2 if time_major else 0), _stream_ptr()), "assl_logmel_pitched_f32")
+            _ptr(tile_sums), (1 if power else 0) | (2 if time_major else 0), _stream_ptr()), name)
 
     def __del__(self):
         try:

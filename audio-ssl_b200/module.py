@@ -142,9 +142,16 @@ class UpstreamInputPipeline:
     of equal-length windows, or with a list of raw 1-D clips of different lengths: those go through
     ``extract_window`` first (``config["pretrain"]["input"]["length_wave"]`` seconds, or ``unit_length``
     samples), their crop offsets drawn by the sampler in the reference's order.
+
+    ``inputs_ready=True`` (with ``lookahead=True``, ``[B, L]`` batches): the caller promises that the waveforms of a call
+    were complete on the device BEFORE the kernel launched last on the stream started (a resident dataset; an upload
+    guarded by an event the stream has waited on).  The log-mel kernel is then launched with assl_logmel_deferred_f32:
+    it reads and transforms its first frame pairs under the tail of the views launched before it and waits for them only
+    before its first store.  Same results.
     """
 
-    def __init__(self, config, len_of_files, *, to_mel_spec=None, unit_length=None, **kw):
+    def __init__(self, config, len_of_files, *, to_mel_spec=None, unit_length=None, inputs_ready=False, **kw):
+        self.inputs_ready = bool(inputs_ready)
         self.tfms = AugmentationModule(config, len_of_files, **kw)
         self.plan = to_mel_spec.plan if to_mel_spec is not None else Plan()
         self.l2 = config["pretrain"].get("normalization") == "l2"
@@ -207,9 +214,11 @@ class UpstreamInputPipeline:
                 gain = torch.empty(b, dtype=torch.float32, device=wave.device)
                 _native.check(_native.lib().assl_wave_l2_gain_f32(_ptr(wave), b, wave.shape[1], wave.stride(0), _ptr(gain),
                                                                   _stream_ptr()))
-            return self._front_then_previous_views(wave, gain, tf._params(params, 0, b, g0=eng.head))
+            # deferred only when no kernel of this call wrote what the log-mel kernel reads (no gain pass, no conversion copy)
+            ready = self.inputs_ready and gain is None and wave.data_ptr() == getattr(waveforms, "data_ptr", lambda: 0)()
+            return self._front_then_previous_views(wave, gain, tf._params(params, 0, b, g0=eng.head), deferred=ready)
 
-    def _front_then_previous_views(self, part, gain, p):
+    def _front_then_previous_views(self, part, gain, p, deferred=False):
         """[b, L] windows of THIS batch -> log-mel into the ring -> statistics; then the views of the oldest pending batch
         (one batch back; two across GPUs, see ViewEngine.split_stats)."""
         eng, tf = self.tfms.engine, self.tfms
@@ -219,7 +228,8 @@ class UpstreamInputPipeline:
         tiles = self.plan.num_tiles(part.shape[1])
         sums = torch.empty((b, tiles, 2), dtype=torch.float64, device=part.device) if tf.pre_norm else None
         split = tf.pre_norm and eng.split_stats
-        self.plan.logmel_into(part, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain, pitch=eng.pitch)
+        self.plan.logmel_into(part, eng.ring, slot0=eng.slot0, cap=eng.cap, tile_sums=sums, gain=gain, pitch=eng.pitch,
+                              deferred=deferred)
         if split:
             # sharded run: the statistics of the batch before are scanned now -- every rank sent its sums a step ago, so
             # nobody waits for the slowest rank -- then this batch's sums go out; both run beside the deferred views below

@@ -105,6 +105,16 @@ int assl_logmel_f32(const assl_plan* plan, const float* wave, const float* wave_
 int assl_logmel_pitched_f32(const assl_plan* plan, const float* wave, const float* wave_gain, int64_t B,
                             int64_t L, int64_t ld, float* lms, int64_t slot0, int64_t cap, int64_t pitch,
                             double* tile_sums, int32_t out_kind, void* stream);
+/* The same, DEFERRED: the launch does not wait for the kernel launched before it on the stream at its start; every warp
+ * loads and transforms its first frame pair the moment its CTA has an SM -- under the tail of that kernel -- and waits
+ * for it only before its first STORE (slots, tile_sums).  The caller guarantees that the kernel launched before it does
+ * not WRITE what this launch reads (wave, wave_gain: do not use it right behind assl_wave_l2_gain_f32 or
+ * assl_extract_window_f32).  Completion stays ordered: a kernel that waits for this launch also gets the completion of
+ * everything launched before it.  (The lookahead order of UpstreamInputPipeline: log-mel(k+1) behind the views of
+ * batch k-1.) */
+int assl_logmel_deferred_f32(const assl_plan* plan, const float* wave, const float* wave_gain, int64_t B,
+                             int64_t L, int64_t ld, float* lms, int64_t slot0, int64_t cap, int64_t pitch,
+                             double* tile_sums, int32_t out_kind, void* stream);
 
 /* Per-clip sum of squares of the waveform -> gain[b] = 1 / max(||wave_b||_2, 1e-12)
  * (F.normalize(p=2), src/dataset/upstream_dataset.py:62-63). */

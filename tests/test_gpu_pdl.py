@@ -113,3 +113,57 @@ def test_lookahead_pipeline_returns_the_same_views_one_call_later():
         assert a1.shape == b1.shape and torch.equal(a1, b1) and torch.equal(a2, b2)
     sd = look.tfms.state_dict()
     assert sd["clips_done"] == sum(sizes)
+
+
+def test_deferred_logmel_gives_the_same_views():
+    """inputs_ready=True: the log-mel kernel is launched with assl_logmel_deferred_f32 (reads and transforms its first
+    frame pairs under the tail of the views launched before it, waits only before its first store).  Resident
+    waveforms, many steps streamed without a synchronisation, batches big enough for every SM to hold a CTA of the
+    views when the next log-mel kernel arrives: bit-identical to the ordinary lookahead order."""
+    import random
+
+    import audiossl_b200 as A
+    g = torch.Generator(device="cpu").manual_seed(23)
+    batches = [(torch.randn(1024, 16000, generator=g) * 0.1).cuda() for _ in range(4)]
+    order = [k % 4 for k in range(14)]
+    torch.cuda.synchronize()
+
+    def run(ready):
+        np.random.seed(31); random.seed(31)
+        pipe = A.UpstreamInputPipeline(CFG, 10 ** 7, max_batch=1024, lookahead=True, inputs_ready=ready)
+        outs = []
+        for k in order:
+            out = pipe(batches[k])
+            if out is not None:
+                outs.append((out[0].clone(), out[1].clone()))
+        outs.append(pipe.flush())
+        torch.cuda.synchronize()
+        return outs
+
+    want, got = run(False), run(True)
+    assert len(got) == len(want) == len(order)
+    for (a1, a2), (b1, b2) in zip(got, want):
+        assert torch.equal(a1, b1) and torch.equal(a2, b2)
+
+
+def test_deferred_logmel_alone_matches_the_ordinary_launch():
+    """assl_logmel_deferred_f32 through the C ABI right behind a long foreign kernel that writes NONE of its inputs."""
+    import audiossl_b200 as A
+    from audiossl_b200 import _native
+    from audiossl_b200.frontend import _ptr, _stream_ptr
+    plan = A.Plan()
+    g = torch.Generator(device="cpu").manual_seed(29)
+    wave = (torch.randn(300, 15200, generator=g) * 0.1).cuda()
+    t = plan.num_frames(15200)
+    want = torch.empty((300, 64, t), device="cuda")
+    plan.logmel_into(wave, want)
+    torch.cuda.synchronize()
+    got = torch.full((300, 64, t), float("nan"), device="cuda")
+    filler = torch.empty(64 << 20, device="cuda")
+    for _ in range(3):
+        filler.normal_()                                # (busy SMs when the deferred launch arrives)
+        plan.logmel_into(wave, got, deferred=True)
+    torch.cuda.synchronize()
+    assert torch.equal(got, want)
+    assert _native.lib().assl_logmel_deferred_f32(None, _ptr(wave), None, 1, 15200, 15200, _ptr(got), 0, 0, 0, None, 0,
+                                                  _stream_ptr()) == 1
