@@ -101,6 +101,9 @@ SIGNATURES = {
     "assl_pipeline_host_sync": (C.c_int, [_P]),
     "assl_pipeline_host_f32": (C.c_int, [_P, C.POINTER(ViewCfg), _P, _I64, _P, _I64, _I64, _I64, _I64, _I64,
                                           _P, _P, _P, _P, _P, C.POINTER(_P), C.POINTER(_P), _P]),
+    "assl_pipeline_host_pcm16": (C.c_int, [_P, C.POINTER(ViewCfg), _P, _I64, _P, _I64, _I64, _I64, _I64, _I64,
+                                          _P, _P, _P, _P, _P, C.POINTER(_P), C.POINTER(_P), _P]),
+    "assl_pcm16_to_f32": (C.c_int, [_P, _I64, _P, _P]),
 }
 
 

@@ -20,7 +20,7 @@ inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 inline int64_t ring_pitch(int64_t T) { return (T + 3) & ~static_cast<int64_t>(3); }   // 16-byte aligned ring rows
 
 struct WsLayout {
-  size_t state, stats_ring, lms_ring, tile_sums, clip_slot, mix_slot, alpha, crop, wave[2], view1[2], view2[2], total;
+  size_t state, stats_ring, lms_ring, tile_sums, clip_slot, mix_slot, alpha, crop, wave[2], pcm[2], view1[2], view2[2], total;
 };
 
 WsLayout layout(const assl_plan* p, int64_t B, int64_t L, int64_t cap) {
@@ -40,11 +40,39 @@ WsLayout layout(const assl_plan* p, int64_t B, int64_t L, int64_t cap) {
   w.crop = o;       o = align_up(o + 2 * static_cast<size_t>(B) * 8 * sizeof(int32_t));
   for (int i = 0; i < 2; ++i) {
     w.wave[i] = o;  o = align_up(o + static_cast<size_t>(B) * L * sizeof(float));
+    w.pcm[i] = o;   o = align_up(o + static_cast<size_t>(B) * L * sizeof(int16_t));     // 16-bit PCM uploads land here
     w.view1[i] = o; o = align_up(o + static_cast<size_t>(B) * plane);
     w.view2[i] = o; o = align_up(o + static_cast<size_t>(B) * plane);
   }
   w.total = o;
   return w;
+}
+
+// 16-bit PCM -> fp32 in [-1, 1): x / 32768 (exact), what soundfile / torchaudio.load hand the reference for a 16-bit
+// file (librosa.core.load, /root/reference/src/dataset/upstream_dataset.py:55).  Eight samples per thread where the
+// pointers allow 16-byte words.
+__global__ void __launch_bounds__(256) pcm16_to_f32_kernel(const int16_t* __restrict__ in, float* __restrict__ out, long long n, int vec) {
+  const long long i = blockIdx.x * 256ll + threadIdx.x;
+  constexpr float k = 1.0f / 32768.0f;
+  if (vec) {
+    if (8 * i + 8 <= n) {
+      const int4 v = __ldg(reinterpret_cast<const int4*>(in) + i);
+      const int w[4] = {v.x, v.y, v.z, v.w};
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        f[2 * j] = static_cast<float>(static_cast<short>(w[j] & 0xffff)) * k;
+        f[2 * j + 1] = static_cast<float>(w[j] >> 16) * k;
+      }
+      float4* o = reinterpret_cast<float4*>(out) + 2 * i;
+      o[0] = make_float4(f[0], f[1], f[2], f[3]);
+      o[1] = make_float4(f[4], f[5], f[6], f[7]);
+    } else {
+      for (long long j = 8 * i; j < n; ++j) out[j] = static_cast<float>(in[j]) * k;
+    }
+  } else if (i < n) {
+    out[i] = static_cast<float>(in[i]) * k;
+  }
 }
 
 __global__ void iota_slots_kernel(int32_t* slot, long long B, long long slot0, long long cap) {
@@ -101,6 +129,16 @@ extern "C" int64_t assl_pipeline_workspace_bytes(const assl_plan* p, int64_t B, 
   return static_cast<int64_t>(layout(p, B, L, cap).total);
 }
 
+extern "C" int assl_pcm16_to_f32(const int16_t* pcm, int64_t n, float* out, void* stream) {
+  if (!pcm || !out || n < 0) return ASSL_ERR_INVALID_ARG;
+  if (n == 0) return ASSL_OK;
+  const int vec = (reinterpret_cast<uintptr_t>(pcm) % 16 == 0) && (reinterpret_cast<uintptr_t>(out) % 16 == 0);
+  const long long threads = vec ? (n + 7) / 8 : n;
+  if ((threads + 255) / 256 > 0x7fffffffll) return ASSL_ERR_UNSUPPORTED;
+  pcm16_to_f32_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, assl::as_stream(stream)>>>(pcm, out, n, vec);
+  return assl::launch_status();
+}
+
 extern "C" int assl_pipeline_host_sync(assl_pipeline* pipe) {
   if (!pipe) return ASSL_ERR_INVALID_ARG;
   bool ok = cudaStreamSynchronize(pipe->s_in) == cudaSuccess;
@@ -108,11 +146,10 @@ extern "C" int assl_pipeline_host_sync(assl_pipeline* pipe) {
   return ok ? ASSL_OK : ASSL_ERR_CUDA;
 }
 
-extern "C" int assl_pipeline_host_f32(assl_pipeline* pipe, const assl_view_cfg* vc, void* ws, int64_t ws_bytes,
-                                      const float* host_wave, int64_t B, int64_t L, int64_t slot0, int64_t cap,
-                                      int64_t max_update, const int32_t* host_mix_slot, const float* host_alpha,
-                                      const int32_t* host_crop, float* host_view1, float* host_view2,
-                                      float** dev_view1, float** dev_view2, void* stream) {
+static int pipeline_host(assl_pipeline* pipe, const assl_view_cfg* vc, void* ws, int64_t ws_bytes, const void* host_wave,
+                         bool pcm16, int64_t B, int64_t L, int64_t slot0, int64_t cap, int64_t max_update,
+                         const int32_t* host_mix_slot, const float* host_alpha, const int32_t* host_crop, float* host_view1,
+                         float* host_view2, float** dev_view1, float** dev_view2, void* stream) {
   using namespace assl;
   if (!pipe || !vc || !ws || !host_wave || !host_mix_slot || !host_alpha || !host_crop) return ASSL_ERR_INVALID_ARG;
   const assl_plan* p = pipe->plan;
@@ -136,6 +173,7 @@ extern "C" int assl_pipeline_host_f32(assl_pipeline* pipe, const assl_view_cfg* 
   float* alpha = reinterpret_cast<float*>(base + w.alpha) + par * B * 2;
   int32_t* crop = reinterpret_cast<int32_t*>(base + w.crop) + par * B * 8;
   float* wave = reinterpret_cast<float*>(base + w.wave[par]);
+  int16_t* pcm = reinterpret_cast<int16_t*>(base + w.pcm[par]);
   float* v1 = reinterpret_cast<float*>(base + w.view1[par]);
   float* v2 = reinterpret_cast<float*>(base + w.view2[par]);
   const int64_t elems = static_cast<int64_t>(p->cfg.n_mels) * T;
@@ -172,7 +210,14 @@ extern "C" int assl_pipeline_host_f32(assl_pipeline* pipe, const assl_view_cfg* 
   for (int c = 0; c < n_chunks && ok && rc == ASSL_OK; ++c) {
     const int64_t b0 = B * c / n_chunks, b1 = B * (c + 1) / n_chunks, nb = b1 - b0;
     if (nb == 0) continue;
-    cp(wave + b0 * L, host_wave + b0 * L, static_cast<size_t>(nb) * L * sizeof(float), cudaMemcpyHostToDevice, pipe->s_in);
+    if (pcm16) {   // half the upload; widened on the device, on the upload stream (behind the link, not before the kernels)
+      cp(pcm + b0 * L, static_cast<const int16_t*>(host_wave) + b0 * L, static_cast<size_t>(nb) * L * sizeof(int16_t),
+         cudaMemcpyHostToDevice, pipe->s_in);
+      if (ok && assl_pcm16_to_f32(pcm + b0 * L, nb * L, wave + b0 * L, pipe->s_in) != ASSL_OK) ok = false;
+    } else {
+      cp(wave + b0 * L, static_cast<const float*>(host_wave) + b0 * L, static_cast<size_t>(nb) * L * sizeof(float),
+         cudaMemcpyHostToDevice, pipe->s_in);
+    }
     ok = ok && cudaEventRecord(pipe->ev_in[c], pipe->s_in) == cudaSuccess;
     ok = ok && cudaStreamWaitEvent(st, pipe->ev_in[c], 0) == cudaSuccess;
     const int64_t s0 = (slot0 + b0) % cap;
@@ -199,4 +244,22 @@ extern "C" int assl_pipeline_host_f32(assl_pipeline* pipe, const assl_view_cfg* 
   if (dev_view1) *dev_view1 = v1;
   if (dev_view2) *dev_view2 = v2;
   return ok ? launch_status() : ASSL_ERR_CUDA;
+}
+
+extern "C" int assl_pipeline_host_f32(assl_pipeline* pipe, const assl_view_cfg* vc, void* ws, int64_t ws_bytes,
+                                      const float* host_wave, int64_t B, int64_t L, int64_t slot0, int64_t cap,
+                                      int64_t max_update, const int32_t* host_mix_slot, const float* host_alpha,
+                                      const int32_t* host_crop, float* host_view1, float* host_view2,
+                                      float** dev_view1, float** dev_view2, void* stream) {
+  return pipeline_host(pipe, vc, ws, ws_bytes, host_wave, false, B, L, slot0, cap, max_update, host_mix_slot, host_alpha,
+                       host_crop, host_view1, host_view2, dev_view1, dev_view2, stream);
+}
+
+extern "C" int assl_pipeline_host_pcm16(assl_pipeline* pipe, const assl_view_cfg* vc, void* ws, int64_t ws_bytes,
+                                        const int16_t* host_wave, int64_t B, int64_t L, int64_t slot0, int64_t cap,
+                                        int64_t max_update, const int32_t* host_mix_slot, const float* host_alpha,
+                                        const int32_t* host_crop, float* host_view1, float* host_view2,
+                                        float** dev_view1, float** dev_view2, void* stream) {
+  return pipeline_host(pipe, vc, ws, ws_bytes, host_wave, true, B, L, slot0, cap, max_update, host_mix_slot, host_alpha,
+                       host_crop, host_view1, host_view2, dev_view1, dev_view2, stream);
 }

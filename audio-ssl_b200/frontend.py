@@ -105,11 +105,15 @@ class HostPipeline:
         """One call.  ``ws`` device uint8 workspace; ``host_wave`` / ``host_view*`` pinned CPU tensors; ``mix_slot`` /
         ``alpha`` / ``crop`` contiguous numpy arrays that stay alive until ``sync()``."""
         hp = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)   # noqa: E731
-        _native.check(_native.lib().assl_pipeline_host_f32(
+        # int16 waveforms: 16-bit PCM as the audio file holds it (x / 32768 on the device, half the upload)
+        name = "assl_pipeline_host_pcm16" if host_wave.dtype == torch.int16 else "assl_pipeline_host_f32"
+        if name.endswith("f32") and host_wave.dtype != torch.float32:
+            raise TypeError("host_wave must be float32 or int16 (PCM)")
+        _native.check(getattr(_native.lib(), name)(
             self.handle, C.byref(vcfg), _ptr(ws), ws.numel(), hp(host_wave), int(batch), int(n_samples), int(slot0), int(cap),
             int(max_update), mix_slot.ctypes.data_as(C.c_void_p), alpha.ctypes.data_as(C.c_void_p),
             crop.ctypes.data_as(C.c_void_p), hp(host_view1), hp(host_view2), None, None,
-            stream if stream is not None else _stream_ptr()), "assl_pipeline_host_f32")
+            stream if stream is not None else _stream_ptr()), name)
 
     def sync(self):
         _native.check(_native.lib().assl_pipeline_host_sync(self.handle), "assl_pipeline_host_sync")

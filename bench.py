@@ -553,12 +553,13 @@ def run_ours(args):
     vcfg = _native.ViewCfg(N_MELS, T, int(N_MELS * 1.0), int(T * 1.5), 0, 1)
     keep = []
 
-    def host_step(s):
+    def host_step(s, waves=None):
         p = fast.draw(s * B, B, N_MELS, T)
         mix = np.where(p.src_clip >= 0, p.src_clip % cap, -1).astype(np.int32)
         alpha, crop = np.ascontiguousarray(p.alpha), np.ascontiguousarray(p.crop)
         keep.append((mix, alpha, crop))                       # the async copies read these until the sync
-        pipe.run(vcfg, ws, host_waves[s % args.rotate], B, L, (s * B) % cap, cap, max_update, mix, alpha, crop, hv1, hv2)
+        pipe.run(vcfg, ws, (waves or host_waves)[s % args.rotate], B, L, (s * B) % cap, cap, max_update, mix, alpha, crop,
+                 hv1, hv2)
 
     for s in range(W):
         host_step(s)
@@ -571,8 +572,21 @@ def run_ours(args):
     pipe.sync()                                                # every download has landed in host memory
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
-    clocks = sampler.stop() if sampler else None
     checksum = float(hv1[0, 0, :4].sum())
+    # the same with the waveforms as 16-bit PCM in host memory (what a 16-bit audio file holds; assl_pipeline_host_pcm16
+    # widens x / 32768 on the device): half the upload.  Reported beside ``e2e``, which stays the fp32-buffer number.
+    host_pcm = [(w * 32768.0).round().clamp_(-32768, 32767).to(torch.int16).pin_memory() for w in host_waves]
+    for s in range(W + n_e2e, 2 * W + n_e2e):
+        host_step(s, host_pcm)
+    pipe.sync()
+    fence()
+    t0 = time.perf_counter()
+    for s in range(2 * W + n_e2e, 2 * W + 2 * n_e2e):
+        host_step(s, host_pcm)
+    pipe.sync()
+    torch.cuda.synchronize()
+    pcm_s = max_over_ranks(time.perf_counter() - t0)
+    clocks = sampler.stop() if sampler else None
     if ex is not None:
         ex.check()
     pipe.close()
@@ -614,6 +628,10 @@ def run_ours(args):
                 "api": "assl_pipeline_host_f32 + assl_pipeline_host_sync (pinned host waveforms in, both views back to pinned "
                        "host memory; uploads/kernels/downloads of consecutive calls overlap"
                        + ("; statistics exchanged between the ranks inside every call)" if ex is not None else ")")},
+        "e2e_pcm16": {"value": world * B * n_e2e / pcm_s, "unit": UNIT, "h2d_bytes_per_step": B * L * 2 + B * 40,
+                      "d2h_bytes_per_step": 2 * B * N_MELS * T * 4, "ms_per_step": 1e3 * pcm_s / n_e2e,
+                      "api": "assl_pipeline_host_pcm16: the same call with the waveforms as 16-bit PCM in pinned host memory "
+                             "(widened to x / 32768 on the device, the values librosa.core.load gives the reference)"},
         "gpu_launches": K * launches_per_step, "clocks": clocks,
     }
     if configs:

@@ -358,7 +358,18 @@ int assl_pipeline_host_f32(assl_pipeline* pipe, const assl_view_cfg* vcfg, void*
                            const int32_t* host_mix_slot, const float* host_alpha,
                            const int32_t* host_crop, float* host_view1, float* host_view2,
                            float** dev_view1, float** dev_view2, void* stream);
+/* The same with 16-bit PCM waveforms in host memory -- the samples a 16-bit audio file holds; the reference gets them
+ * as x / 32768 in fp32 from librosa.core.load (src/dataset/upstream_dataset.py:55) and so does the kernel chain here:
+ * half the upload, widened on the device (exact), same views bit for bit as assl_pipeline_host_f32 on x / 32768. */
+int assl_pipeline_host_pcm16(assl_pipeline* pipe, const assl_view_cfg* vcfg, void* ws,
+                             int64_t ws_bytes, const int16_t* host_wave, int64_t B, int64_t L,
+                             int64_t slot0, int64_t cap, int64_t max_update,
+                             const int32_t* host_mix_slot, const float* host_alpha,
+                             const int32_t* host_crop, float* host_view1, float* host_view2,
+                             float** dev_view1, float** dev_view2, void* stream);
 int assl_pipeline_host_sync(assl_pipeline* pipe);
+/* Device buffers: out[i] = pcm[i] / 32768 (the widening step on its own). */
+int assl_pcm16_to_f32(const int16_t* pcm, int64_t n, float* out, void* stream);
 
 #ifdef __cplusplus
 }

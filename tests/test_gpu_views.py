@@ -210,6 +210,61 @@ def test_c_abi_host_pipeline_matches_device_pipeline():
         _close(hv[k][1], want[k][1], rtol=1e-6, atol=2e-6, what=f"call {k} view2")
 
 
+def test_pcm16_host_pipeline_is_the_f32_pipeline_on_x_over_32768():
+    """assl_pipeline_host_pcm16 (16-bit PCM in host memory, widened on the device) == assl_pipeline_host_f32 fed
+    x / 32768 -- what librosa.core.load hands the reference for a 16-bit file (upstream_dataset.py:55) -- bit for bit
+    over several overlapped calls; and the widening kernel on its own, aligned and unaligned."""
+    import ctypes as C
+    import audiossl_b200 as A
+    from audiossl_b200 import _native
+    lib = _native.lib()
+    B, L, calls = 48, 15200, 4
+    g = torch.Generator(device="cpu").manual_seed(77)
+    pcm = [torch.randint(-32768, 32768, (B, L), generator=g, dtype=torch.int32).to(torch.int16).pin_memory() for _ in range(calls)]
+    pcm[0][0, :4] = torch.tensor([-32768, 32767, 0, -1], dtype=torch.int16)
+    f32 = [(p.to(torch.float32) / 32768.0).pin_memory() for p in pcm]
+    plan = A.Plan()
+    T = plan.num_frames(L)
+    cap = 1024 + B
+    vcfg = _native.ViewCfg(64, T, 64, int(T * 1.5), 0, 1)
+    fast = A.FastSampler(seed=5)
+    params = []
+    for k in range(calls):
+        p = fast.draw(k * B, B, 64, T)
+        params.append((np.where(p.src_clip >= 0, p.src_clip % cap, -1).astype(np.int32), np.ascontiguousarray(p.alpha),
+                       np.ascontiguousarray(p.crop)))
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def run(waves):
+        host = A.HostPipeline(plan)
+        ws = torch.zeros(host.workspace_bytes(B, L, cap), dtype=torch.uint8, device="cuda")
+        hv = [(torch.empty(B, 64, T).pin_memory(), torch.empty(B, 64, T).pin_memory()) for _ in range(calls)]
+        for k in range(calls):
+            mix, alpha, crop = params[k]
+            host.run(vcfg, ws, waves[k], B, L, (k * B) % cap, cap, 10 ** 6, mix, alpha, crop, hv[k][0], hv[k][1], stream=st)
+        host.sync()
+        torch.cuda.synchronize()
+        host.close()
+        return hv
+
+    want, got = run(f32), run(pcm)
+    for k in range(calls):
+        assert torch.equal(got[k][0], want[k][0]) and torch.equal(got[k][1], want[k][1]), f"call {k}"
+    with pytest.raises(TypeError):
+        A.HostPipeline(plan).run(vcfg, torch.zeros(8, dtype=torch.uint8, device="cuda"), f32[0].double(), B, L, 0, cap, 10,
+                                 *params[0])
+    # the widening step alone: 16-byte aligned (eight samples per thread, ragged tail) and unaligned (one per thread)
+    P = lambda t: C.c_void_p(t.data_ptr())                            # noqa: E731
+    src = pcm[0].reshape(-1).cuda()
+    for off, n in ((0, 100003), (1, 4099), (0, 7), (8, 64)):
+        out = torch.full((n + 1,), float("nan"), device="cuda")
+        dst = out[1:] if off == 1 else out[:n]
+        _native.check(lib.assl_pcm16_to_f32(P(src[off:]), n, P(dst), None), "assl_pcm16_to_f32")
+        torch.cuda.synchronize()
+        assert torch.equal(dst[:n], src[off:off + n].to(torch.float32) / 32768.0)
+    assert lib.assl_pcm16_to_f32(None, 4, P(out), None) == 1
+
+
 @pytest.mark.parametrize("n_parts", [1, 5, 51])
 def test_running_stats_many_chunks_and_freeze(n_parts):
     """20000 clips in one call (three passes of the 8-CTA cluster, a partial last chunk), statistics freezing in the
