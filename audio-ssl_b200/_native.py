@@ -81,6 +81,7 @@ SIGNATURES = {
     "assl_exchange_error": (C.c_int, [_P]),
     "assl_exchange_send": (C.c_int, [_P, _P, _I64, _I64, _P]),
     "assl_running_stats_exchange_scan": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _I64, C.c_int32, C.c_int32, _P]),
+    "assl_exchange_scan_send": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _I64, C.c_int32, _P, _I64, _I64, _P]),
     "assl_running_stats_exchange": (C.c_int, [_P, _P, _P, _I64, _I64, _I64, _I64, _P, _I64, _I64, C.c_int32, _P]),
     "assl_peer_alloc": (C.c_int, [C.POINTER(_P), _I64, _P]),
     "assl_peer_free": (C.c_int, [_P]),

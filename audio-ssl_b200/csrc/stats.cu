@@ -81,7 +81,10 @@ struct ExArgs {
   int world = 0;                 // 0 = single process, no exchange
   int rank = 0;
   long long seg = 0;             // records per segment (max_clips + 1)
-  unsigned seq = 0;              // this call's number (never 0)
+  unsigned seq = 0;              // this call's number (never 0); SCAN side when send_after is set
+  unsigned send_seq = 0;         // SEND side: the number of the call whose records go out (= seq unless send_after)
+  int send_after = 0;            // scan call ``seq`` (sent a step ago) FIRST, then wait for the grid before this one
+                                 // and send call ``send_seq``: assl_exchange_scan_send
   int n_dst = 0;                 // SEND: the buffers this rank's segment is stored into -- every rank's (peer transport:
   uint4* dst[ASSL_EXCHANGE_MAX_WORLD] = {};   //  stores over NVLink) or only its own (staged: the caller all-gathers)
   const uint4* src = nullptr;    // SCAN: this rank's buffer of the call's parity
@@ -107,8 +110,8 @@ __device__ __forceinline__ unsigned long long global_ns() {
 }
 // one record = (a, b) as two flagged 16-byte words
 __device__ __forceinline__ void put_record(const ExArgs& x, long long index, double a, double b) {
-  const uint4 ra = make_uint4(__double2loint(a), x.seq, __double2hiint(a), x.seq);
-  const uint4 rb = make_uint4(__double2loint(b), x.seq, __double2hiint(b), x.seq);
+  const uint4 ra = make_uint4(__double2loint(a), x.send_seq, __double2hiint(a), x.send_seq);
+  const uint4 rb = make_uint4(__double2loint(b), x.send_seq, __double2hiint(b), x.send_seq);
   for (int j = 0; j < x.n_dst; ++j) {
     uint4* rec = x.dst[j] + 2 * (x.rank * x.seg + index);
     st_volatile_v4(rec, ra);
@@ -143,6 +146,19 @@ __global__ void __launch_bounds__(256) stats_send_kernel(const ExArgs x, const d
   clip_total8(pair_sums, idx, b, n_parts, threadIdx.x & 7, &sx, &sxx);
   if ((threadIdx.x & 7) == 0 && idx < b) put_record(x, 1 + idx, sx, sxx);
   if (blockIdx.x == 0 && threadIdx.x == 0) put_record(x, 0, static_cast<double>(b), 0.0);
+}
+
+// Sending side inside the scan cluster: totals of this rank's clips -> its segment in EVERY destination buffer (stores over
+// NVLink for the peers; the local copy goes the same way).  All kStatCtas CTAs take part, 128 clips each per pass.
+__device__ __forceinline__ void send_own(const ExArgs& x, const double* send_sums, long long send_b, long long send_parts,
+                                         unsigned rank, int tid) {
+  for (long long base = 0; base < send_b; base += kScanThreads) {
+    const long long idx = base + rank * (kScanThreads / 8) + (tid >> 3);
+    double sx, sxx;
+    clip_total8(send_sums, idx, send_b, send_parts, tid & 7, &sx, &sxx);
+    if ((tid & 7) == 0 && idx < send_b) put_record(x, 1 + idx, sx, sxx);
+  }
+  if (rank == 0 && tid == 0) put_record(x, 0, static_cast<double>(send_b), 0.0);
 }
 
 // state: [0] n_put  [1] sum of m_j (j>=1)  [2] sum of v_j (j>=1)  [3] mean  [4] std  [5..6] reserved  [7] exchange error
@@ -180,17 +196,7 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
   if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); s_late = 0; }
 
   if (x.world > 0) {
-    if (send_sums) {
-      // ---- fused form, sending side: totals of this rank's clips -> its segment in EVERY rank's buffer
-      //      (stores over NVLink for the peers; the local copy goes the same way)
-      for (long long base = 0; base < send_b; base += kScanThreads) {
-        const long long idx = base + rank * (kScanThreads / 8) + (tid >> 3);
-        double sx, sxx;
-        clip_total8(send_sums, idx, send_b, send_parts, tid & 7, &sx, &sxx);
-        if ((tid & 7) == 0 && idx < send_b) put_record(x, 1 + idx, sx, sxx);
-      }
-      if (rank == 0 && tid == 0) put_record(x, 0, static_cast<double>(send_b), 0.0);
-    }
+    if (send_sums && !x.send_after) send_own(x, send_sums, send_b, send_parts, rank, tid);   // fused form: send, then scan
     // ---- receiving side.  Headers first: how many clips every sender brought
     __syncthreads();
     if (tid < x.world) {
@@ -237,7 +243,10 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
         state[7] = 1.0;
         if (x.host_err) { *reinterpret_cast<volatile int*>(x.host_err) = 1; __threadfence_system(); }
       }
-      if (x.deferred && rank == 0) pdl_wait();
+      if (x.send_after) {                             // the peers still get this rank's records of the next call
+        pdl_wait();
+        send_own(x, send_sums, send_b, send_parts, rank, tid);
+      } else if (x.deferred && rank == 0) pdl_wait();
       return;
     }
     n_parts = 1;
@@ -335,7 +344,15 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
   }
   // deferred launch: this grid ran beside the one launched before it; whoever waits for THIS grid to complete (the
   // next kernel's pdl_wait) must also get that one's completion (one CTA holds the grid open, the others free their SMs)
-  if (x.deferred && rank == 0) pdl_wait();
+  if (x.send_after) {
+    // scan-then-send (assl_exchange_scan_send): the records of the NEXT call go out from here, once the grid before this
+    // one (the log-mel kernel whose per-pair sums they add up) has completed.  The cluster barrier first: a peer that
+    // has all of this rank's new records (header included) may overwrite the parity this call's records sat in, so
+    // every CTA must be done reading them before the first new record leaves.
+    cluster.sync();
+    pdl_wait();
+    send_own(x, send_sums, send_b, send_parts, rank, tid);
+  } else if (x.deferred && rank == 0) pdl_wait();
 }
 
 __global__ void __launch_bounds__(256) clip_sums_kernel(const double* tile_sums, long long B, long long n_parts, double* clip_sums) {
@@ -505,7 +522,7 @@ unsigned seq_word(unsigned long long call) { return static_cast<unsigned>(call &
 
 assl::ExArgs send_args(const assl_exchange* x, unsigned long long call) {
   assl::ExArgs a;
-  a.world = x->world; a.rank = x->rank; a.seg = x->seg; a.seq = seq_word(call);
+  a.world = x->world; a.rank = x->rank; a.seg = x->seg; a.seq = a.send_seq = seq_word(call);
   const size_t off = static_cast<size_t>(call & 1) * x->rec_bytes;
   if (x->staged) { a.n_dst = 1; a.dst[0] = reinterpret_cast<uint4*>(x->local + off); }
   else { a.n_dst = x->world; for (int r = 0; r < x->world; ++r) a.dst[r] = reinterpret_cast<uint4*>(x->peer[r] + off); }
@@ -617,12 +634,13 @@ extern "C" int assl_exchange_send(assl_exchange* x, const double* pair_sums, int
 
 static int exchange_scan(assl_exchange* x, double* state, int64_t elems, int64_t max_update, float* mean_std, int64_t slot0,
                          int64_t cap, int32_t write_all, int32_t deferred, const double* send_sums, int64_t send_b,
-                         int64_t send_parts, void* stream) {
+                         int64_t send_parts, void* stream, bool send_after = false) {
   using namespace assl;
   const unsigned long long call = x->scanned + 1;
-  ExArgs a = send_sums ? send_args(x, call) : ExArgs();
+  // (scan_args overwrites seq with the scanned call's number; send_seq keeps the number of the call that goes out)
+  ExArgs a = (send_sums || send_after) ? send_args(x, send_after ? x->sent + 1 : call) : ExArgs();
   scan_args(x, call, &a);
-  a.write_all = write_all ? 1 : 0; a.deferred = deferred ? 1 : 0;
+  a.write_all = write_all ? 1 : 0; a.deferred = deferred ? 1 : 0; a.send_after = send_after ? 1 : 0;
   if (launch_pdl(running_stats_kernel, dim3(kStatCtas), dim3(kScanThreads), 0, as_stream(stream), state,
                  static_cast<const double*>(nullptr), 0ll, 1ll, 1.0 / static_cast<double>(elems), static_cast<long long>(max_update),
                  0ll, 0ll, mean_std, static_cast<long long>(slot0), static_cast<long long>(cap), a, send_sums,
@@ -654,6 +672,22 @@ extern "C" int assl_running_stats_exchange(assl_exchange* x, double* state, cons
   x->sent_b[(x->sent + 1) & 1] = B;
   const int rc = exchange_scan(x, state, elems, max_update, mean_std, slot0, cap, write_all, 0, pair_sums, B, n_parts, stream);
   if (rc == ASSL_OK) x->sent += 1;
+  return rc;
+}
+
+extern "C" int assl_exchange_scan_send(assl_exchange* x, double* state, int64_t elems, int64_t max_update, float* mean_std,
+                                       int64_t slot0, int64_t cap, int32_t write_all, const double* pair_sums, int64_t B,
+                                       int64_t n_parts, void* stream) {
+  if (!x || !x->connected || !state || !mean_std || elems < 1 || max_update < 1 || slot0 < 0 || cap < 0 ||
+      (!pair_sums && B > 0) || B < 0 || B > x->max_clips || n_parts < 1)
+    return ASSL_ERR_INVALID_ARG;
+  if (reinterpret_cast<uintptr_t>(pair_sums) % 16 != 0) return ASSL_ERR_INVALID_ARG;
+  if (x->scanned + 1 != x->sent) return ASSL_ERR_INVALID_ARG;          // exactly one call sent and not yet scanned
+  const long long b = x->sent_b[x->sent & 1];
+  if (cap > 0 && ((write_all ? static_cast<long long>(x->world) * b : b) > cap || slot0 >= cap)) return ASSL_ERR_INVALID_ARG;
+  const int rc = exchange_scan(x, state, elems, max_update, mean_std, slot0, cap, write_all, 1, pair_sums, B, n_parts, stream,
+                               true);
+  if (rc == ASSL_OK) { x->sent += 1; x->sent_b[x->sent & 1] = B; }
   return rc;
 }
 

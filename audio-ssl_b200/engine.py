@@ -150,6 +150,18 @@ class StatsExchange:
             self.handle, _ptr(state), elems, int(max_update), _ptr(stats), slot0, cap, 1 if write_all else 0,
             1 if deferred else 0, _stream_ptr()), "assl_running_stats_exchange_scan")
 
+    def scan_send(self, state, elems, max_update, stats, slot0, cap, sums, b, n_parts):
+        """The deferred scan of the call sent a step ago and the send of this step's sums in ONE launch
+        (assl_exchange_scan_send); two launches with the staged transport (the segments have to be gathered in between)."""
+        self.check()
+        if self.staged:
+            self.scan(state, elems, max_update, stats, slot0, cap, deferred=True)
+            self.send(sums, b, n_parts)
+            return
+        _native.check(_native.lib().assl_exchange_scan_send(
+            self.handle, _ptr(state), elems, int(max_update), _ptr(stats), slot0, cap, 0, _ptr(sums), b, n_parts,
+            _stream_ptr()), "assl_exchange_scan_send")
+
     def run(self, state, sums, b, n_parts, elems, max_update, stats, slot0, cap, write_all=False):
         """Send + scan of one call: ONE kernel over peer memory; send, all-gather, scan with the staged transport."""
         self.check()
@@ -324,6 +336,19 @@ class ViewEngine:
         if b > ex.max_clips:
             raise ValueError(f"{b} clips in one call, the statistics exchange was opened for max_batch = {ex.max_clips}")
         ex.send(sums, b, n_parts)
+        self._sent = (self.slot0, b)
+        self._keep2, self._keep = getattr(self, "_keep", None), sums
+
+    def scan_then_send_stats(self, sums, n_parts):
+        """split_stats, one step: the statistics of the batch sent a step ago are scanned (deferred: nobody waits for the
+        slowest rank, its records have long landed) and this batch's sums go out -- one launch when a batch is pending."""
+        if getattr(self, "_sent", None) is None:
+            return self.send_stats(sums, n_parts)
+        ex = self.exchange(sums.device)
+        b = sums.shape[0]
+        if b > ex.max_clips:
+            raise ValueError(f"{b} clips in one call, the statistics exchange was opened for max_batch = {ex.max_clips}")
+        ex.scan_send(self.state, self.f * self.t, self.max_update, self.stats, self._sent[0], self.cap, sums, b, n_parts)
         self._sent = (self.slot0, b)
         self._keep2, self._keep = getattr(self, "_keep", None), sums
 

@@ -233,8 +233,9 @@ class UpstreamInputPipeline:
         if split:
             # sharded run: the statistics of the batch before are scanned now -- every rank sent its sums a step ago, so
             # nobody waits for the slowest rank -- then this batch's sums go out; both run beside the deferred views below
-            eng.scan_pending_stats(deferred=True)   # (may start under the log-mel kernel's tail: it reads records and state only)
-            eng.send_stats(sums, tiles)
+            # (one launch: the scan may start under the log-mel kernel's tail -- it reads records and state only -- and the
+            #  same cluster sends once that kernel has completed)
+            eng.scan_then_send_stats(sums, tiles)
         elif tf.pre_norm:
             eng.update_stats(sums, tiles)
         eng.ahead += b

@@ -241,6 +241,7 @@ class Workload:
         self.exchange = exchange_factory(B) if world > 1 else None
         self.split = self.look and self.exchange is not None
         self.scan_deferred = int(os.environ.get("ASSL_BENCH_SCAN_DEFERRED", "1"))
+        self.merged = self.split and not self.exchange.staged and os.environ.get("ASSL_BENCH_SCAN_SEND", "1") != "0"
         # the log-mel kernel of the next batch reads and transforms its first frame pairs under the tail of the views launched
         # before it and waits for them only before its first store (assl_logmel_deferred_f32, inputs_ready=True in the module
         #  -- the waveforms are resident and complete long before any step)
@@ -283,7 +284,7 @@ class Workload:
 
     @property
     def launches_per_step(self):
-        return 4 if self.split else 3
+        return 4 if (self.split and not self.merged) else 3
 
     def step(self, events=None):
         """One step; ``events`` = 4 CUDA events recorded around the three stages (serialises the dependent launches)."""
@@ -298,12 +299,16 @@ class Workload:
                         self.pitch, sums, 0, st))
         rec(1)
         if self.split:
-            if s > 0:                  # statistics of the PREVIOUS batch: every rank sent its sums a step ago
-                chk(lib.assl_running_stats_exchange_scan(self.exchange.handle, self.p_state, self.elems, self.max_update,
-                                                         self.p_stats, ((s - 1) * B) % cap, cap, 0, self.scan_deferred, st))
-            chk(lib.assl_exchange_send(self.exchange.handle, sums, B, self.tiles, st))
-            if self.exchange.staged:
-                self.exchange._gather()
+            if s > 0 and self.merged:  # statistics of the PREVIOUS batch (every rank sent its sums a step ago) + this batch's send
+                chk(lib.assl_exchange_scan_send(self.exchange.handle, self.p_state, self.elems, self.max_update, self.p_stats,
+                                                ((s - 1) * B) % cap, cap, 0, sums, B, self.tiles, st))
+            else:
+                if s > 0:
+                    chk(lib.assl_running_stats_exchange_scan(self.exchange.handle, self.p_state, self.elems, self.max_update,
+                                                             self.p_stats, ((s - 1) * B) % cap, cap, 0, self.scan_deferred, st))
+                chk(lib.assl_exchange_send(self.exchange.handle, sums, B, self.tiles, st))
+                if self.exchange.staged:
+                    self.exchange._gather()
         elif self.gbank:
             self.exchange.run(self.eng.state, self.sums[s & 1], B, self.tiles, self.elems, self.max_update, self.eng.stats,
                               (s * B * self.world) % self.eng.gcap, self.eng.gcap, write_all=True)

@@ -240,6 +240,11 @@ int assl_two_views_global_f32(const assl_view_cfg* cfg, const float* lms, const 
  *                        AFTER the send -- scan(k-1) . log-mel(k) . send(k) . views(k-1) -- the records have long
  *                        landed and no rank waits for the slowest one inside a step.  A call has to be scanned before
  *                        the next one is sent (two parities)
+ * assl_exchange_scan_send  the two above in ONE launch for the lookahead order: the deferred scan of the call sent a step
+ *                        ago (exactly one call must be pending), then -- in the same cluster, after the kernel launched
+ *                        before it on the stream (the log-mel kernel of THIS step) has completed -- the send of this
+ *                        step's pair_sums [B, n_parts, 2].  Step order log-mel(k) . scan(k-1)+send(k) . views(k-2): one
+ *                        small kernel between the log-mel kernel and the views instead of two
  * assl_running_stats_exchange  send + scan of one call in ONE kernel (peer transport), for the ordinary step order:
  *                        arguments as assl_running_stats, except pair_sums [B, n_parts, 2] are THIS rank's clips
  * assl_exchange_error    ASSL_ERR_PEER_TIMEOUT once a scan gave up waiting for a peer (assl_exchange_set_timeout,
@@ -261,6 +266,9 @@ int assl_exchange_send(assl_exchange* x, const double* pair_sums, int64_t B, int
 int assl_running_stats_exchange_scan(assl_exchange* x, double* state, int64_t elems, int64_t max_update,
                                      float* mean_std, int64_t slot0, int64_t cap, int32_t write_all,
                                      int32_t deferred, void* stream);
+int assl_exchange_scan_send(assl_exchange* x, double* state, int64_t elems, int64_t max_update, float* mean_std,
+                            int64_t slot0, int64_t cap, int32_t write_all, const double* pair_sums, int64_t B,
+                            int64_t n_parts, void* stream);
 int assl_running_stats_exchange(assl_exchange* x, double* state, const double* pair_sums, int64_t B,
                                 int64_t n_parts, int64_t elems, int64_t max_update, float* mean_std,
                                 int64_t slot0, int64_t cap, int32_t write_all, void* stream);

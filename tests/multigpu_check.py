@@ -96,6 +96,32 @@ def main():
         assert torch.equal(sa, sb) and torch.equal(ta, tb), ("uneven", step)
     ex_split.check()
 
+    # ---- 1c. scan of the call sent a step ago + send of this step's sums in ONE launch (assl_exchange_scan_send), uneven
+    #      and empty batches included: after every step the statistics are those of one process one step earlier
+    sa, sb = (torch.zeros(8, dtype=torch.float64, device=dev) for _ in range(2))
+    ta, tb = (torch.zeros((cap, 2), dtype=torch.float32, device=dev) for _ in range(2))
+    snaps, pending = [], None
+    for step in range(7):
+        counts = [(300 if step % 3 == 0 else 25 + 11 * r) if (step != 4 or r != 0) else 0 for r in range(world)]
+        every = [torch.rand((c, parts, 2), generator=g, dtype=torch.float64) * 50 + 1 for c in counts]
+        mine = every[rank].to(dev) if counts[rank] else torch.zeros((1, parts, 2), dtype=torch.float64, device=dev)
+        slot0 = (300 * step) % cap
+        if pending is None:
+            ex_split.send(mine, counts[rank], parts)
+        else:
+            ex_split.scan_send(sa, elems, max_update, ta, pending, cap, mine, counts[rank], parts)
+            torch.cuda.synchronize()
+            assert torch.equal(sa, snaps[-1][0]) and torch.equal(ta, snaps[-1][1]), ("scan_send", step)
+        pending = slot0
+        _native.check(lib.assl_running_stats(P(sb), P(torch.cat(every).to(dev)), sum(counts), parts, elems, max_update,
+                                             sum(counts[:rank]), counts[rank], P(tb), slot0, cap, st()))
+        torch.cuda.synchronize()
+        snaps.append((sb.clone(), tb.clone()))
+    ex_split.scan(sa, elems, max_update, ta, pending, cap)
+    torch.cuda.synchronize()
+    assert torch.equal(sa, sb) and torch.equal(ta, tb), "scan_send: last scan"
+    ex_split.check()
+
     # ---- 2. sharded pipeline vs one process
     cfg = {"pretrain": {"normalization": "mean_var", "input": {"length_wave": 0.5},
                         "augmentations": {"RandomResizeCrop": {"virtual_crop_scale": [1.0, 1.5], "freq_crop_scale": [0.6, 1.5],
