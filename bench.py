@@ -611,7 +611,7 @@ def run_ours(args):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, B),
         "path": {"stats_exchange": exchange_kind,
-                 "step_order": ("log-mel(k), scan(k-1), send(k), views(k-2) (deferred launch)" if (lookahead_on and world > 1) else
+                 "step_order": ("log-mel(k), scan(k-1)+send(k) in one launch (assl_exchange_scan_send), views(k-2) (deferred launch)" if (lookahead_on and world > 1) else
                                 "log-mel(k), statistics(k), views(k-1): the views of the previous batch are launched deferred "
                                 "(assl_two_views_deferred_f32, UpstreamInputPipeline(lookahead=True)); every step runs all the "
                                 "kernels" if lookahead_on else "log-mel(k), statistics(k), views(k)"),
