@@ -118,8 +118,8 @@ __device__ __forceinline__ float4 tap_weights(float t, int bilinear) {
 
 // shared memory: frequency taps [F] (weights, row byte offsets), time taps [TW] (weights, first-tap byte offset), rows
 __host__ __device__ inline size_t views_smem_bytes(int canvas_h, int src_w, int n_freq, int tw) {
-  return sizeof(float) * static_cast<size_t>(canvas_h) * src_w + (sizeof(float4) + sizeof(int4)) * static_cast<size_t>(n_freq) +
-         (sizeof(float4) + sizeof(int)) * static_cast<size_t>(tw) + sizeof(unsigned long long) * kViewWarps;   // + one mbarrier per warp
+  return sizeof(float) * static_cast<size_t>(canvas_h) * src_w + sizeof(float4) * static_cast<size_t>(n_freq) +
+         sizeof(int) * static_cast<size_t>((n_freq + 3) & ~3) + (sizeof(float4) + sizeof(int)) * static_cast<size_t>(tw) + sizeof(unsigned long long) * kViewWarps;   // + one mbarrier per warp
 }
 
 // What a CTA knows about its view, tile and staged rows.  A staged row holds the crop columns xs_lo .. xs_hi of one crop
@@ -316,8 +316,8 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int F = a.c.n_freq, T = a.c.n_time;
   float4* s_wy = reinterpret_cast<float4*>(smem_raw);                // [F]   frequency tap weights
-  int4* s_ya = reinterpret_cast<int4*>(s_wy + F);                    // [F]   frequency tap rows, as byte offsets into s_src
-  float4* s_wx = reinterpret_cast<float4*>(s_ya + F);                // [TW]  time tap weights of the tile's output columns
+  int* s_top = reinterpret_cast<int*>(s_wy + F);                     // [F]   row of an output row's fourth frequency tap (padded to 4)
+  float4* s_wx = reinterpret_cast<float4*>(s_top + ((F + 3) & ~3));  // [TW]  time tap weights of the tile's output columns
   int* s_xu = reinterpret_cast<int*>(s_wx + TW);                     // [TW]  byte offset of a column's first tap in a row
   unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_xu + TW);   // [8] one mbarrier per warp (bulk copies)
   float* s_src = reinterpret_cast<float*>(s_bar + kViewWarps);       // [h][src_w]  mixed crop span, then (in place,
@@ -396,9 +396,7 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
       int iy; float ty;
       source_index(oy, g.h, F, &iy, &ty);
       s_wy[oy] = tap_weights(ty, bil);
-      const int rb = a.src_w * 4;
-      s_ya[oy] = make_int4(min(max(iy - 1, 0), g.h - 1) * rb, min(max(iy, 0), g.h - 1) * rb,
-                           min(max(iy + 1, 0), g.h - 1) * rb, min(max(iy + 2, 0), g.h - 1) * rb);
+      s_top[oy] = iy + 2;                                  // the fourth tap's row, UNCLAMPED: stage C's position in the crop
     }
     for (int c = tid; c < TW; c += kViewThreads) {
       int ix; float tx;
@@ -461,33 +459,40 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
     const int oy0 = warp * rows_per_warp, oy1 = min(F, oy0 + rows_per_warp);
     const int rb = a.src_w * 4;
     float* orow = outp + oy0 * T;
-    float t0[NC], t1[NC], t2[NC], t3[NC];
-    int prev = -1 - rb;                                         // second tap row of the previous output row (byte offset)
-    for (int oy = oy0; oy < oy1; ++oy, orow += T) {
-      const float4 wy = s_wy[oy];
-      const int4 ya = s_ya[oy];
-      const int moved = ya.y - prev;                            // the same for every lane
-      prev = ya.y;
-      if (moved == rb) {                                        // one row down: (t0, t1, t2, t3) <- (t1, t2, t3, new)
-        const float* r3 = reinterpret_cast<const float*>(col0 + ya.w);
+    // The walk is over the crop's rows: position r = row of the fourth tap (unclamped; taps = rows r-3 .. r clamped to the
+    // crop, which is exactly ATen's clamping of iy-1 .. iy+2).  Every output row whose position is r is written from the
+    // four rows in registers, then the oldest register takes row r+1.  Unrolled by four so that the registers keep
+    // their names while their roles rotate: nothing is moved.
+    float ra[NC], rb4[NC], rc[NC], rd[NC];
+    const int hm1 = g.h - 1;
+    auto load_row = [&](float (&dst)[NC], int row) {
+      const float* src = reinterpret_cast<const float*>(col0 + min(max(row, 0), hm1) * rb);
 #pragma unroll
-        for (int c = 0; c < NC; ++c) { t0[c] = t1[c]; t1[c] = t2[c]; t2[c] = t3[c]; t3[c] = r3[32 * c]; }
-      } else if (moved != 0) {                                  // the block's first row (or a scale above 1): all four
-        const float* r0 = reinterpret_cast<const float*>(col0 + ya.x);
-        const float* r1 = reinterpret_cast<const float*>(col0 + ya.y);
-        const float* r2 = reinterpret_cast<const float*>(col0 + ya.z);
-        const float* r3 = reinterpret_cast<const float*>(col0 + ya.w);
+      for (int c = 0; c < NC; ++c) dst[c] = src[32 * c];
+    };
+    int oy = oy0;
+    int r = oy0 < oy1 ? s_top[oy0] : 0, pos = r;
+    load_row(ra, r - 3); load_row(rb4, r - 2); load_row(rc, r - 1); load_row(rd, r);
+    auto emit = [&](const float (&t0)[NC], const float (&t1)[NC], const float (&t2)[NC], const float (&t3)[NC]) {
+      while (oy < oy1 && pos == r) {                            // (warp-uniform)
+        const float4 wy = s_wy[oy];
 #pragma unroll
-        for (int c = 0; c < NC; ++c) { t0[c] = r0[32 * c]; t1[c] = r1[32 * c]; t2[c] = r2[32 * c]; t3[c] = r3[32 * c]; }
+        for (int c = 0; c < NC; ++c) {                          // (every load stayed inside the staged rows: no guard)
+          float acc = t0[c] * wy.x;
+          acc = fmaf(t1[c], wy.y, acc);
+          acc = fmaf(t2[c], wy.z, acc);
+          acc = fmaf(t3[c], wy.w, acc);
+          if (live[c]) store_view(orow + 32 * c, acc);
+        }
+        ++oy; orow += T;
+        pos = s_top[min(oy, F - 1)];
       }
-#pragma unroll
-      for (int c = 0; c < NC; ++c) {                            // (every load stays inside the staged rows: no guard)
-        float acc = t0[c] * wy.x;
-        acc = fmaf(t1[c], wy.y, acc);
-        acc = fmaf(t2[c], wy.z, acc);
-        acc = fmaf(t3[c], wy.w, acc);
-        if (live[c]) store_view(orow + 32 * c, acc);
-      }
+    };
+    while (oy < oy1) {
+      emit(ra, rb4, rc, rd); if (oy >= oy1) break; load_row(ra, ++r);
+      emit(rb4, rc, rd, ra); if (oy >= oy1) break; load_row(rb4, ++r);
+      emit(rc, rd, ra, rb4); if (oy >= oy1) break; load_row(rc, ++r);
+      emit(rd, ra, rb4, rc); if (oy >= oy1) break; load_row(rd, ++r);
     }
   }
   // deferred launch: this grid ran beside the one launched before it; whoever waits for THIS grid to complete
