@@ -219,12 +219,36 @@ def main():
         assert raised and float(sl[7]) == 1.0
         assert torch.equal(sl[:5], before[:5])               # n_put, carries, mean, std: untouched
     dist.barrier()
+    #      (c) the same lateness inside scan + send in one launch: the last rank sends call 1 two seconds late, the others'
+    #      scan of call 1 gives up (statistics untouched) -- and STILL sends call 2 from the same kernel, or the late rank,
+    #      whose own scan of call 1 finds every record, would wait for call 2 in vain.
+    ex_split.set_timeout(0.5)
+    sc, tc = torch.zeros(8, dtype=torch.float64, device=dev), torch.zeros((cap, 2), dtype=torch.float32, device=dev)
+    mine = allsums[rank].to(dev)
+    if rank == world - 1:
+        time.sleep(2.0)
+    ex_split.send(mine, 50, parts)                                            # call 1
+    _native.check(lib.assl_exchange_scan_send(ex_split.handle, P(sc), elems, max_update, P(tc), 0, cap, 0, P(mine), 50, parts,
+                                              st()), "assl_exchange_scan_send")                 # scan of call 1 + call 2 out
+    torch.cuda.synchronize()
+    late = lib.assl_exchange_error(ex_split.handle) != 0
+    if rank == world - 1:
+        assert not late and float(sc[7]) == 0.0 and float(sc[0]) == min(50 * world, max_update)
+    else:
+        assert late and float(sc[7]) == 1.0 and float(sc[:5].abs().sum()) == 0.0
+    dist.barrier()                                                            # everyone has sent call 2 by now
+    ex_split.set_timeout(30.0)
+    n_before = float(sc[0])
+    ex_split.scan(sc, elems, max_update, tc, 50, cap)                        # call 2: every record is there, on every rank
+    torch.cuda.synchronize()
+    assert float(sc[0]) == min(n_before + 50 * world, max_update)
+    dist.barrier()
     for e in (ex, ex_split, ex_staged):
         e.close()
     if rank == 0:
         print(f"multigpu_check: OK on {world} GPUs (fused == split == staged == NCCL path == single stream, bit for bit; "
               f"uneven shards; global bank == unsharded run, {remote} remote bank entries on rank 0; lookahead order == "
-              f"ordinary order; NormalizeBatch(sync); late rank waited for / timeout raised)")
+              f"ordinary order; NormalizeBatch(sync); late rank waited for / timeout raised / scan+send still sends)")
     dist.destroy_process_group()
 
 
