@@ -133,6 +133,81 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
     k0[j] = first;
     cnt[j] = n;
   }
+  // Where a run starts is free within its padding: any even first bin that still covers the interval's bins with the
+  // same number of parts will do (the mask says which bins count).  The choice decides the 16-byte bank group
+  // (first bin / 2) mod 8 of the part's 128-bit loads, and a quarter-warp's eight loads are conflict-free when its
+  // eight parts sit in eight different groups -- so the starts are chosen to spread the parts evenly over the groups
+  // (at most one part per group and quarter-warp): first the single moves that help most, then augmenting paths of
+  // single-part intervals from an over-full group to one with room.
+  {
+    int total = 0;
+    for (int j = 0; j < n_iv; ++j) total += cnt[j] > 0 ? cnt[j] / assl::kPartBins : 1;
+    const int room = 4 * ((total + 31) / 32);                    // quarter-warps over all slots = most parts per group
+    std::vector<int> lo_of(n_iv, 0), hi_of(n_iv, -1);
+    for (int j = 0; j < n_iv; ++j)
+      if (cnt[j] > 0) {
+        lo_of[j] = n_bins; 
+        for (int k = 0; k < n_bins; ++k)
+          if (bin_in(j, k)) { lo_of[j] = lo_of[j] < k ? lo_of[j] : k; hi_of[j] = k; }
+      }
+    auto n_parts_of = [&](int j) { return cnt[j] > 0 ? cnt[j] / assl::kPartBins : 1; };
+    auto group_of = [&](int start, int c) { return (start / 2 + 4 * c) & 7; };      // part c of a run: 8 bins = 4 groups on
+    auto smallest_start = [&](int j) {                          // even, >= 0, the run still reaches the interval's last bin
+      int s = hi_of[j] - cnt[j] + 1;
+      s = s < 0 ? 0 : s;
+      return (s + 1) & ~1;
+    };
+    int load[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int j = 0; j < n_iv; ++j)
+      for (int c = 0; c < n_parts_of(j); ++c) ++load[group_of(k0[j], c)];
+    auto excess = [&](const int* l) { int e = 0; for (int g = 0; g < 8; ++g) e += l[g] > room ? l[g] - room : 0; return e; };
+    auto spread = [&](const int* l) { int e = 0; for (int g = 0; g < 8; ++g) e += l[g] * l[g]; return e; };
+    auto moved = [&](int j, int s, int* l) {                    // loads with interval j's run started at s instead
+      for (int c = 0; c < n_parts_of(j); ++c) { --l[group_of(k0[j], c)]; ++l[group_of(s, c)]; }
+    };
+    for (int pass = 0; pass < 256 && excess(load) > 0; ++pass) {              // best single move, while one helps
+      int best_j = -1, best_s = 0, best_e = excess(load), best_q = spread(load);
+      for (int j = 0; j < n_iv; ++j) {
+        if (cnt[j] == 0) continue;
+        for (int st = smallest_start(j); st <= (lo_of[j] & ~1); st += 2) {
+          if (st == k0[j]) continue;
+          int l[8];
+          for (int g = 0; g < 8; ++g) l[g] = load[g];
+          moved(j, st, l);
+          const int e = excess(l), q = spread(l);
+          if (e < best_e || (e == best_e && q < best_q)) { best_j = j; best_s = st; best_e = e; best_q = q; }
+        }
+      }
+      if (best_j < 0) break;
+      moved(best_j, best_s, load);
+      k0[best_j] = best_s;
+    }
+    for (int pass = 0; pass < 256 && excess(load) > 0; ++pass) {              // augmenting paths, one part at a time
+      int src = 0;
+      while (load[src] <= room) ++src;
+      int from[8], via_j[8], via_s[8], queue[8], qh = 0, qt = 0;
+      for (int g = 0; g < 8; ++g) from[g] = -2;
+      from[src] = -1; queue[qt++] = src;
+      int dst = -1;
+      while (qh < qt && dst < 0) {
+        const int a = queue[qh++];
+        for (int j = 0; j < n_iv && dst < 0; ++j) {
+          if (cnt[j] != assl::kPartBins || group_of(k0[j], 0) != a) continue;  // single-part intervals sitting in group a
+          bool used = false;
+          for (int g = 0; g < 8; ++g) used = used || (from[g] >= 0 && via_j[g] == j);
+          if (used) continue;
+          for (int st = smallest_start(j); st <= (lo_of[j] & ~1); st += 2) {
+            const int b = group_of(st, 0);
+            if (from[b] != -2) continue;
+            from[b] = a; via_j[b] = j; via_s[b] = st; queue[qt++] = b;
+            if (load[b] < room) { dst = b; break; }
+          }
+        }
+      }
+      if (dst < 0) break;                                       // (stays correct, a quarter-warp then pays a second wavefront)
+      for (int g = dst; from[g] >= 0; g = from[g]) { k0[via_j[g]] = via_s[g]; --load[from[g]]; ++load[g]; }
+    }
+  }
   // Lanes of the log-mel kernel own pieces of intervals for the whole launch.  Every interval is cut into
   // parts of exactly kPartBins bins (its weight run is zero-padded to whole parts), so all lanes run the
   // same straight-line code; a lane owns one part per slot.  Two parts of one interval never share a slot:
@@ -148,8 +223,17 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
         parts.push_back({cnt[j] > 0 ? k0[j] + c : 0, j});
     const int n_slots = (static_cast<int>(parts.size()) + 31) / 32;
     if (n_slots > assl::kIvSlots) { delete p; return ASSL_ERR_UNSUPPORTED; }
-    while (static_cast<int>(parts.size()) < 32 * n_slots) parts.push_back({0, -1});
     auto group = [](const Part& x) { return (x.k0 / 2) & 7; };
+    {   // padding parts own nothing (every bin masked): they read wherever the emptiest bank group is
+      int load[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      for (const Part& x : parts) ++load[group(x)];
+      while (static_cast<int>(parts.size()) < 32 * n_slots) {
+        int g = 0;
+        for (int c = 1; c < 8; ++c) if (load[c] < load[g]) g = c;
+        parts.push_back({2 * g, -1});
+        ++load[g];
+      }
+    }
     std::stable_sort(parts.begin(), parts.end(), [&](const Part& x, const Part& y) { return group(x) < group(y); });
     const int n_q = 4 * n_slots;                                 // quarter-warps over all slots
     std::vector<std::vector<Part>> quarter(n_q);
@@ -211,8 +295,28 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
         for (int c = 1; c < 8; ++c)
           if (clash[c] < clash[best] || (clash[c] == clash[best] && used_per_colour[c] < used_per_colour[best])) best = c;
         colour[j] = best;
-        pos[j] = best + 8 * used_per_colour[best]++;
+        ++used_per_colour[best];
       }
+      // repair: while some interval shares its colour with a quarter-mate, give it the colour that clashes least
+      // (sideways moves allowed a bounded number of times; 8 colours for quarters of 8 usually end at no clash at all)
+      for (int pass = 0; pass < 64; ++pass) {
+        bool any = false;
+        for (int j : by_deg) {
+          int clash[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+          for (int m : mates[j]) ++clash[colour[m]];
+          if (clash[colour[j]] == 0) continue;
+          any = true;
+          int best = colour[j];
+          for (int k = 1; k <= 8; ++k) {                         // (starting behind the current colour: ties rotate)
+            const int c = (colour[j] + k + pass) & 7;
+            if (clash[c] < clash[best] || (c != colour[j] && clash[c] == clash[best] && pass % 3 == 2)) best = c;
+          }
+          colour[j] = best;
+        }
+        if (!any) break;
+      }
+      int next_of[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      for (int j = 0; j < n_iv; ++j) pos[j] = colour[j] + 8 * next_of[colour[j]]++;
     }
     int n_pos = 0;
     for (int j = 0; j < n_iv; ++j) n_pos = n_pos > pos[j] + 1 ? n_pos : pos[j] + 1;
@@ -225,7 +329,7 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
       for (size_t i = 0; i < quarter[q].size(); ++i) {
         const Part& x = quarter[q][i];
         const int sl = slot_of(q), lane = (q / n_slots) * 8 + static_cast<int>(i);
-        if (x.iv < 0) continue;
+        if (x.iv < 0) { lane_iv[static_cast<size_t>(sl) * 32 + lane] = make_int4(x.k0, 0, 0, 0); continue; }   // (mask 0, owns nothing)
         int vm = 0;
         for (int r = 0; r < assl::kPartBins; ++r) vm |= (bin_in(x.iv, x.k0 + r) ? 1 : 0) << r;
         const double width = mel_f[x.iv + 1] - mel_f[x.iv];
