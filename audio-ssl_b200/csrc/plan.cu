@@ -2,6 +2,8 @@
 // (/root/reference/src/utils/utils.py:24) plus the window / twiddle tables of the FFT kernel.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -317,6 +319,16 @@ extern "C" int assl_plan_create(assl_plan** out, const assl_cfg* cfg) {
       }
       int next_of[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       for (int j = 0; j < n_iv; ++j) pos[j] = colour[j] + 8 * next_of[colour[j]]++;
+    }
+    if (getenv("ASSL_PLAN_DEBUG")) {                             // how conflict-free the dealing came out
+      int group_clash = 0, colour_clash = 0;
+      for (int q = 0; q < n_q; ++q) {
+        int gs[8] = {0, 0, 0, 0, 0, 0, 0, 0}, cs[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (const Part& x : quarter[q]) { ++gs[group(x)]; if (x.iv >= 0) ++cs[colour[x.iv]]; }
+        for (int c = 0; c < 8; ++c) { group_clash += gs[c] > 1 ? gs[c] - 1 : 0; colour_clash += cs[c] > 1 ? cs[c] - 1 : 0; }
+      }
+      fprintf(stderr, "assl plan: %d parts in %d slots; quarter-warps with a bank group twice: %d, with a total's colour twice: %d\n",
+              static_cast<int>(parts.size()), n_slots, group_clash, colour_clash);
     }
     int n_pos = 0;
     for (int j = 0; j < n_iv; ++j) n_pos = n_pos > pos[j] + 1 ? n_pos : pos[j] + 1;
