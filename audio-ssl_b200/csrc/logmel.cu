@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
         if (p < 0) p = -p;
         if (p > last) p = 2ll * last - p;
         p = p < 0 ? 0 : (p > last ? last : p);       // only frames >= T can land here; never read back
-        buf[i] = __ldg(src + p);
+        buf[i] = __ldcg(src + p);                    // (L2, like the bulk copies: a deferred launch has made no acquire yet)
       }
       __syncwarp();
     }

@@ -189,12 +189,12 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, cons
   const int u_end = g.xo + g.nslots;                           // one past the last slot in use
 
   auto load4 = [&](const float* p, int c) -> float4 {          // (dense rows: c = the group's first column)
-    if (VEC) return __ldg(reinterpret_cast<const float4*>(p));
+    if (VEC) return __ldcg(reinterpret_cast<const float4*>(p));
     float4 r;
-    r.x = __ldg(p);
-    r.y = c + 1 < T ? __ldg(p + 1) : 0.f;
-    r.z = c + 2 < T ? __ldg(p + 2) : 0.f;
-    r.w = c + 3 < T ? __ldg(p + 3) : 0.f;
+    r.x = __ldcg(p);
+    r.y = c + 1 < T ? __ldcg(p + 1) : 0.f;
+    r.z = c + 2 < T ? __ldcg(p + 2) : 0.f;
+    r.w = c + 3 < T ? __ldcg(p + 3) : 0.f;
     return r;
   };
   auto mix1 = [&](float x, float z) -> float {
@@ -332,16 +332,18 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
   if (a.tiles_t > 1) { tile = static_cast<int>(blk % static_cast<unsigned>(a.tiles_t)); blk /= static_cast<unsigned>(a.tiles_t); }
   pdl_launch_dependents();                     // the next kernel may take SMs as this grid's last wave drains
   if (!a.deferred) pdl_wait();                 // nothing global is read before the previous grid has completed
-  if (a.order) blk = static_cast<unsigned>(a.order[blk]);   // CTAs start in launch order: the host puts the big crops first
+  if (a.order) blk = static_cast<unsigned>(__ldcg(a.order + blk));   // CTAs start in launch order: the host puts the big crops first
   const int v = static_cast<int>(blk & 1u);
   const long long b = blk >> 1;
 
   // ---- every per-view parameter in one hop ...
-  const int4 cr = __ldg(reinterpret_cast<const int4*>(a.crop) + (b * 2 + v));
-  const int xslot = __ldg(a.clip_slot + b);
-  const int zslot = __ldg(a.mix_slot + (b * 2 + v));
+  // (every global read of this kernel goes to L2 -- ld.global.cg and bulk copies, never the SM's L1: a deferred launch
+  //  starts without griddepcontrol.wait, i.e. without the acquire that would drop lines an earlier kernel left there)
+  const int4 cr = __ldcg(reinterpret_cast<const int4*>(a.crop) + (b * 2 + v));
+  const int xslot = __ldcg(a.clip_slot + b);
+  const int zslot = __ldcg(a.mix_slot + (b * 2 + v));
   Sel sel;
-  sel.al = __ldg(a.alpha + (b * 2 + v));
+  sel.al = __ldcg(a.alpha + (b * 2 + v));
   sel.mix = zslot >= 0;
   // GB (global bank, a separate instantiation so the default kernel keeps its register budget): the bank entry may
   // sit in a peer's ring (loads over NVLink) and the (mean, std) pairs live in a ring over global clips
@@ -359,9 +361,9 @@ __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewAr
   // ... then the two (mean, std) pairs, in flight while the geometry and the first row addresses are worked out
   sel.mu = 0.f; sel.sd = 1.f; sel.zmu = 0.f; sel.zsd = 1.f;
   if (a.mean_std) {
-    const float2 xs = __ldg(reinterpret_cast<const float2*>(a.mean_std) + xstat);
+    const float2 xs = __ldcg(reinterpret_cast<const float2*>(a.mean_std) + xstat);
     sel.mu = xs.x; sel.sd = xs.y;
-    if (sel.mix) { const float2 zs = __ldg(reinterpret_cast<const float2*>(a.mean_std) + zstat); sel.zmu = zs.x; sel.zsd = zs.y; }
+    if (sel.mix) { const float2 zs = __ldcg(reinterpret_cast<const float2*>(a.mean_std) + zstat); sel.zmu = zs.x; sel.zsd = zs.y; }
   }
 
   Geo g;
