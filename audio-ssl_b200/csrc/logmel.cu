@@ -434,12 +434,15 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) logmel_kernel(const LogmelA
       if (two) { dst[frame_stride] = l1; s1 += l1; s2 = fmaf(l1, l1, s2); }
     }
     if (a.pair_sums) {                               // per frame pair (sum, sum^2), fixed butterfly order
+      // The first step splits the work: the lower half-warp goes on with the sums, the upper one with the sums of
+      // squares (each lane hands over the value it does not keep), so the remaining four steps move ONE value per lane --
+      // five shuffles instead of ten, and the same additions in the same order as a butterfly over both values.
+      const bool upper = lane >= 16;
+      float keep = upper ? s2 : s1;
+      keep += __shfl_xor_sync(0xffffffffu, upper ? s1 : s2, 16);
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-      }
-      if (lane == 0) reinterpret_cast<double2*>(a.pair_sums)[cur] = make_double2(s1, s2);
+      for (int o = 8; o > 0; o >>= 1) keep += __shfl_xor_sync(0xffffffffu, keep, o);
+      if ((lane & 15) == 0) a.pair_sums[2 * cur + (lane >> 4)] = static_cast<double>(keep);   // lane 0: sum, lane 16: sum^2
     }
     cur = nxt; nxt = nn; pc = pn; ++it;
   }
