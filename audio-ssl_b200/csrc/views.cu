@@ -310,7 +310,7 @@ __device__ __forceinline__ void stage_rows_any(const ViewArgs& a, const Geo& g, 
   else stage_rows<G, false, VEC, BULK>(a, g, sel, s_src, bar, lane, warp, mid);
 }
 
-// TW = output frames per tile (32 / 64 / 128)
+// TW = output frames per tile (32 / 64 / 96 / 128)
 template <int TW, bool GB, bool VEC>
 __global__ void __launch_bounds__(kViewThreads, 4) two_views_kernel(const ViewArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -581,7 +581,10 @@ static int two_views_impl(const assl_view_cfg* vc, const float* lms, const float
     return static_cast<int>((s + 3 + 3) / 4 * 4);
   };
   int rc = ASSL_ERR_UNSUPPORTED;
-  if (T > 64) { a.src_w = span(128); rc = launch_views<128>(a, vec, as_stream(stream)); }
+  // tile width = lanes x column groups of stages B and C: the narrowest that holds the clip (T = 96, DeLoRes-S' 0.95 s,
+  // takes three groups, not four with one idle), 128 for anything wider (tiled over time)
+  if (T > 96) { a.src_w = span(128); rc = launch_views<128>(a, vec, as_stream(stream)); }
+  if (rc == ASSL_ERR_UNSUPPORTED && T > 64) { a.src_w = span(96); rc = launch_views<96>(a, vec, as_stream(stream)); }
   if (rc == ASSL_ERR_UNSUPPORTED && T > 32) { a.src_w = span(64); rc = launch_views<64>(a, vec, as_stream(stream)); }
   if (rc == ASSL_ERR_UNSUPPORTED) { a.src_w = span(32); rc = launch_views<32>(a, vec, as_stream(stream)); }
   return rc;
