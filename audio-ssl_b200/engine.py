@@ -303,7 +303,7 @@ class ViewEngine:
 
     @property
     def split_stats(self):
-        """Lookahead order across GPUs -- log-mel(k) . scan(k-1) . send(k) . views(k-2): the sums of batch k are SENT right
+        """Lookahead order across GPUs -- log-mel(k) . scan(k-1)+send(k) . views(k-2): the sums of batch k are SENT right
         behind its log-mel kernel and SCANNED one step later, beside the views of the batch before (launched deferred),
         so neither the wait for the slowest rank nor the scan itself sits between two log-mel kernels."""
         return self.depth == 2

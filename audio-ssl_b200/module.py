@@ -191,7 +191,7 @@ class UpstreamInputPipeline:
         return self.tfms._post(v1, v2)
 
     # -- lookahead=True: software-pipelined step order  log-mel(k) . statistics(k) . views(k-1)
-    #    (across GPUs: log-mel(k) . scan(k-1) . send(k) . views(k-2), see ViewEngine.split_stats)
+    #    (across GPUs: log-mel(k) . scan(k-1)+send(k) in one launch . views(k-2), see ViewEngine.split_stats)
     def _call_lookahead(self, waveforms, params):
         """Run the front end and the statistics of THIS batch and return the two views of the PREVIOUS one (``None`` on
         the first call; ``flush()`` returns the last batch's).  The views of batch k-1 are launched right behind the

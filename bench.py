@@ -209,7 +209,7 @@ class ClockSampler(threading.Thread):
 class Workload:
     """Device-resident step loop for one (per-GPU batch, clip length): the C ABI driven through ctypes with raw pointers
     taken once (~5 us per call, so the host stays ahead of the GPU).  Step order with lookahead, one GPU:
-    log-mel(k) . statistics(k) . views(k-1); across GPUs: log-mel(k) . scan(k-1) . send(k) . views(k-2)."""
+    log-mel(k) . statistics(k) . views(k-1); across GPUs: log-mel(k) . scan(k-1)+send(k) (one launch) . views(k-2)."""
 
     def __init__(self, A, lib, dev, rank, world, batch, n_samples, exchange_factory, lookahead=True, gbank=False,
                  rotate_bytes=256 << 20, rotate_min=2, seed=1234):

@@ -237,7 +237,7 @@ int assl_two_views_global_f32(const assl_view_cfg* cfg, const float* lms, const 
  *                        launched before it on the stream at its start but at its end, like assl_two_views_deferred_f32
  *                        -- everything it depends on travels in the flagged records and in ``state`` (written by the
  *                        previous scan, which a log-mel launch in between has already waited for).  Issued one step
- *                        AFTER the send -- scan(k-1) . log-mel(k) . send(k) . views(k-1) -- the records have long
+ *                        AFTER the send -- log-mel(k) . scan(k-1) . send(k) . views(k-2) -- the records have long
  *                        landed and no rank waits for the slowest one inside a step.  A call has to be scanned before
  *                        the next one is sent (two parities)
  * assl_exchange_scan_send  the two above in ONE launch for the lookahead order: the deferred scan of the call sent a step
