@@ -191,9 +191,11 @@ __global__ void __cluster_dims__(kStatCtas, 1, 1) __launch_bounds__(kScanThreads
   const int tid = threadIdx.x;
   pdl_launch_dependents();                           // (the two-view kernel's CTAs wait for this grid to complete)
   if (!x.deferred) pdl_wait();                       // the log-mel kernel's per-pair sums are complete and visible
-  const long long n0 = static_cast<long long>(state[0]);
-  double carry_m = state[1], carry_v = state[2];
-  if (tid == 0) { s_frozen[0] = static_cast<float>(state[3]); s_frozen[1] = static_cast<float>(state[4]); s_late = 0; }
+  // (read from L2, never the SM's L1: a deferred launch starts without griddepcontrol.wait, i.e. without the acquire that
+  //  would drop a line of ``state`` an earlier scan on this SM left there)
+  const long long n0 = static_cast<long long>(__ldcg(state));
+  double carry_m = __ldcg(state + 1), carry_v = __ldcg(state + 2);
+  if (tid == 0) { s_frozen[0] = static_cast<float>(__ldcg(state + 3)); s_frozen[1] = static_cast<float>(__ldcg(state + 4)); s_late = 0; }
 
   if (x.world > 0) {
     if (send_sums && !x.send_after) send_own(x, send_sums, send_b, send_parts, rank, tid);   // fused form: send, then scan
