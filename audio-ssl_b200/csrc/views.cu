@@ -245,15 +245,15 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, cons
   float* srow = s_src + (warp + kViewWarps * k0) * a.src_w;
   const int srow_step = kViewWarps * a.src_w;
   float4 xv[kDepth][G], zv[BULK ? 1 : kDepth][G];
-  auto fetch = [&](int set, int k) {                            // (no-op past the last row)
+  auto fetch = [&](int set, int k) {                            // (no-op past the last row: that set is never emitted)
 #pragma unroll
     for (int q = 0; q < G; ++q) {
-      xv[set][q] = zv[BULK ? 0 : set][q] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (k < k1) {                                             // warp-uniform
         xv[set][q] = load4(xq[q], col[q]);
         if (!BULK && mix) zv[set][q] = load4(zq[q], col[q]);    // CTA-uniform (compile-time true for LOGMIX)
       }
-      xq[q] += row_step; zq[q] += row_step;
+      xq[q] += row_step;
+      if (!BULK) zq[q] += row_step;
     }
   };
   auto emit = [&](int set) {
@@ -261,8 +261,9 @@ __device__ __forceinline__ void stage_rows(const ViewArgs& a, const Geo& g, cons
 #pragma unroll
     for (int q = 0; q < G; ++q) {
       const float4 x = xv[set][q];
-      float4 z = zv[BULK ? 0 : set][q];
-      if (BULK) { z = make_float4(0.f, 0.f, 0.f, 0.f); if (zbulk && on[q]) z = row4[g.j_in0 + lane + 32 * q]; }
+      float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (BULK) { if (zbulk && on[q]) z = row4[g.j_in0 + lane + 32 * q]; }
+      else if (mix) z = zv[set][q];
       float4 o;
       o.x = mix1(x.x, z.x);
       o.y = col[q] + 1 < T ? mix1(x.y, z.y) : 0.f;              // (the last group may reach past the clip's last column:
