@@ -508,6 +508,7 @@ def run_ours(args):
                       else ", fused send + scan"))
     launches_per_step = wl.launches_per_step
     lookahead_on = wl.look
+    front_overlap = wl.front_overlap
     wl.close()
     del wl
     torch.cuda.empty_cache()
@@ -615,6 +616,9 @@ def run_ours(args):
                                 "log-mel(k), statistics(k), views(k-1): the views of the previous batch are launched deferred "
                                 "(assl_two_views_deferred_f32, UpstreamInputPipeline(lookahead=True)); every step runs all the "
                                 "kernels" if lookahead_on else "log-mel(k), statistics(k), views(k)"),
+                 "logmel_launch": ("assl_logmel_deferred_f32 (resident inputs: the kernel transforms its first frame pairs under "
+                                   "the tail of the views before it and waits for them before its first store; "
+                                   "UpstreamInputPipeline(inputs_ready=True))" if front_overlap else "assl_logmel_pitched_f32"),
                  "mixup_bank": ("global FIFO, bank entries read from the peers' rings over NVLink (optional mode)" if gbank
                                 else "rank-local FIFO (as each reference worker's)")},
         "sustained": {"value": world * B * n_sus / (sus_ms * 1e-3), "unit": UNIT, "steps": n_sus, "seconds": sus_ms * 1e-3,
