@@ -156,3 +156,23 @@ def test_unaligned_and_strided_waveforms(mel):
     out = torch.empty_like(ref)
     mel.plan.logmel_into(wide[:, :8000], out)                  # ld = 8004
     assert torch.equal(out, ref)
+
+
+def test_filterbank_parts_are_dealt_without_bank_conflicts():
+    """The plan starts every interval's run where its 16-byte bank group is free and colours the interval totals: no
+    quarter-warp of the log-mel kernel's filterbank pass reads a bank group twice (csrc/plan.cu; what the kernel's
+    shared-memory pipe, its nearest limit, pays for otherwise).  Reported by the plan itself under ASSL_PLAN_DEBUG."""
+    import re
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, os.path.join(root, "tools", "plan_debug.py")], capture_output=True, text=True,
+                         timeout=300)
+    assert res.returncode == 0, res.stderr[-2000:]
+    lines = [l for l in res.stderr.splitlines() if "assl plan:" in l]
+    assert len(lines) >= 3, res.stderr[-2000:]
+    first = lines[0]                                              # the reference's configuration: 64 mels, 60-7800 Hz
+    assert first.startswith("n_mels 64 fmin 60.0 fmax 7800.0") and "96 parts in 3 slots" in first, first
+    for l in lines:
+        m = re.search(r"bank group twice: (\d+), with a total's colour twice: (\d+)", l)
+        assert m and int(m.group(1)) == 0 and int(m.group(2)) == 0, l
